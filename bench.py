@@ -1,0 +1,298 @@
+#!/usr/bin/env python
+"""Benchmark of the B200-native Bayesian-optimisation suggestion path.
+
+Metric (BASELINE.json): acquisition evaluations per second (FP64) at d=32, n_obs=2048, plus
+get_suggestions p50 latency.  A "step" is one warm-up sweep (acquisition_function.py:88-92) over the
+whole candidate set of config C3 (16M candidates, Matern nu=1.5, POI eps=0) at a fixed GP state;
+candidates are sharded over the ranks by contiguous index range and the per-rank bests are merged with
+one all-gather (strong scaling: the global candidate count is fixed).
+
+  value   whole-job candidates/s with candidates resident in HBM (device-timed, max over ranks)
+  e2e     the same through the C-ABI call with HOST (pinned) candidate buffers: host->device copies and
+          the device->host read of the result are inside the timed region
+  roofline  FP64 tensor (DMMA) bound; achieved = algorithmic flops per candidate x candidates / duration of
+          the sweep kernel (CUDA events on its own stream); peak = cuBLAS DGEMM 8192^3 measured in this
+          run (MEASURED_PEAKS.json has no FP64 entry)
+  cpu_baseline  the reference's sklearn/scipy path (oracle/reference_path.py) on the host cores, on a
+          bounded sample of the same workload
+
+`--impl reference` times that CPU path alone (rank 0 only).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+D, N_OBS, NU = 32, 2048, 1.5
+THETA = 1.2                      # log length-scale of the benchmark state (near the fitted optimum)
+METRIC = 'acquisition evals/sec (FP64) at d=32,n_obs=2048'
+UNIT = 'evals/s'
+
+
+def flops_per_eval(n, d):
+    """SURVEY.md section 8d / BASELINE.md: n(3d+10) + n^2 + 4n (triangular variance)."""
+    return n * (3 * d + 10) + n * n + 4 * n
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks and throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    FIELDS = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,'
+              'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
+              'clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, gpu_index):
+        super().__init__(daemon=True)
+        self.gpu_index = gpu_index
+        self.rows = []
+        self.proc = None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(
+                ['nvidia-smi', '-i', str(self.gpu_index), '--query-gpu=' + self.FIELDS,
+                 '--format=csv,noheader,nounits', '-lms', '200'],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.rows.append([c.strip() for c in line.split(',')])
+        except Exception:
+            pass
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+        self.join(timeout=2)
+        sm, reasons, sm_max = [], set(), None
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                sm_max = float(r[1])
+                for name, flag in zip(names, r[3:7]):
+                    if flag.lower().startswith('active'):
+                        reasons.add(name)
+            except (ValueError, IndexError):
+                continue
+        busy = sorted(sm)[len(sm) // 2:] if sm else []
+        return {'sm_mhz': float(np.median(busy)) if busy else None, 'sm_max_mhz': sm_max,
+                'reasons': sorted(reasons), 'samples': len(sm)}
+
+
+def reference_arm(args, rank):
+    """The reference's CPU implementation (sklearn predict + scipy norm) on the host cores."""
+    if rank != 0:
+        return
+    import warnings
+    from oracle import gp_numpy as G
+    from oracle import reference_path as R
+    X, y, bounds = R.synthetic_problem(N_OBS, D)
+    gp = R.make_gp(G.KERNEL_MATERN, float(np.exp(THETA)), NU, 0, np.random.RandomState(1))
+    gp.optimizer = None                    # fixed GP state, as in our arm
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        gp.fit(X, y)
+    y_max = float(y.max())
+    sample = args.cpu_sample
+    rs = np.random.RandomState(7)
+    xc = rs.uniform(0, 1, (sample, D))
+
+    def step():
+        ys = R.acquisition(gp, xc, G.ACQ_POI, y_max, 0.0, 0.0)
+        return int(ys.argmax())
+
+    for _ in range(min(args.warmup, 1)):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = (time.perf_counter() - t0) / args.steps
+    value = sample / dt
+    cores = os.cpu_count()
+    line = {
+        'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
+        'steps': args.steps, 'warmup': min(args.warmup, 1), 'ms_per_step': dt * 1e3,
+        'higher_is_better': True, 'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f64',
+        'data': 'synthetic',
+        'config': workload_config(args, 1),
+        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+                         'sample': '%d candidates per step (one predict call), sklearn %s / scipy path of '
+                                   'oracle/reference_path.py' % (sample, __import__('sklearn').__version__)},
+        'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+    }
+    print(json.dumps(line))
+
+
+def workload_config(args, world):
+    return {'workload': 'C3: BO 32-dim continuous, POI eps=0, matern nu=1.5, n_obs=2048, '
+                        'num_warmup=%d candidates (global), fixed GP state theta=%.1f' % (args.candidates, THETA),
+            'candidates': args.candidates, 'd': D, 'n_obs': N_OBS, 'parallelism': 'shard%d' % world,
+            'l2': 'inputs larger than L2 (candidate shard >= 0.5 GB, K* slabs 310 MB)'}
+
+
+def measure_dgemm_tflops(torch, dev, n=8192, reps=6):
+    a = torch.randn(n, n, dtype=torch.float64, device=dev)
+    b = torch.randn(n, n, dtype=torch.float64, device=dev)
+    torch.matmul(a, b)
+    torch.cuda.synchronize()
+    best = float('inf')
+    for _ in range(reps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        torch.matmul(a, b)
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    del a, b
+    return 2.0 * n ** 3 / (best * 1e-3) / 1e12
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=3)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--candidates', type=int, default=1 << 24)
+    ap.add_argument('--cpu-sample', type=int, default=1 << 15)
+    ap.add_argument('--sweep-impl', type=int, default=1)
+    ap.add_argument('--skip-latency', action='store_true')
+    args = ap.parse_args()
+
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+
+    if args.impl == 'reference':
+        reference_arm(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from polyaxon_b200 import _lib
+    from polyaxon_b200 import dist as pdist
+    from oracle.reference_path import synthetic_problem
+
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py needs a CUDA device: polyaxon_b200 has no CPU path')
+    torch.cuda.set_device(local_rank)
+    dev = torch.device('cuda', local_rank)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+
+    X, y, _ = synthetic_problem(N_OBS, D)
+    y_max = float(y.max())
+    h = _lib.Handle(local_rank)
+    h.set_option('sweep_impl', args.sweep_impl)
+    stream = torch.cuda.current_stream()
+    h.set_stream(stream.cuda_stream)
+    h.set_data(X, y, _lib.KERNEL_MATERN, NU)
+    h.set_theta(THETA)
+
+    lo, hi = pdist.shard_range(args.candidates, rank, world)
+    n_local = hi - lo
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(1234 + rank)
+    xc_dev = torch.rand(n_local, D, dtype=torch.float64, device=dev, generator=gen)
+    xc_host = torch.empty(n_local, D, dtype=torch.float64, pin_memory=True)
+    xc_host.copy_(xc_dev)
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def step_device():
+        v, i, _ = h.sweep_dev(xc_dev.data_ptr(), n_local, _lib.ACQ_POI, y_max, eps=0.0, idx_base=lo)
+        return pdist.merge_best(v, i if n_local else -1, device=dev)
+
+    def step_host():
+        v, i, _ = h.sweep(xc_host.numpy(), _lib.ACQ_POI, y_max, eps=0.0, idx_base=lo)
+        return pdist.merge_best(v, i if n_local else -1, device=dev)
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        launches0 = h.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        kernel_ms = 0.0
+        e0.record(stream)
+        result = None
+        for _ in range(steps):
+            result = fn()
+            kernel_ms += h.last_sweep_stats()[0]
+        e1.record(stream)
+        barrier()
+        ms = max_over_ranks(e0.elapsed_time(e1) / steps)
+        return ms, kernel_ms / steps, h.launch_count() - launches0, result
+
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    ms_dev, kernel_ms, launches, best_dev = timed(step_device, args.steps, args.warmup)
+    clocks = sampler.stop() if sampler else None
+    ms_e2e, _, _, best_host = timed(step_host, args.steps, max(1, min(args.warmup, 1)))
+    assert best_dev == best_host, 'device-resident and host-buffer sweeps disagree: %r %r' % (best_dev, best_host)
+
+    if rank == 0:
+        value = args.candidates / (ms_dev * 1e-3)
+        e2e = args.candidates / (ms_e2e * 1e-3)
+        fpe = flops_per_eval(N_OBS, D)
+        achieved = fpe * n_local / (kernel_ms * 1e-3) / 1e12
+        peak = measure_dgemm_tflops(torch, dev)
+        line = {
+            'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
+            'warmup': args.warmup, 'ms_per_step': ms_dev, 'higher_is_better': True, 'scaling': 'strong',
+            'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
+            'config': workload_config(args, world),
+            'e2e': {'value': e2e, 'unit': UNIT, 'h2d_bytes_per_step': n_local * D * 8 * world,
+                    'd2h_bytes_per_step': 16 * world, 'ms_per_step': ms_e2e},
+            'gpu_launches': launches,
+            'clocks': clocks,
+            'roofline': {'bound': 'tensor', 'achieved': achieved, 'peak': peak, 'unit': 'TFLOP/s',
+                         'frac': achieved / peak, 'traffic': None,
+                         'kernel': 'sweep_tma_kernel' if args.sweep_impl == 1 else 'sweep_simple_kernel',
+                         'kernel_ms_per_launch': kernel_ms,
+                         'flops_per_eval': fpe,
+                         'peak_source': 'cuBLAS DGEMM 8192^3 FP64 measured in this run (best of 6); '
+                                        'MEASURED_PEAKS.json has no FP64 figure'},
+            'best': {'value': best_dev[0], 'index': best_dev[1]},
+        }
+        # CPU baseline beside it: bounded sample, all host cores
+        try:
+            import io
+            import contextlib
+            buf = io.StringIO()
+            with contextlib.redirect_stdout(buf):
+                ref_args = argparse.Namespace(**vars(args))
+                ref_args.steps, ref_args.warmup = 2, 1
+                reference_arm(ref_args, 0)
+            ref = json.loads(buf.getvalue().strip().splitlines()[-1])
+            line['cpu_baseline'] = ref['cpu_baseline']
+        except Exception as exc:  # the baseline must never hide the GPU numbers
+            line['cpu_baseline'] = {'value': None, 'unit': UNIT, 'cores': os.cpu_count(), 'kind': 'port',
+                                    'sample': 'failed: %r' % (exc,)}
+        print(json.dumps(line))
+    h.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()

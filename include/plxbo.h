@@ -1,0 +1,110 @@
+/*
+ * plxbo.h -- C ABI of the B200-native Bayesian-optimisation suggestion path.
+ *
+ * The reference (Polyaxon 0.2.8, polyaxon/hpsearch/search_managers/bayesian_optimization/) is pure
+ * Python and has no FFI of its own: all arithmetic happens inside scikit-learn / scipy calls.  Each
+ * entry point below replaces one of those call sites; the reference file:line is given beside it.
+ * INTEGRATION.md shows the ctypes stub a maintainer of the reference would bind these with.
+ *
+ * Conventions
+ *   - plain C types; every matrix is float64, row-major (numpy C order), caller-owned;
+ *   - pointers are HOST pointers unless the parameter name ends in _dev;
+ *   - every function returns a status (0 = ok); plx_last_error() gives the message;
+ *   - PLX_ERR_NOT_PD reports a Cholesky failure -- the Python layer raises numpy.linalg.LinAlgError,
+ *     which is what sklearn does at _gpr.py:351-361;
+ *   - one handle per process and device, not thread-safe; work is issued on the handle's stream
+ *     (plx_bo_set_stream) and functions that return results to the host synchronise that stream;
+ *   - there is no CPU fallback: without a CUDA device plx_bo_create fails.
+ */
+#ifndef PLXBO_H
+#define PLXBO_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct plx_bo* plx_bo_handle;
+
+enum {
+  PLX_OK = 0,
+  PLX_ERR_INVALID = 1,     /* bad argument */
+  PLX_ERR_CUDA = 2,        /* CUDA runtime / driver error */
+  PLX_ERR_NOT_PD = 3,      /* kernel matrix not positive definite */
+  PLX_ERR_STATE = 4,       /* call order: data / theta not set */
+  PLX_ERR_UNSUPPORTED = 5  /* e.g. Matern nu without a closed form */
+};
+
+/* kernels: acquisition_function.py:36-40 (sklearn RBF / Matern, scalar length scale) */
+enum { PLX_KERNEL_RBF = 0, PLX_KERNEL_MATERN = 1 };
+/* acquisition functions: acquisition_function.py:48-68 */
+enum { PLX_ACQ_UCB = 0, PLX_ACQ_EI = 1, PLX_ACQ_POI = 2 };
+
+int plx_bo_create(int device, plx_bo_handle* out);
+void plx_bo_destroy(plx_bo_handle h);
+const char* plx_last_error(plx_bo_handle h);   /* h may be NULL: error of the last failed create */
+const char* plx_version(void);
+
+/* Use the caller's CUDA stream (a cudaStream_t passed as void*); NULL restores the handle's own. */
+int plx_bo_set_stream(plx_bo_handle h, void* stream);
+
+/* Options: "sweep_impl" (1 = TMA ring [default], 0 = plain-load cross-check). */
+int plx_bo_set_option(plx_bo_handle h, const char* name, long long value);
+
+/* Observations.  Replaces the arguments of GaussianProcessRegressor.fit(X, y) at optimizer.py:21
+ * and the kernel construction at acquisition_function.py:36-46.  nu must be 0.5, 1.5, 2.5 or inf
+ * for PLX_KERNEL_MATERN; jitter is sklearn's `alpha` (1e-10 in the reference). */
+int plx_gp_set_data(plx_bo_handle h, const double* X, const double* y, int n, int d, int kernel, double nu,
+                    double jitter);
+
+/* Batched log-marginal likelihood and d/dtheta at B values of theta = log(length_scale).
+ * Replaces GaussianProcessRegressor.log_marginal_likelihood(theta, eval_gradient=True)
+ * (sklearn _gpr.py:583-654).  A non-PD member yields lml = -inf, grad = 0 as sklearn does (:592-593).
+ * grad may be NULL. */
+int plx_gp_lml(plx_bo_handle h, const double* thetas, int B, double* lml, double* grad);
+
+/* Hyper-parameter fit.  Replaces the optimiser loop of GaussianProcessRegressor.fit
+ * (sklearn _gpr.py:299-368): one bounded L-BFGS-B run from theta0 and one from each of
+ * theta_restarts[0..n_restarts), all advanced together; the run with the smallest -LML wins
+ * (first minimum, as numpy.argmin at :336-337) and the posterior state is built at its theta.
+ * per_run (nullable) receives n_restarts+1 rows of {theta_start, theta_opt, lml_opt, n_evals}. */
+int plx_gp_fit(plx_bo_handle h, double theta0, const double* theta_restarts, int n_restarts, double theta_lo,
+               double theta_hi, double* theta_star, double* lml_star, double* per_run);
+
+/* Posterior state at a fixed theta: L = chol(K + jitter I), alpha = K^-1 y, L^-1.
+ * Replaces sklearn _gpr.py:349-367. */
+int plx_gp_set_theta(plx_bo_handle h, double theta);
+
+/* Copy the state back for verification: L (n x n, lower), alpha (n), Linv (n x n); any may be NULL. */
+int plx_gp_get_state(plx_bo_handle h, double* L, double* alpha, double* Linv);
+
+/* Warm-up sweep.  Replaces UtilityFunction.max_compute's sampling stage
+ * (acquisition_function.py:88-92) including compute() -> gp.predict(return_std=True)
+ * (:48-68, sklearn _gpr.py:446-500).  Candidates are N x d; best_index is idx_base + the position of
+ * the first maximum (numpy.argmax semantics, NaN wins); best_x receives that candidate (d doubles).
+ * mean / std / acq (nullable, HOST, N doubles each) receive the per-candidate values. */
+int plx_acq_sweep(plx_bo_handle h, const double* Xc, long long N, long long idx_base, int acq, double kappa,
+                  double eps, double y_max, double* best_value, long long* best_index, double* best_x,
+                  double* mean, double* std, double* acq_values);
+
+/* Same, candidates already resident in device memory (no per-candidate dumps). */
+int plx_acq_sweep_dev(plx_bo_handle h, const double* Xc_dev, long long N, long long idx_base, int acq,
+                      double kappa, double eps, double y_max, double* best_value, long long* best_index,
+                      double* best_x);
+
+/* Device time in milliseconds of the main sweep kernel(s) of the last plx_acq_sweep* call, measured
+ * with CUDA events on the launching stream, and how many kernels that call launched. */
+int plx_last_sweep_stats(plx_bo_handle h, double* kernel_ms, long long* launches);
+
+/* Total number of kernels this handle has launched since creation. */
+long long plx_launch_count(plx_bo_handle h);
+
+/* Host-only: the one-variable L-BFGS-B used by plx_gp_fit, driven by a callback (for testing against
+ * scipy.optimize.minimize(method="L-BFGS-B", jac=True), sklearn _gpr.py:660-666). */
+typedef void (*plx_fg_callback)(double x, double* f, double* g, void* user);
+int plx_lbfgsb1d_minimize(plx_fg_callback fg, void* user, double x0, double lo, double hi, double* x, double* f,
+                          int* n_evals, int* n_iters, int* status);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PLXBO_H */

@@ -1,0 +1,39 @@
+"""In-tree build of libplxbo.so (hand-written CUDA for sm_100a + the C ABI).  nvcc cross-compiles
+without a GPU; the .so is git-ignored but travels to the GPU box with the repo snapshot."""
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, 'csrc')
+OUT = os.path.join(HERE, 'libplxbo.so')
+SOURCES = ['api.cu']
+HEADERS = ['mma_f64.cuh', 'gp_kernels.cuh', 'sweep.cuh', 'lbfgsb1d.h', os.path.join('..', '..', 'include', 'plxbo.h')]
+NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
+              '-shared', '-Xcompiler', '-fPIC']
+
+
+def up_to_date():
+    if not os.path.exists(OUT):
+        return False
+    t = os.path.getmtime(OUT)
+    deps = [os.path.join(CSRC, f) for f in SOURCES + HEADERS]
+    return all(os.path.getmtime(p) <= t for p in deps if os.path.exists(p))
+
+
+def build(force=False, verbose=False):
+    if not force and up_to_date():
+        return OUT
+    nvcc = os.environ.get('NVCC', 'nvcc')
+    cmd = [nvcc] + NVCC_FLAGS + (['-Xptxas', '-v'] if verbose else []) + ['-o', OUT] + SOURCES
+    res = subprocess.run(cmd, cwd=CSRC, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if res.returncode != 0:
+        sys.stderr.write(res.stdout)
+        raise RuntimeError('nvcc failed building libplxbo.so')
+    if verbose:
+        print(res.stdout)
+    return OUT
+
+
+if __name__ == '__main__':
+    print(build(force='--force' in sys.argv, verbose='-v' in sys.argv))

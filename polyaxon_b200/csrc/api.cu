@@ -1,0 +1,560 @@
+// C ABI of libplxbo.so: handle, workspace management and launch sequences.
+// Declarations and the reference call site each entry point replaces: include/plxbo.h.
+#include "../../include/plxbo.h"
+#include "sweep.cuh"
+#include "lbfgsb1d.h"
+
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace plx;
+
+namespace {
+std::string g_create_error;
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+}  // namespace
+
+struct plx_bo {
+  int device = 0, num_sms = 148;
+  cudaStream_t own_stream = nullptr, stream = nullptr, copy_stream = nullptr;
+  std::string err;
+  long long launches = 0;
+  EncodeTiledFn encode = nullptr;
+
+  // observations
+  bool have_data = false;
+  int n = 0, d = 0, npad = 0, nb = 0, kind = 0;
+  double jitter = 1e-10;
+  double* dX = nullptr; size_t x_cap = 0;
+  double* dy = nullptr; size_t y_cap = 0;
+
+  // batched fit workspace
+  int bcap = 0, wnpad = 0;
+  BatchPtrs bp{};
+  double *d_thetas = nullptr, *d_logdet = nullptr, *d_w = nullptr, *d_alpha = nullptr, *d_partial = nullptr,
+         *d_lml = nullptr, *d_grad = nullptr;
+  int* d_info = nullptr;
+  int ntri = 0;
+
+  // posterior state used by the sweep
+  bool have_state = false, state_factor_valid = false;
+  double theta = 0.0;
+  double* dZ = nullptr; size_t z_cap = 0;
+  double* d_alpha_state = nullptr; size_t as_cap = 0;
+  double* dKs = nullptr; size_t ks_cap = 0;
+  CUtensorMap tmZ, tmK;
+
+  // sweep buffers
+  double* d_blk_val = nullptr; long long* d_blk_idx = nullptr;
+  double* d_best_val = nullptr; long long* d_best_idx = nullptr;
+  double* dcand[2] = {nullptr, nullptr}; size_t cand_cap = 0;
+  double* d_out[3] = {nullptr, nullptr, nullptr}; size_t out_cap = 0;
+  cudaEvent_t ev_copy[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
+  std::vector<cudaEvent_t> ev_pool;
+  int sweep_impl = 1;
+  double last_ms = 0.0; long long last_launches = 0;
+};
+
+#define CK(call)                                                                            \
+  do {                                                                                      \
+    cudaError_t e_ = (call);                                                                \
+    if (e_ != cudaSuccess) {                                                                \
+      h->err = std::string(#call) + ": " + cudaGetErrorString(e_);                          \
+      return PLX_ERR_CUDA;                                                                  \
+    }                                                                                       \
+  } while (0)
+
+#define LAUNCH_CHECK(name)                                                                  \
+  do {                                                                                      \
+    ++h->launches;                                                                          \
+    cudaError_t e_ = cudaGetLastError();                                                    \
+    if (e_ != cudaSuccess) {                                                                \
+      h->err = std::string("launch of " name ": ") + cudaGetErrorString(e_);                \
+      return PLX_ERR_CUDA;                                                                  \
+    }                                                                                       \
+  } while (0)
+
+static int fail(plx_bo* h, int code, const std::string& msg) { h->err = msg; return code; }
+
+template <typename T>
+static int ensure(plx_bo* h, T*& p, size_t& cap, size_t need) {
+  if (need <= cap && p != nullptr) return PLX_OK;
+  if (p) CK(cudaFree(p));
+  p = nullptr; cap = 0;
+  CK(cudaMalloc(reinterpret_cast<void**>(&p), need * sizeof(T)));
+  cap = need;
+  return PLX_OK;
+}
+
+static int kernel_kind(int kernel, double nu, int* kind) {
+  if (kernel == PLX_KERNEL_RBF) { *kind = K_RBF; return PLX_OK; }
+  if (kernel != PLX_KERNEL_MATERN) return PLX_ERR_INVALID;
+  if (nu == 0.5) *kind = K_M05;
+  else if (nu == 1.5) *kind = K_M15;
+  else if (nu == 2.5) *kind = K_M25;
+  else if (std::isinf(nu) && nu > 0) *kind = K_RBF;
+  else return PLX_ERR_UNSUPPORTED;
+  return PLX_OK;
+}
+
+extern "C" const char* plx_version(void) { return "plxbo 0.1 (sm_100a)"; }
+
+extern "C" const char* plx_last_error(plx_bo_handle h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+extern "C" int plx_bo_create(int device, plx_bo_handle* out) {
+  if (!out) return PLX_ERR_INVALID;
+  *out = nullptr;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0) {
+    g_create_error = std::string("no CUDA device: ") + cudaGetErrorString(e) +
+                     " (this library has no CPU path)";
+    return PLX_ERR_CUDA;
+  }
+  if (device < 0 || device >= count) { g_create_error = "device index out of range"; return PLX_ERR_INVALID; }
+  plx_bo* h = new plx_bo();
+  h->device = device;
+  auto bail = [&](const std::string& m) { g_create_error = m; delete h; return PLX_ERR_CUDA; };
+  if (cudaSetDevice(device) != cudaSuccess) return bail("cudaSetDevice failed");
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return bail("cudaGetDeviceProperties failed");
+  if (prop.major != 10) return bail(std::string("device is sm_") + std::to_string(prop.major * 10 + prop.minor) +
+                                    "; this library is built for sm_100a only");
+  h->num_sms = prop.multiProcessorCount;
+  if (cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking) != cudaSuccess) return bail("stream create failed");
+  if (cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking) != cudaSuccess) return bail("stream create failed");
+  h->stream = h->own_stream;
+  for (int i = 0; i < 2; ++i) {
+    if (cudaEventCreateWithFlags(&h->ev_copy[i], cudaEventDisableTiming) != cudaSuccess) return bail("event create failed");
+    if (cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming) != cudaSuccess) return bail("event create failed");
+  }
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess || !fn ||
+      qres != cudaDriverEntryPointSuccess)
+    return bail("cuTensorMapEncodeTiled not available from the driver");
+  h->encode = reinterpret_cast<EncodeTiledFn>(fn);
+  // opt in to large dynamic shared memory once
+  cudaFuncSetAttribute(potf2_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, POTF_SMEM);
+  cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM);
+  cudaFuncSetAttribute(chol_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM);
+  cudaFuncSetAttribute(trtri_t_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM);
+  cudaFuncSetAttribute(trtri_u_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM);
+  cudaFuncSetAttribute(kinv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM);
+  cudaFuncSetAttribute(sweep_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SWEEP_SMEM);
+  cudaFuncSetAttribute(sweep_simple_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SWEEP_SIMPLE_SMEM);
+  if (cudaGetLastError() != cudaSuccess) return bail("cudaFuncSetAttribute failed (is the library built for this GPU?)");
+  if (cudaMalloc(&h->d_blk_val, sizeof(double) * 1024) != cudaSuccess ||
+      cudaMalloc(&h->d_blk_idx, sizeof(long long) * 1024) != cudaSuccess ||
+      cudaMalloc(&h->d_best_val, sizeof(double)) != cudaSuccess ||
+      cudaMalloc(&h->d_best_idx, sizeof(long long)) != cudaSuccess)
+    return bail("cudaMalloc failed");
+  *out = h;
+  return PLX_OK;
+}
+
+extern "C" void plx_bo_destroy(plx_bo_handle h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  cudaDeviceSynchronize();
+  void* ptrs[] = {h->dX, h->dy, h->bp.A, h->bp.L, h->bp.U, h->bp.W, h->bp.T, h->d_thetas, h->d_logdet, h->d_w,
+                  h->d_alpha, h->d_partial, h->d_lml, h->d_grad, h->d_info, h->dZ, h->d_alpha_state, h->dKs,
+                  h->d_blk_val, h->d_blk_idx, h->d_best_val, h->d_best_idx, h->dcand[0], h->dcand[1],
+                  h->d_out[0], h->d_out[1], h->d_out[2]};
+  for (void* p : ptrs) if (p) cudaFree(p);
+  for (int i = 0; i < 2; ++i) { if (h->ev_copy[i]) cudaEventDestroy(h->ev_copy[i]); if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]); }
+  for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
+  if (h->own_stream) cudaStreamDestroy(h->own_stream);
+  if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+  delete h;
+}
+
+extern "C" int plx_bo_set_stream(plx_bo_handle h, void* stream) {
+  if (!h) return PLX_ERR_INVALID;
+  h->stream = stream ? reinterpret_cast<cudaStream_t>(stream) : h->own_stream;
+  return PLX_OK;
+}
+
+extern "C" int plx_bo_set_option(plx_bo_handle h, const char* name, long long value) {
+  if (!h || !name) return PLX_ERR_INVALID;
+  if (std::strcmp(name, "sweep_impl") == 0 && (value == 0 || value == 1)) { h->sweep_impl = static_cast<int>(value); return PLX_OK; }
+  return fail(h, PLX_ERR_INVALID, std::string("unknown option or value: ") + name);
+}
+
+extern "C" long long plx_launch_count(plx_bo_handle h) { return h ? h->launches : 0; }
+
+extern "C" int plx_gp_set_data(plx_bo_handle h, const double* X, const double* y, int n, int d, int kernel,
+                               double nu, double jitter) {
+  if (!h || !X || !y || n <= 0 || d <= 0) return h ? fail(h, PLX_ERR_INVALID, "set_data: bad arguments") : PLX_ERR_INVALID;
+  int kind;
+  const int rc = kernel_kind(kernel, nu, &kind);
+  if (rc == PLX_ERR_UNSUPPORTED)
+    return fail(h, rc, "Matern nu must be 0.5, 1.5, 2.5 or inf on the device path (general nu needs Bessel K_nu)");
+  if (rc != PLX_OK) return fail(h, rc, "unknown kernel id");
+  CK(cudaSetDevice(h->device));
+  h->n = n; h->d = d; h->kind = kind; h->jitter = jitter;
+  h->npad = (n + 127) / 128 * 128; h->nb = h->npad / 128;
+  h->have_data = false; h->have_state = false; h->state_factor_valid = false;
+  int r;
+  if ((r = ensure(h, h->dX, h->x_cap, static_cast<size_t>(n) * d)) != PLX_OK) return r;
+  if ((r = ensure(h, h->dy, h->y_cap, static_cast<size_t>(h->npad))) != PLX_OK) return r;
+  CK(cudaMemsetAsync(h->dy, 0, sizeof(double) * h->npad, h->stream));
+  CK(cudaMemcpyAsync(h->dX, X, sizeof(double) * n * d, cudaMemcpyHostToDevice, h->stream));
+  CK(cudaMemcpyAsync(h->dy, y, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  h->have_data = true;
+  return PLX_OK;
+}
+
+static int ensure_batch(plx_bo* h, int B) {
+  if (B <= h->bcap && h->wnpad == h->npad) return PLX_OK;
+  const int cap = std::max(B, h->wnpad == h->npad ? h->bcap : 0);
+  void* old[] = {h->bp.A, h->bp.L, h->bp.U, h->bp.W, h->bp.T, h->d_thetas, h->d_logdet, h->d_w, h->d_alpha,
+                 h->d_partial, h->d_lml, h->d_grad, h->d_info};
+  for (void* p : old) if (p) CK(cudaFree(p));
+  h->bp = BatchPtrs{}; h->d_thetas = h->d_logdet = h->d_w = h->d_alpha = h->d_partial = h->d_lml = h->d_grad = nullptr;
+  h->d_info = nullptr; h->bcap = 0; h->state_factor_valid = false;
+  const size_t mat = static_cast<size_t>(h->npad) * h->npad, blk = static_cast<size_t>(h->nb) * 128 * 128;
+  const int nt32 = (h->n + 31) / 32;
+  h->ntri = nt32 * (nt32 + 1) / 2;
+  CK(cudaMalloc(&h->bp.A, sizeof(double) * mat * cap));
+  CK(cudaMalloc(&h->bp.L, sizeof(double) * mat * cap));
+  CK(cudaMalloc(&h->bp.U, sizeof(double) * mat * cap));
+  CK(cudaMalloc(&h->bp.W, sizeof(double) * blk * cap));
+  CK(cudaMalloc(&h->bp.T, sizeof(double) * blk * cap));
+  CK(cudaMalloc(&h->d_thetas, sizeof(double) * cap));
+  CK(cudaMalloc(&h->d_logdet, sizeof(double) * cap));
+  CK(cudaMalloc(&h->d_w, sizeof(double) * h->npad * cap));
+  CK(cudaMalloc(&h->d_alpha, sizeof(double) * h->npad * cap));
+  CK(cudaMalloc(&h->d_partial, sizeof(double) * h->ntri * cap));
+  CK(cudaMalloc(&h->d_lml, sizeof(double) * cap));
+  CK(cudaMalloc(&h->d_grad, sizeof(double) * cap));
+  CK(cudaMalloc(&h->d_info, sizeof(int) * cap));
+  h->bp.mat_stride = mat; h->bp.blk_stride = blk;
+  h->bcap = cap; h->wnpad = h->npad;
+  return PLX_OK;
+}
+
+// Launch sequence of one batched LML (+gradient) evaluation; results stay on the device.
+static int launch_lml(plx_bo* h, int B, bool want_grad) {
+  cudaStream_t st = h->stream;
+  const int npad = h->npad, nb = h->nb, n = h->n;
+  CK(cudaMemsetAsync(h->d_logdet, 0, sizeof(double) * B, st));
+  CK(cudaMemsetAsync(h->d_info, 0, sizeof(int) * B, st));
+  kmat_kernel<0><<<dim3(npad / 32, npad / 32, B), 256, 0, st>>>(h->dX, n, h->d, npad, h->d_thetas, h->kind,
+                                                               h->jitter, h->bp, nullptr, nullptr, 0);
+  LAUNCH_CHECK("kmat_kernel");
+  for (int k = 0; k < nb; ++k) {
+    potf2_inv_kernel<<<B, 256, POTF_SMEM, st>>>(h->bp, k, n, npad, h->d_logdet, h->d_info);
+    LAUNCH_CHECK("potf2_inv_kernel");
+    const int T = nb - k - 1;
+    if (T > 0) {
+      chol_panel_kernel<<<dim3(T, B), 256, GEMM_SMEM, st>>>(h->bp, k, npad);
+      LAUNCH_CHECK("chol_panel_kernel");
+      chol_syrk_kernel<<<dim3(T * (T + 1) / 2, B), 256, GEMM_SMEM, st>>>(h->bp, k, npad);
+      LAUNCH_CHECK("chol_syrk_kernel");
+    }
+  }
+  for (int j = 1; j < nb; ++j) {
+    trtri_t_kernel<<<dim3(j, B), 256, GEMM_SMEM, st>>>(h->bp, j, npad);
+    LAUNCH_CHECK("trtri_t_kernel");
+    trtri_u_kernel<<<dim3(j, B), 256, GEMM_SMEM, st>>>(h->bp, j, npad);
+    LAUNCH_CHECK("trtri_u_kernel");
+  }
+  uty_kernel<<<dim3(npad / 32, B), 256, 0, st>>>(h->bp, h->dy, npad, h->d_w);
+  LAUNCH_CHECK("uty_kernel");
+  uw_kernel<<<dim3(npad / 8, B), 256, 0, st>>>(h->bp, h->d_w, npad, h->d_alpha);
+  LAUNCH_CHECK("uw_kernel");
+  if (want_grad) {
+    kinv_kernel<<<dim3(nb * (nb + 1) / 2, B), 256, GEMM_SMEM, st>>>(h->bp, npad);
+    LAUNCH_CHECK("kinv_kernel");
+    kmat_kernel<1><<<dim3(h->ntri, 1, B), 256, 0, st>>>(h->dX, n, h->d, npad, h->d_thetas, h->kind, h->jitter,
+                                                       h->bp, h->d_alpha, h->d_partial, h->ntri);
+    LAUNCH_CHECK("kmat_kernel<grad>");
+  }
+  lml_finalize_kernel<<<B, 256, 0, st>>>(h->dy, h->d_alpha, h->d_logdet, h->d_info,
+                                         want_grad ? h->d_partial : nullptr, h->ntri, n, npad, h->d_lml,
+                                         want_grad ? h->d_grad : nullptr);
+  LAUNCH_CHECK("lml_finalize_kernel");
+  return PLX_OK;
+}
+
+static int eval_lml(plx_bo* h, const double* thetas, int B, double* lml, double* grad) {
+  int r;
+  if ((r = ensure_batch(h, B)) != PLX_OK) return r;
+  h->state_factor_valid = false;
+  CK(cudaMemcpyAsync(h->d_thetas, thetas, sizeof(double) * B, cudaMemcpyHostToDevice, h->stream));
+  if ((r = launch_lml(h, B, grad != nullptr)) != PLX_OK) return r;
+  CK(cudaMemcpyAsync(lml, h->d_lml, sizeof(double) * B, cudaMemcpyDeviceToHost, h->stream));
+  if (grad) CK(cudaMemcpyAsync(grad, h->d_grad, sizeof(double) * B, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return PLX_OK;
+}
+
+extern "C" int plx_gp_lml(plx_bo_handle h, const double* thetas, int B, double* lml, double* grad) {
+  if (!h || !thetas || !lml || B <= 0) return h ? fail(h, PLX_ERR_INVALID, "gp_lml: bad arguments") : PLX_ERR_INVALID;
+  if (!h->have_data) return fail(h, PLX_ERR_STATE, "gp_lml: call plx_gp_set_data first");
+  CK(cudaSetDevice(h->device));
+  return eval_lml(h, thetas, B, lml, grad);
+}
+
+static int make_map(plx_bo* h, CUtensorMap* map, double* base, size_t rows, size_t cols) {
+  cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(cols) * 8};
+  cuuint32_t box[2] = {KCH, TILE};
+  cuuint32_t estr[2] = {1, 1};
+  const CUresult r = h->encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, base, dims, strides, box, estr,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(h, PLX_ERR_CUDA, "cuTensorMapEncodeTiled failed with code " + std::to_string(r));
+  return PLX_OK;
+}
+
+extern "C" int plx_gp_set_theta(plx_bo_handle h, double theta) {
+  if (!h) return PLX_ERR_INVALID;
+  if (!h->have_data) return fail(h, PLX_ERR_STATE, "gp_set_theta: call plx_gp_set_data first");
+  CK(cudaSetDevice(h->device));
+  h->have_state = false;
+  double lml;
+  int r = eval_lml(h, &theta, 1, &lml, nullptr);
+  if (r != PLX_OK) return r;
+  if (std::isinf(lml) && lml < 0)
+    return fail(h, PLX_ERR_NOT_PD, "kernel matrix is not positive definite at theta=" + std::to_string(theta));
+  const size_t mat = static_cast<size_t>(h->npad) * h->npad;
+  if ((r = ensure(h, h->dZ, h->z_cap, mat)) != PLX_OK) return r;
+  if ((r = ensure(h, h->d_alpha_state, h->as_cap, static_cast<size_t>(h->npad))) != PLX_OK) return r;
+  if ((r = ensure(h, h->dKs, h->ks_cap, static_cast<size_t>(h->num_sms) * 128 * h->npad)) != PLX_OK) return r;
+  transpose_kernel<<<dim3(h->npad / 32, h->npad / 32), 256, 0, h->stream>>>(h->bp.U, h->dZ, h->npad);
+  LAUNCH_CHECK("transpose_kernel");
+  CK(cudaMemcpyAsync(h->d_alpha_state, h->d_alpha, sizeof(double) * h->npad, cudaMemcpyDeviceToDevice, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  if ((r = make_map(h, &h->tmZ, h->dZ, h->npad, h->npad)) != PLX_OK) return r;
+  if ((r = make_map(h, &h->tmK, h->dKs, static_cast<size_t>(h->num_sms) * 128, h->npad)) != PLX_OK) return r;
+  h->theta = theta; h->have_state = true; h->state_factor_valid = true;
+  return PLX_OK;
+}
+
+extern "C" int plx_gp_get_state(plx_bo_handle h, double* L, double* alpha, double* Linv) {
+  if (!h) return PLX_ERR_INVALID;
+  if (!h->have_state) return fail(h, PLX_ERR_STATE, "gp_get_state: no posterior state");
+  CK(cudaSetDevice(h->device));
+  const size_t n = h->n, npad = h->npad;
+  if (L) {
+    if (!h->state_factor_valid) return fail(h, PLX_ERR_STATE, "gp_get_state: L was overwritten by a later plx_gp_lml");
+    CK(cudaMemcpy2DAsync(L, n * 8, h->bp.L, npad * 8, n * 8, n, cudaMemcpyDeviceToHost, h->stream));
+  }
+  if (Linv) CK(cudaMemcpy2DAsync(Linv, n * 8, h->dZ, npad * 8, n * 8, n, cudaMemcpyDeviceToHost, h->stream));
+  if (alpha) CK(cudaMemcpyAsync(alpha, h->d_alpha_state, n * 8, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  if (L)      // the factor's strict upper triangle is never written on the device
+    for (size_t i = 0; i < n; ++i) for (size_t j = i + 1; j < n; ++j) L[i * n + j] = 0.0;
+  if (Linv)
+    for (size_t i = 0; i < n; ++i) for (size_t j = i + 1; j < n; ++j) Linv[i * n + j] = 0.0;
+  return PLX_OK;
+}
+
+extern "C" int plx_gp_fit(plx_bo_handle h, double theta0, const double* theta_restarts, int n_restarts,
+                          double theta_lo, double theta_hi, double* theta_star, double* lml_star, double* per_run) {
+  if (!h || n_restarts < 0 || (n_restarts > 0 && !theta_restarts) || !(theta_lo < theta_hi))
+    return h ? fail(h, PLX_ERR_INVALID, "gp_fit: bad arguments") : PLX_ERR_INVALID;
+  if (!h->have_data) return fail(h, PLX_ERR_STATE, "gp_fit: call plx_gp_set_data first");
+  CK(cudaSetDevice(h->device));
+  const int R = n_restarts + 1;
+  std::vector<Lbfgsb1D> runs(R);
+  std::vector<double> starts(R);
+  for (int r = 0; r < R; ++r) {
+    starts[r] = (r == 0) ? theta0 : theta_restarts[r - 1];
+    runs[r].lo = theta_lo; runs[r].hi = theta_hi;
+    runs[r].start(starts[r]);
+  }
+  std::vector<double> xs(R), fs(R), gs(R);
+  std::vector<int> who(R);
+  for (;;) {
+    int m = 0;
+    for (int r = 0; r < R; ++r) if (!runs[r].done) { who[m] = r; xs[m] = runs[r].x_eval; ++m; }
+    if (m == 0) break;
+    const int rc = eval_lml(h, xs.data(), m, fs.data(), gs.data());
+    if (rc != PLX_OK) return rc;
+    for (int i = 0; i < m; ++i) runs[who[i]].feed(-fs[i], -gs[i]);   // minimise -LML
+  }
+  int best = 0;
+  for (int r = 1; r < R; ++r) if (runs[r].f < runs[best].f) best = r;     // first minimum, like numpy.argmin
+  if (per_run)
+    for (int r = 0; r < R; ++r) {
+      per_run[4 * r + 0] = starts[r]; per_run[4 * r + 1] = runs[r].x;
+      per_run[4 * r + 2] = -runs[r].f; per_run[4 * r + 3] = runs[r].nfev;
+    }
+  if (theta_star) *theta_star = runs[best].x;
+  if (lml_star) *lml_star = -runs[best].f;
+  return plx_gp_set_theta(h, runs[best].x);
+}
+
+// ---------------------------------------------------------------------------------------------
+// sweep
+// ---------------------------------------------------------------------------------------------
+static void fill_params(plx_bo* h, SweepParams& p, const double* Xc_dev, long long N, long long idx_base, int acq,
+                        double kappa, double eps, double y_max) {
+  p.Xc = Xc_dev; p.N = N; p.idx_base = idx_base;
+  p.d = h->d; p.n = h->n; p.npad = h->npad; p.n16 = (h->n + 15) / 16 * 16;
+  p.X = h->dX; p.alpha = h->d_alpha_state; p.Z = h->dZ; p.ell = std::exp(h->theta);
+  p.kind = h->kind; p.acq = acq; p.kappa = kappa; p.eps = eps; p.y_max = y_max;
+  p.Ks = h->dKs; p.out_mean = p.out_std = p.out_acq = nullptr;
+  p.blk_val = h->d_blk_val; p.blk_idx = h->d_blk_idx;
+}
+
+static int launch_sweep(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cudaEvent_t e1) {
+  const long long ntiles = (p.N + 127) / 128;
+  const int grid = static_cast<int>(std::min<long long>(ntiles, h->num_sms));
+  if (grid <= 0) return PLX_OK;
+  if (e0) CK(cudaEventRecord(e0, h->stream));
+  if (h->sweep_impl == 1) {
+    sweep_tma_kernel<<<grid, 384, SWEEP_SMEM, h->stream>>>(h->tmZ, h->tmK, p);
+    LAUNCH_CHECK("sweep_tma_kernel");
+  } else {
+    sweep_simple_kernel<<<grid, 256, SWEEP_SIMPLE_SMEM, h->stream>>>(p);
+    LAUNCH_CHECK("sweep_simple_kernel");
+  }
+  if (e1) CK(cudaEventRecord(e1, h->stream));
+  sweep_merge_kernel<<<1, 32, 0, h->stream>>>(h->d_blk_val, h->d_blk_idx, grid, h->d_best_val, h->d_best_idx);
+  LAUNCH_CHECK("sweep_merge_kernel");
+  return PLX_OK;
+}
+
+static int reset_best(plx_bo* h) {
+  const double ninf = -INFINITY; const long long big = 0x7fffffffffffffffLL;
+  CK(cudaMemcpyAsync(h->d_best_val, &ninf, sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  CK(cudaMemcpyAsync(h->d_best_idx, &big, sizeof(long long), cudaMemcpyHostToDevice, h->stream));
+  return PLX_OK;
+}
+
+static int need_events(plx_bo* h, size_t count) {
+  while (h->ev_pool.size() < count) {
+    cudaEvent_t e;
+    CK(cudaEventCreate(&e));
+    h->ev_pool.push_back(e);
+  }
+  return PLX_OK;
+}
+
+static int check_sweep_args(plx_bo* h, const void* Xc, long long N, int acq, double* bv, long long* bi) {
+  if (!h) return PLX_ERR_INVALID;
+  if (N < 0 || (N > 0 && !Xc) || acq < 0 || acq > 2 || !bv || !bi) return fail(h, PLX_ERR_INVALID, "acq_sweep: bad arguments");
+  if (!h->have_state) return fail(h, PLX_ERR_STATE, "acq_sweep: no posterior state (call plx_gp_fit or plx_gp_set_theta)");
+  return PLX_OK;
+}
+
+extern "C" int plx_acq_sweep_dev(plx_bo_handle h, const double* Xc_dev, long long N, long long idx_base, int acq,
+                                 double kappa, double eps, double y_max, double* best_value,
+                                 long long* best_index, double* best_x) {
+  int r = check_sweep_args(h, Xc_dev, N, acq, best_value, best_index);
+  if (r != PLX_OK) return r;
+  CK(cudaSetDevice(h->device));
+  const long long l0 = h->launches;
+  if ((r = need_events(h, 2)) != PLX_OK) return r;
+  if ((r = reset_best(h)) != PLX_OK) return r;
+  SweepParams p;
+  fill_params(h, p, Xc_dev, N, idx_base, acq, kappa, eps, y_max);
+  if ((r = launch_sweep(h, p, h->ev_pool[0], h->ev_pool[1])) != PLX_OK) return r;
+  CK(cudaMemcpyAsync(best_value, h->d_best_val, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaMemcpyAsync(best_index, h->d_best_idx, sizeof(long long), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  float ms = 0.f;
+  if (N > 0) CK(cudaEventElapsedTime(&ms, h->ev_pool[0], h->ev_pool[1]));
+  h->last_ms = ms; h->last_launches = h->launches - l0;
+  if (N == 0) { *best_index = -1; *best_value = NAN; return PLX_OK; }
+  if (best_x) CK(cudaMemcpy(best_x, Xc_dev + (*best_index - idx_base) * h->d, sizeof(double) * h->d, cudaMemcpyDeviceToHost));
+  return PLX_OK;
+}
+
+extern "C" int plx_acq_sweep(plx_bo_handle h, const double* Xc, long long N, long long idx_base, int acq,
+                             double kappa, double eps, double y_max, double* best_value, long long* best_index,
+                             double* best_x, double* mean, double* sd, double* acq_values) {
+  int r = check_sweep_args(h, Xc, N, acq, best_value, best_index);
+  if (r != PLX_OK) return r;
+  CK(cudaSetDevice(h->device));
+  const long long l0 = h->launches;
+  if (N == 0) { *best_index = -1; *best_value = NAN; h->last_ms = 0; h->last_launches = 0; return PLX_OK; }
+  const int d = h->d;
+  // chunk: a whole number of waves of 128-candidate tiles, at most ~64 MiB of candidates
+  const long long wave = 128LL * h->num_sms;
+  long long k = (64LL << 20) / (8LL * d * wave);
+  if (k < 1) k = 1;
+  const long long chunk = std::min<long long>(wave * k, (N + 127) / 128 * 128);
+  const long long nchunks = (N + chunk - 1) / chunk;
+  if (h->cand_cap < static_cast<size_t>(chunk) * d) {
+    for (int b = 0; b < 2; ++b) { if (h->dcand[b]) CK(cudaFree(h->dcand[b])); h->dcand[b] = nullptr; }
+    h->cand_cap = 0;
+    for (int b = 0; b < 2; ++b) CK(cudaMalloc(&h->dcand[b], sizeof(double) * chunk * d));
+    h->cand_cap = static_cast<size_t>(chunk) * d;
+  }
+  const bool dump = mean || sd || acq_values;
+  if (dump && h->out_cap < static_cast<size_t>(chunk)) {
+    for (int b = 0; b < 3; ++b) { if (h->d_out[b]) CK(cudaFree(h->d_out[b])); h->d_out[b] = nullptr; }
+    h->out_cap = 0;
+    for (int b = 0; b < 3; ++b) CK(cudaMalloc(&h->d_out[b], sizeof(double) * chunk));
+    h->out_cap = static_cast<size_t>(chunk);
+  }
+  if ((r = need_events(h, static_cast<size_t>(2 * nchunks))) != PLX_OK) return r;
+  if ((r = reset_best(h)) != PLX_OK) return r;
+  for (long long c = 0; c < nchunks; ++c) {
+    const int b = static_cast<int>(c & 1);
+    const long long off = c * chunk, cn = std::min(chunk, N - off);
+    CK(cudaStreamWaitEvent(h->copy_stream, h->ev_done[b], 0));          // kernel that last read dcand[b]
+    CK(cudaMemcpyAsync(h->dcand[b], Xc + off * d, sizeof(double) * cn * d, cudaMemcpyHostToDevice, h->copy_stream));
+    CK(cudaEventRecord(h->ev_copy[b], h->copy_stream));
+    CK(cudaStreamWaitEvent(h->stream, h->ev_copy[b], 0));
+    SweepParams p;
+    fill_params(h, p, h->dcand[b], cn, idx_base + off, acq, kappa, eps, y_max);
+    if (dump) { p.out_mean = h->d_out[0]; p.out_std = h->d_out[1]; p.out_acq = h->d_out[2]; }
+    if ((r = launch_sweep(h, p, h->ev_pool[2 * c], h->ev_pool[2 * c + 1])) != PLX_OK) return r;
+    CK(cudaEventRecord(h->ev_done[b], h->stream));
+    if (dump) {
+      if (mean) CK(cudaMemcpyAsync(mean + off, h->d_out[0], sizeof(double) * cn, cudaMemcpyDeviceToHost, h->stream));
+      if (sd) CK(cudaMemcpyAsync(sd + off, h->d_out[1], sizeof(double) * cn, cudaMemcpyDeviceToHost, h->stream));
+      if (acq_values) CK(cudaMemcpyAsync(acq_values + off, h->d_out[2], sizeof(double) * cn, cudaMemcpyDeviceToHost, h->stream));
+    }
+  }
+  CK(cudaMemcpyAsync(best_value, h->d_best_val, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaMemcpyAsync(best_index, h->d_best_idx, sizeof(long long), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  double total = 0.0;
+  for (long long c = 0; c < nchunks; ++c) {
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, h->ev_pool[2 * c], h->ev_pool[2 * c + 1]));
+    total += ms;
+  }
+  h->last_ms = total; h->last_launches = h->launches - l0;
+  if (best_x) std::memcpy(best_x, Xc + (*best_index - idx_base) * d, sizeof(double) * d);
+  return PLX_OK;
+}
+
+extern "C" int plx_last_sweep_stats(plx_bo_handle h, double* kernel_ms, long long* launches) {
+  if (!h) return PLX_ERR_INVALID;
+  if (kernel_ms) *kernel_ms = h->last_ms;
+  if (launches) *launches = h->last_launches;
+  return PLX_OK;
+}
+
+extern "C" int plx_lbfgsb1d_minimize(plx_fg_callback fg, void* user, double x0, double lo, double hi, double* x,
+                                     double* f, int* n_evals, int* n_iters, int* status) {
+  if (!fg || !(lo < hi)) return PLX_ERR_INVALID;
+  Lbfgsb1D m;
+  m.lo = lo; m.hi = hi;
+  m.start(x0);
+  while (!m.done) {
+    double fv = 0.0, gv = 0.0;
+    fg(m.x_eval, &fv, &gv, user);
+    m.feed(fv, gv);
+  }
+  if (x) *x = m.x;
+  if (f) *f = m.f;
+  if (n_evals) *n_evals = m.nfev;
+  if (n_iters) *n_iters = m.iter;
+  if (status) *status = m.status;
+  return PLX_OK;
+}

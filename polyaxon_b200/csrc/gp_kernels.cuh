@@ -1,0 +1,395 @@
+// Gaussian-process state kernels: kernel-matrix build, blocked FP64 Cholesky, triangular inverse,
+// alpha = K^-1 y, explicit K^-1 for the marginal-likelihood gradient.  All batched over the
+// length-scale restarts (grid.y / grid.z = batch index), all float64.
+//
+// Reference arithmetic being replaced (third-party, reached from optimizer.py:21):
+//   sklearn _gpr.py:583-654  log_marginal_likelihood(theta, eval_gradient=True)
+//   sklearn _gpr.py:349-367  L = cholesky(K + alpha I), alpha_ = cho_solve(L, y)
+//   sklearn kernels.py:1558-1587 (RBF), :1713-1786 (Matern nu = 0.5 / 1.5 / 2.5)
+//
+// HBM layout per batch member b (npad = n rounded up to 128, leading dimension ld = npad):
+//   A[b]  npad x ld  K + jitter*I (symmetric, identity in the padding); trailing updates in place;
+//                    reused for K^-1 once the factor exists
+//   L[b]  npad x ld  lower Cholesky factor (row-major)
+//   U[b]  npad x ld  U = L^-T, upper triangular (row-major), i.e. U[c][r] = (L^-1)[r][c]
+//   W[b]  nb x 128 x 128  inverses of the diagonal blocks of L (lower)
+//   T[b]  nb x 128 x 128  scratch for the triangular-inverse recurrence
+#pragma once
+#include "mma_f64.cuh"
+#include <math.h>
+
+namespace plx {
+
+enum KernelKind { K_RBF = 0, K_M05 = 1, K_M15 = 2, K_M25 = 3 };
+
+__device__ __forceinline__ double kern_value(int kind, double r2) {
+  if (kind == K_RBF) return exp(-0.5 * r2);
+  const double r = sqrt(r2);
+  if (kind == K_M05) return exp(-r);
+  if (kind == K_M15) { const double t = r * 1.7320508075688772; return (1.0 + t) * exp(-t); }
+  const double t = r * 2.23606797749979;
+  return (1.0 + t + t * t / 3.0) * exp(-t);
+}
+
+// dK/dtheta for theta = log(length_scale) as sklearn forms it (kernels.py:1575, :1752-1773)
+__device__ __forceinline__ double kern_dtheta(int kind, double r2) {
+  if (kind == K_RBF) return exp(-0.5 * r2) * r2;
+  const double r = sqrt(r2);
+  const double d2 = r * r;                       // sklearn squares the rooted distance again
+  if (kind == K_M05) return (r != 0.0) ? exp(-r) * d2 / r : 0.0;
+  if (kind == K_M15) return 3.0 * d2 * exp(-sqrt(3.0 * d2));
+  const double t = sqrt(5.0 * d2);
+  return 5.0 / 3.0 * d2 * (t + 1.0) * exp(-t);
+}
+
+struct BatchPtrs {
+  double* A; double* L; double* U; double* W; double* T;
+  size_t mat_stride;     // npad * ld
+  size_t blk_stride;     // nb * 128 * 128
+};
+
+// ---------------------------------------------------------------------------------------------
+// K(X, X) + jitter*I for every theta of the batch.  32x32 output tile per CTA, X rows staged in
+// shared memory in dimension chunks of 32.  HBM-bound: writes npad^2 doubles per batch member.
+// mode 0: write K into A (padding = identity).
+// mode 1: gradient reduction  sum_{a,b<n} (alpha_a alpha_b - Kinv[a][b]) * dK/dtheta[a][b]
+//         over the lower 32-tiles (off-diagonal tiles weighted 2), one partial per CTA.
+// ---------------------------------------------------------------------------------------------
+constexpr int DCH = 32;
+
+template <int MODE>
+__global__ void __launch_bounds__(256) kmat_kernel(const double* __restrict__ X, int n, int d, int npad,
+                                                   const double* __restrict__ thetas, int kind, double jitter,
+                                                   BatchPtrs bp, const double* __restrict__ alpha,
+                                                   double* __restrict__ partial, int ntri) {
+  __shared__ double Xi[32][DCH + 1];
+  __shared__ double Xj[32][DCH + 1];
+  __shared__ double red[8];
+  const int b = blockIdx.z;
+  int ti, tj;
+  if (MODE == 0) { ti = blockIdx.y; tj = blockIdx.x; }
+  else {
+    // linear index over the lower triangle of 32-tiles: p = ti*(ti+1)/2 + tj
+    const int p = blockIdx.x;
+    ti = static_cast<int>((sqrt(8.0 * p + 1.0) - 1.0) * 0.5);
+    while ((ti + 1) * (ti + 2) / 2 <= p) ++ti;
+    while (ti * (ti + 1) / 2 > p) --ti;
+    tj = p - ti * (ti + 1) / 2;
+  }
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const double ell = exp(thetas[b]);
+  const int i0 = ti * 32, j0 = tj * 32;
+  double r2[4] = {0.0, 0.0, 0.0, 0.0};
+  for (int dc = 0; dc < d; dc += DCH) {
+    const int dn = min(DCH, d - dc);
+    __syncthreads();
+    for (int e = threadIdx.x; e < 32 * DCH; e += 256) {
+      const int row = e / DCH, col = e % DCH;
+      double vi = 0.0, vj = 0.0;
+      if (col < dn) {
+        if (i0 + row < n) vi = X[static_cast<size_t>(i0 + row) * d + dc + col] / ell;
+        if (j0 + row < n) vj = X[static_cast<size_t>(j0 + row) * d + dc + col] / ell;
+      }
+      Xi[row][col] = vi; Xj[row][col] = vj;
+    }
+    __syncthreads();
+    for (int q = 0; q < dn; ++q) {
+      const double xj = Xj[tx][q];
+#pragma unroll
+      for (int r = 0; r < 4; ++r) { const double df = Xi[ty + 8 * r][q] - xj; r2[r] += df * df; }
+    }
+  }
+  const size_t ld = npad;
+  if (MODE == 0) {
+    double* A = bp.A + b * bp.mat_stride;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int i = i0 + ty + 8 * r, j = j0 + tx;
+      double v;
+      if (i < n && j < n) v = (i == j) ? 1.0 + jitter : kern_value(kind, r2[r]);
+      else v = (i == j) ? 1.0 : 0.0;
+      A[i * ld + j] = v;
+    }
+  } else {
+    const double* Kinv = bp.A + b * bp.mat_stride;
+    const double* al = alpha + static_cast<size_t>(b) * npad;
+    double s = 0.0;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int i = i0 + ty + 8 * r, j = j0 + tx;
+      if (i < n && j < n) {
+        const double g = (i == j) ? 0.0 : kern_dtheta(kind, r2[r]);
+        s += (al[i] * al[j] - Kinv[i * ld + j]) * g;
+      }
+    }
+    if (ti != tj) s *= 2.0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (tx == 0) red[ty] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double t = 0.0;
+      for (int w = 0; w < 8; ++w) t += red[w];
+      partial[static_cast<size_t>(b) * ntri + blockIdx.x] = t;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Diagonal block k: unblocked Cholesky of the 128x128 block in shared memory, then its inverse by
+// column-parallel forward substitution.  Writes L_kk, W_k = L_kk^-1, U_kk = W_k^T, adds the
+// block's sum(log diag) to logdet[b] and records the first non-positive pivot in info[b].
+// One CTA per batch member; latency-bound (128 dependent column steps).
+// ---------------------------------------------------------------------------------------------
+constexpr int POTF_LD = 129;
+constexpr int POTF_SMEM = (128 * POTF_LD + 256) * 8;
+
+__global__ void __launch_bounds__(256) potf2_inv_kernel(BatchPtrs bp, int k, int n, int npad,
+                                                        double* __restrict__ logdet, int* __restrict__ info) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double* S = reinterpret_cast<double*>(smem_raw);        // S[i][j] at S[i*129 + j]
+  double* dl = S + 128 * POTF_LD;                         // diagonal of L
+  double* wdiag = dl + 128;                               // diagonal of W
+  const int b = blockIdx.x, tid = threadIdx.x;
+  const size_t ld = npad;
+  const double* A = bp.A + b * bp.mat_stride + (static_cast<size_t>(k) * 128) * ld + k * 128;
+  for (int e = tid; e < 128 * 128; e += 256) {
+    const int i = e >> 7, j = e & 127;
+    S[i * POTF_LD + j] = A[i * ld + j];
+  }
+  __shared__ int bad;
+  if (tid == 0) bad = 0;
+  for (int j = 0; j < 128; ++j) {
+    __syncthreads();                    // trailing update of column j-1 is complete
+    double ajj = S[j * POTF_LD + j];    // stays untouched during this step (dl holds the root)
+    if (!(ajj > 0.0)) {                 // non-positive or NaN pivot: not positive definite
+      if (tid == 0 && bad == 0) bad = k * 128 + j + 1;
+      ajj = 1.0;
+    }
+    const double ljj = sqrt(ajj);
+    if (tid == 0) dl[j] = ljj;
+    for (int i = j + 1 + tid; i < 128; i += 256) S[i * POTF_LD + j] /= ljj;
+    __syncthreads();
+    // trailing update of the lower triangle: S[i][c] -= S[i][j] * S[c][j], j < c <= i
+    for (int i = j + 1 + (tid >> 4); i < 128; i += 16) {
+      const double lij = S[i * POTF_LD + j];
+      for (int c = j + 1 + (tid & 15); c <= i; c += 16) S[i * POTF_LD + c] -= lij * S[c * POTF_LD + j];
+    }
+  }
+  __syncthreads();
+  if (tid < 128) S[tid * POTF_LD + tid] = dl[tid];
+  __syncthreads();
+  // inverse: thread c owns column c of W; W[i][c] (i > c) kept in the strict upper triangle S[c][i]
+  if (tid < 128) {
+    const int c = tid;
+    const double wcc = 1.0 / S[c * POTF_LD + c];
+    wdiag[c] = wcc;
+    for (int i = c + 1; i < 128; ++i) {
+      double s = S[i * POTF_LD + c] * wcc;
+      for (int m = c + 1; m < i; ++m) s += S[i * POTF_LD + m] * S[c * POTF_LD + m];
+      S[c * POTF_LD + i] = -s / S[i * POTF_LD + i];
+    }
+  }
+  __syncthreads();
+  double* Lo = bp.L + b * bp.mat_stride + (static_cast<size_t>(k) * 128) * ld + k * 128;
+  double* Uo = bp.U + b * bp.mat_stride + (static_cast<size_t>(k) * 128) * ld + k * 128;
+  double* Wo = bp.W + b * bp.blk_stride + static_cast<size_t>(k) * 128 * 128;
+  for (int e = tid; e < 128 * 128; e += 256) {
+    const int i = e >> 7, j = e & 127;
+    double l, w;
+    if (i > j) { l = S[i * POTF_LD + j]; w = S[j * POTF_LD + i]; }
+    else if (i == j) { l = S[i * POTF_LD + i]; w = wdiag[i]; }
+    else { l = 0.0; w = 0.0; }
+    Lo[i * ld + j] = l;
+    Wo[i * 128 + j] = w;
+    // U_kk = W^T: element (i, j) of U is W[j][i]
+    double u;
+    if (j > i) u = S[i * POTF_LD + j]; else if (i == j) u = wdiag[i]; else u = 0.0;
+    Uo[i * ld + j] = u;
+  }
+  if (tid < 32) {
+    double s = 0.0;
+    for (int i = tid; i < 128; i += 32)
+      if (k * 128 + i < n) s += log(S[i * POTF_LD + i]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (tid == 0) {
+      logdet[b] += s;
+      if (bad != 0 && info[b] == 0) info[b] = bad;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// 128x128-tile DMMA kernels of the blocked algorithms.  Each CTA: one output tile, 256 threads.
+// ---------------------------------------------------------------------------------------------
+constexpr int GEMM_SMEM = 4 * TILE_BYTES + 1024;
+
+__device__ __forceinline__ unsigned char* align1k(unsigned char* p) {
+  return reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(p) + 1023) & ~static_cast<uintptr_t>(1023));
+}
+
+template <bool NEG, bool SUB>
+__device__ __forceinline__ void store_tile(const WarpAcc& acc, double* C, size_t ldc) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int mf = 0; mf < 4; ++mf)
+#pragma unroll
+    for (int nf = 0; nf < 8; ++nf) {
+      double2* p = reinterpret_cast<double2*>(C + static_cast<size_t>(acc_row(warp, lane, mf)) * ldc +
+                                              acc_col(warp, lane, nf, 0));
+      double2 v = make_double2(acc.c[mf][nf][0], acc.c[mf][nf][1]);
+      if (NEG) { v.x = -v.x; v.y = -v.y; }
+      if (SUB) { const double2 o = *p; v.x = o.x - v.x; v.y = o.y - v.y; }
+      *p = v;
+    }
+}
+
+// panel: L[i][k] = A[i][k] * W_k^T for i = k+1+blockIdx.x
+__global__ void __launch_bounds__(256, 1) chol_panel_kernel(BatchPtrs bp, int k, int npad) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = align1k(smem_raw);
+  const int b = blockIdx.y, i = k + 1 + blockIdx.x;
+  const size_t ld = npad;
+  const double* A = bp.A + b * bp.mat_stride + (static_cast<size_t>(i) * 128) * ld + k * 128;
+  const double* W = bp.W + b * bp.blk_stride + static_cast<size_t>(k) * 128 * 128;
+  WarpAcc acc; acc.zero();
+  mainloop_nt(acc, A, ld, W, 128, 0, 128, smem);
+  store_tile<false, false>(acc, bp.L + b * bp.mat_stride + (static_cast<size_t>(i) * 128) * ld + k * 128, ld);
+}
+
+__device__ __forceinline__ void tri_index(int p, int& ti, int& tj) {
+  ti = static_cast<int>((sqrt(8.0 * p + 1.0) - 1.0) * 0.5);
+  while ((ti + 1) * (ti + 2) / 2 <= p) ++ti;
+  while (ti * (ti + 1) / 2 > p) --ti;
+  tj = p - ti * (ti + 1) / 2;
+}
+
+// trailing update: A[i][j] -= L[i][k] * L[j][k]^T over the lower tiles of the trailing matrix
+__global__ void __launch_bounds__(256, 1) chol_syrk_kernel(BatchPtrs bp, int k, int npad) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = align1k(smem_raw);
+  const int b = blockIdx.y;
+  int ti, tj; tri_index(blockIdx.x, ti, tj);
+  const int i = k + 1 + ti, j = k + 1 + tj;
+  const size_t ld = npad;
+  const double* Li = bp.L + b * bp.mat_stride + (static_cast<size_t>(i) * 128) * ld + k * 128;
+  const double* Lj = bp.L + b * bp.mat_stride + (static_cast<size_t>(j) * 128) * ld + k * 128;
+  WarpAcc acc; acc.zero();
+  mainloop_nt(acc, Li, ld, Lj, ld, 0, 128, smem);
+  store_tile<false, true>(acc, bp.A + b * bp.mat_stride + (static_cast<size_t>(i) * 128) * ld + j * 128, ld);
+}
+
+// triangular inverse, step j, part 1: T[k] = sum_{m in [k*128, j*128)} U[k-rows][m] * L[j-rows][m]
+__global__ void __launch_bounds__(256, 1) trtri_t_kernel(BatchPtrs bp, int j, int npad) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = align1k(smem_raw);
+  const int b = blockIdx.y, k = blockIdx.x;
+  const size_t ld = npad;
+  const double* Uk = bp.U + b * bp.mat_stride + (static_cast<size_t>(k) * 128) * ld;
+  const double* Lj = bp.L + b * bp.mat_stride + (static_cast<size_t>(j) * 128) * ld;
+  WarpAcc acc; acc.zero();
+  mainloop_nt(acc, Uk, ld, Lj, ld, k * 128, j * 128, smem);
+  store_tile<false, false>(acc, bp.T + b * bp.blk_stride + static_cast<size_t>(k) * 128 * 128, 128);
+}
+
+// part 2: U[k][j] = -T[k] * W_j^T
+__global__ void __launch_bounds__(256, 1) trtri_u_kernel(BatchPtrs bp, int j, int npad) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = align1k(smem_raw);
+  const int b = blockIdx.y, k = blockIdx.x;
+  const size_t ld = npad;
+  const double* Tk = bp.T + b * bp.blk_stride + static_cast<size_t>(k) * 128 * 128;
+  const double* Wj = bp.W + b * bp.blk_stride + static_cast<size_t>(j) * 128 * 128;
+  WarpAcc acc; acc.zero();
+  mainloop_nt(acc, Tk, 128, Wj, 128, 0, 128, smem);
+  store_tile<true, false>(acc, bp.U + b * bp.mat_stride + (static_cast<size_t>(k) * 128) * ld + j * 128, ld);
+}
+
+// K^-1 = U U^T on the lower 128-tiles (diagonal tiles in full), written over A.
+__global__ void __launch_bounds__(256, 1) kinv_kernel(BatchPtrs bp, int npad) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = align1k(smem_raw);
+  const int b = blockIdx.y;
+  int ta, tb; tri_index(blockIdx.x, ta, tb);
+  const size_t ld = npad;
+  const double* Ua = bp.U + b * bp.mat_stride + (static_cast<size_t>(ta) * 128) * ld;
+  const double* Ub = bp.U + b * bp.mat_stride + (static_cast<size_t>(tb) * 128) * ld;
+  WarpAcc acc; acc.zero();
+  mainloop_nt(acc, Ua, ld, Ub, ld, ta * 128, npad, smem);
+  store_tile<false, false>(acc, bp.A + b * bp.mat_stride + (static_cast<size_t>(ta) * 128) * ld + tb * 128, ld);
+}
+
+// w[m] = sum_{a <= m} U[a][m] y[a]   (w = L^-1 y).  block (32, 8): 32 columns per CTA.
+__global__ void __launch_bounds__(256) uty_kernel(BatchPtrs bp, const double* __restrict__ y, int npad,
+                                                  double* __restrict__ w) {
+  __shared__ double red[8][33];
+  const int b = blockIdx.y, tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int m = blockIdx.x * 32 + tx;
+  const double* U = bp.U + b * bp.mat_stride;
+  double s = 0.0;
+  for (int a = ty; a <= m; a += 8) s += U[static_cast<size_t>(a) * npad + m] * y[a];
+  red[ty][tx] = s;
+  __syncthreads();
+  if (ty == 0) {
+    double t = 0.0;
+    for (int r = 0; r < 8; ++r) t += red[r][tx];
+    w[static_cast<size_t>(b) * npad + m] = t;
+  }
+}
+
+// alpha[a] = sum_{m >= a} U[a][m] w[m]   (alpha = L^-T w).  One warp per row.
+__global__ void __launch_bounds__(256) uw_kernel(BatchPtrs bp, const double* __restrict__ w, int npad,
+                                                 double* __restrict__ alpha) {
+  const int b = blockIdx.y, lane = threadIdx.x & 31;
+  const int a = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const double* U = bp.U + b * bp.mat_stride + static_cast<size_t>(a) * npad;
+  const double* wb = w + static_cast<size_t>(b) * npad;
+  double s = 0.0;
+  for (int m = (a & ~31) + lane; m < npad; m += 32)
+    if (m >= a) s += U[m] * wb[m];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) alpha[static_cast<size_t>(b) * npad + a] = s;
+}
+
+// lml[b] = -1/2 y^T alpha - logdet - n/2 log(2 pi);  grad[b] = 1/2 * sum(partials)
+__global__ void lml_finalize_kernel(const double* __restrict__ y, const double* __restrict__ alpha,
+                                    const double* __restrict__ logdet, const int* __restrict__ info,
+                                    const double* __restrict__ partial, int ntri, int n, int npad,
+                                    double* __restrict__ lml, double* __restrict__ grad) {
+  __shared__ double red[2][8];
+  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double ya = 0.0, gs = 0.0;
+  for (int i = tid; i < n; i += 256) ya += y[i] * alpha[static_cast<size_t>(b) * npad + i];
+  if (partial != nullptr)
+    for (int i = tid; i < ntri; i += 256) gs += partial[static_cast<size_t>(b) * ntri + i];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    ya += __shfl_xor_sync(0xffffffffu, ya, o);
+    gs += __shfl_xor_sync(0xffffffffu, gs, o);
+  }
+  if (lane == 0) { red[0][warp] = ya; red[1][warp] = gs; }
+  __syncthreads();
+  if (tid == 0) {
+    double a = 0.0, g = 0.0;
+    for (int w = 0; w < 8; ++w) { a += red[0][w]; g += red[1][w]; }
+    if (info[b] != 0) { lml[b] = -INFINITY; if (grad) grad[b] = 0.0; }
+    else {
+      lml[b] = -0.5 * a - logdet[b] - 0.5 * n * 1.8378770664093453;   // log(2 pi)
+      if (grad) grad[b] = 0.5 * g;
+    }
+  }
+}
+
+// Z = U^T (row-major L^-1) for the sweep; 32x32 tiles through shared memory.
+__global__ void __launch_bounds__(256) transpose_kernel(const double* __restrict__ U, double* __restrict__ Z, int npad) {
+  __shared__ double tile[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int bi = blockIdx.y * 32, bj = blockIdx.x * 32;
+  for (int r = ty; r < 32; r += 8) tile[r][tx] = U[static_cast<size_t>(bi + r) * npad + bj + tx];
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8) Z[static_cast<size_t>(bj + r) * npad + bi + tx] = tile[tx][r];
+}
+
+}  // namespace plx
