@@ -1,0 +1,156 @@
+"""``UtilityFunction``: Gaussian-process surrogate + UCB / EI / POI acquisition, on the GPU.
+
+Same constructor, attributes and methods as the reference class
+(``.../bayesian_optimization/acquisition_function.py:17-115``); the arithmetic the reference hands
+to scikit-learn / scipy runs in the CUDA library behind ``polyaxon_b200._lib``:
+
+  reference                                              here
+  -----------------------------------------------------  ------------------------------------------
+  GaussianProcessRegressor(kernel, n_restarts, rng)      DeviceGaussianProcess (same attribute names)
+  gp.fit(X, y)                    optimizer.py:21        plx_gp_set_data + plx_gp_fit
+  gp.predict(x, return_std=True)  :49,53,58              plx_acq_sweep (mean / std dumps)
+  compute(x, y_max)               :62-68                 plx_acq_sweep (acquisition dump)
+  max_compute warm-up             :88-92                 plx_acq_sweep (arg-max on device)
+  max_compute L-BFGS-B loop       :95-111                plx_acq_refine (all seeds batched)
+
+Random numbers are drawn on the host from the reference's own ``RandomState`` in the reference's
+order (restart thetas during fit -> x_tries -> x_seeds), so a seeded group sees bit-identical
+candidate matrices.
+"""
+import numpy as np
+
+from polyaxon_b200 import _lib, device
+from polyaxon_b200.hpsearch.search_managers.utils import get_random_generator
+from polyaxon_b200.schemas.hptuning import (
+    AcquisitionFunctions,
+    GaussianProcessConfig,
+    GaussianProcessesKernels,
+    UtilityFunctionConfig,
+)
+
+THETA_BOUNDS = (float(np.log(1e-5)), float(np.log(1e5)))      # sklearn's default length_scale_bounds
+
+
+def _acq_id(name):
+    if AcquisitionFunctions.is_ucb(name):
+        return _lib.ACQ_UCB
+    if AcquisitionFunctions.is_ei(name):
+        return _lib.ACQ_EI
+    if AcquisitionFunctions.is_poi(name):
+        return _lib.ACQ_POI
+    return None
+
+
+class DeviceGaussianProcess(object):
+    """The slice of ``sklearn.gaussian_process.GaussianProcessRegressor`` the reference touches:
+    ``fit`` / ``predict`` plus the fitted attributes ``theta_``, ``length_scale_``,
+    ``log_marginal_likelihood_value_``, ``L_``, ``alpha_``.  alpha (jitter) is sklearn's default
+    1e-10 and y is not normalised, as in the reference (acquisition_function.py:42-46)."""
+
+    alpha = 1e-10
+
+    def __init__(self, kernel, length_scale, nu, n_restarts_optimizer, random_state, handle=None):
+        self.kernel_id = _lib.KERNEL_RBF if GaussianProcessesKernels.is_rbf(kernel) else _lib.KERNEL_MATERN
+        self.length_scale = float(length_scale)
+        self.nu = float(nu) if nu is not None else 1.5
+        self.n_restarts_optimizer = int(n_restarts_optimizer or 0)
+        self.random_state = random_state
+        self._handle = handle
+        self.fitted = False
+
+    @property
+    def handle(self):
+        if self._handle is None:
+            self._handle = device.get_handle()
+        return self._handle
+
+    def fit(self, X, y):
+        X = np.asarray(X, dtype=np.float64)
+        y = np.asarray(y, dtype=np.float64)
+        if X.ndim != 2 or X.shape[0] != y.shape[0]:
+            raise ValueError('Found input variables with inconsistent numbers of samples: '
+                             '{} and {}'.format(X.shape, y.shape))
+        self.handle.set_data(X, y, self.kernel_id, self.nu, self.alpha)
+        # sklearn draws one theta per restart from the shared generator, before any candidate
+        # (sklearn _gpr.py:329-333); same calls here so the stream stays aligned
+        lo, hi = np.array([THETA_BOUNDS[0]]), np.array([THETA_BOUNDS[1]])
+        restarts = [float(self.random_state.uniform(lo, hi)[0]) for _ in range(self.n_restarts_optimizer)]
+        theta, lml, per_run = self.handle.fit(np.log(self.length_scale), restarts, THETA_BOUNDS)
+        self.theta_ = theta
+        self.length_scale_ = float(np.exp(theta))
+        self.log_marginal_likelihood_value_ = lml
+        self.optimizer_runs_ = per_run
+        self.X_train_, self.y_train_ = X, y
+        self.fitted = True
+        return self
+
+    @property
+    def L_(self):
+        return self.handle.get_state(want_L=True)[0]
+
+    @property
+    def alpha_(self):
+        return self.handle.get_state(want_L=False)[1]
+
+    def predict(self, X, return_std=False):
+        if not self.fitted:
+            raise RuntimeError('DeviceGaussianProcess.predict called before fit')
+        X = np.atleast_2d(np.asarray(X, dtype=np.float64))
+        _, _, _, mean, std, _ = self.handle.sweep(X, _lib.ACQ_UCB, 0.0, kappa=0.0, dump=True)
+        return (mean, std) if return_std else mean
+
+
+class UtilityFunction(object):
+    def __init__(self, config, seed=None):
+        if not isinstance(config, UtilityFunctionConfig):
+            raise ValueError('Received a non valid configuration.')
+        self.config = config
+        self.eps = config.eps
+        self.kappa = config.kappa
+        self.acquisition_function = config.acquisition_function
+        self.random_generator = get_random_generator(seed=seed)
+        self.gaussian_process = self.get_gaussian_process(config=config.gaussian_process,
+                                                          random_generator=self.random_generator)
+
+    @staticmethod
+    def get_gaussian_process(config, random_generator):
+        if not isinstance(config, GaussianProcessConfig):
+            raise ValueError('Received a non valid configuration.')
+        return DeviceGaussianProcess(kernel=config.kernel, length_scale=config.length_scale,
+                                     nu=config.nu, n_restarts_optimizer=config.n_restarts_optimizer,
+                                     random_state=random_generator)
+
+    def _acq_args(self, y_max):
+        acq = _acq_id(self.acquisition_function)
+        return acq, dict(y_max=float(y_max if y_max is not None else 0.0),
+                         kappa=float(self.kappa or 0.0), eps=float(self.eps or 0.0))
+
+    def compute(self, x, y_max):
+        """Acquisition values of the rows of x (acquisition_function.py:62-68)."""
+        acq, args = self._acq_args(y_max)
+        if acq is None:
+            return None
+        x = np.atleast_2d(np.asarray(x, dtype=np.float64))
+        return self.gaussian_process.handle.sweep(x, acq, dump=True, **args)[5]
+
+    def max_compute(self, y_max, bounds, n_warmup=100000, n_iter=250):
+        """arg max of the acquisition function (acquisition_function.py:70-115): `n_warmup` random
+        candidates swept on the device, then `n_iter` bounded quasi-Newton refinements, batched."""
+        acq, args = self._acq_args(y_max)
+        bounds = np.asarray(bounds, dtype=np.float64)
+        h = self.gaussian_process.handle
+        x_tries = self.random_generator.uniform(bounds[:, 0], bounds[:, 1],
+                                                size=(n_warmup, bounds.shape[0]))
+        max_acq, _, x_max = h.sweep(x_tries, acq, **args)
+        x_seeds = self.random_generator.uniform(bounds[:, 0], bounds[:, 1],
+                                                size=(n_iter, bounds.shape[0]))
+        if n_iter > 0:
+            xs, values, success = h.refine(x_seeds, bounds, acq, **args)
+            for x_ref, value, ok in zip(xs, values, success):
+                if not ok:
+                    continue
+                # `>=`: among equal values the later seed wins (acquisition_function.py:109)
+                if max_acq is None or value >= max_acq:
+                    x_max, max_acq = x_ref, value
+        self.last_max_acq_ = max_acq
+        return np.clip(x_max, bounds[:, 0], bounds[:, 1])
