@@ -98,6 +98,24 @@ int plx_last_sweep_stats(plx_bo_handle h, double* kernel_ms, long long* launches
 /* Total number of kernels this handle has launched since creation. */
 long long plx_launch_count(plx_bo_handle h);
 
+/* Warm-up sweep that allocates nothing.  No counterpart in the reference: it exists for host
+ * applications that own the GPU memory budget themselves (all memory handed to their own pool, or a
+ * fixed MPS / container limit) and so cannot let a library call cudaMalloc, and for latency-critical
+ * sections where an allocation is not acceptable.  Every input and output is a DEVICE pointer of the
+ * caller: candidates Xc (N x d), observations X (n x d), alpha (n), Linv (n x n lower triangular,
+ * leading dimension ldz >= n) -- the last two as plx_gp_get_state returns them -- and the two
+ * result cells.  Scratch comes from a static device array (about 8.9 MB per GPU, held until the
+ * process exits), which limits it to n <= 256 observations; larger n is refused with
+ * PLX_ERR_INVALID.  The first call on a device does a one-time set-up and should come before any
+ * stream capture.  All calls share that array: calls that overlap on the GPU race, serialise them.
+ * The work is queued on `stream` (a cudaStream_t as void*, NULL = default stream) and the function
+ * returns without synchronising; with N == 0 the result cells hold (-inf, INT64_MAX).
+ * Errors: plx_last_error(NULL). */
+int plx_acq_sweep_noalloc(int device, void* stream, const double* Xc_dev, long long N, long long idx_base,
+                          const double* X_dev, const double* alpha_dev, const double* Linv_dev, int ldz, int n,
+                          int d, int kernel, double nu, double theta, int acq, double kappa, double eps,
+                          double y_max, double* best_value_dev, long long* best_index_dev);
+
 /* Host-only: the one-variable L-BFGS-B used by plx_gp_fit, driven by a callback (for testing against
  * scipy.optimize.minimize(method="L-BFGS-B", jac=True), sklearn _gpr.py:660-666). */
 typedef void (*plx_fg_callback)(double x, double* f, double* g, void* user);

@@ -38,6 +38,9 @@ SIGNATURES = {
                                   c_double, _dp, POINTER(c_longlong), c_void_p]),
     'plx_last_sweep_stats': (c_int, [c_void_p, _dp, POINTER(c_longlong)]),
     'plx_launch_count': (c_longlong, [c_void_p]),
+    'plx_acq_sweep_noalloc': (c_int, [c_int, c_void_p, c_void_p, c_longlong, c_longlong, c_void_p, c_void_p,
+                                      c_void_p, c_int, c_int, c_int, c_int, c_double, c_double, c_int,
+                                      c_double, c_double, c_double, c_void_p, c_void_p]),
     'plx_lbfgsb1d_minimize': (c_int, [FG_CALLBACK, c_void_p, c_double, c_double, c_double, _dp, _dp,
                                       POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
 }
@@ -198,3 +201,16 @@ def lbfgsb1d_minimize(fun, x0, lo, hi):
     if rc != PLX_OK:
         raise PlxError(rc, 'lbfgsb1d_minimize: invalid arguments')
     return x.value, f.value, ne.value, ni.value, st.value
+
+
+def sweep_noalloc(device, stream, xc_ptr, N, x_ptr, alpha_ptr, linv_ptr, ldz, n, d, kernel, nu, theta, acq, y_max,
+                  best_value_ptr, best_index_ptr, kappa=0.0, eps=0.0, idx_base=0):
+    """plx_acq_sweep_noalloc: every pointer is a raw device address owned by the caller; nothing is
+    allocated and nothing is synchronised (results land in the two device cells on `stream`)."""
+    lib = load()
+    rc = lib.plx_acq_sweep_noalloc(int(device), c_void_p(stream or 0), c_void_p(xc_ptr), int(N), int(idx_base),
+                                   c_void_p(x_ptr), c_void_p(alpha_ptr), c_void_p(linv_ptr), int(ldz), int(n),
+                                   int(d), int(kernel), float(nu), float(theta), int(acq), float(kappa),
+                                   float(eps), float(y_max), c_void_p(best_value_ptr), c_void_p(best_index_ptr))
+    if rc != PLX_OK:
+        raise PlxError(rc, lib.plx_last_error(None).decode())

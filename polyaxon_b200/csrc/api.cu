@@ -558,3 +558,104 @@ extern "C" int plx_lbfgsb1d_minimize(plx_fg_callback fg, void* user, double x0, 
   if (status) *status = m.status;
   return PLX_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// plx_acq_sweep_noalloc: the warm-up sweep for callers that must not allocate device memory.
+//
+// Who needs it: a host application that owns the whole GPU memory budget itself -- a serving or
+// training process that has handed every byte to its own pool, or one running under a fixed
+// MPS / cgroup memory limit -- and therefore forbids cudaMalloc inside library calls, and code in
+// a latency-critical section where an allocation (a device-wide synchronising call) is not
+// acceptable.  Such a caller passes every input and output as device pointers it already owns;
+// the only thing the sweep still needs is scratch (the K* slabs, a zero-padded copy of L^-1 and
+// the per-CTA bests).  That scratch lives in the file-scope array below: about 8.9 MB that every
+// GPU which loads this library holds until the process exits.
+//
+// Limits: n_obs <= 256 (PLX_NOALLOC_MAX_OBS); any d, any number of candidates.  Larger problems
+// are refused with PLX_ERR_INVALID; use the handle API for them.
+//
+// One-time set-up happens inside the FIRST call on each device (symbol address look-up, the
+// shared-memory attribute of the kernel, and the driver's lazy loading of the kernels), so make
+// that first call before any stream capture.  Later calls issue three kernel launches and nothing
+// else.  All calls share the one array and it keeps the previous call's contents; every region a
+// call reads is rewritten by that call first, but two calls that overlap on the GPU (different
+// streams, or different host threads) race on it -- serialise them.
+// ---------------------------------------------------------------------------------------------
+namespace {
+constexpr int NOALLOC_MAX_OBS = 256;
+constexpr int NOALLOC_GRID = 32;                                   // CTAs (one 128 x npad slab each)
+constexpr size_t NOALLOC_Z = static_cast<size_t>(NOALLOC_MAX_OBS) * NOALLOC_MAX_OBS;
+constexpr size_t NOALLOC_KS = static_cast<size_t>(NOALLOC_GRID) * 128 * NOALLOC_MAX_OBS;
+constexpr size_t NOALLOC_DOUBLES = NOALLOC_Z + NOALLOC_KS + 2 * NOALLOC_GRID;
+constexpr int NOALLOC_MAX_DEVICES = 64;
+}  // namespace
+
+static __device__ __align__(256) double g_noalloc_scratch[NOALLOC_DOUBLES];
+
+// In host code the name g_noalloc_scratch is only a handle for the runtime, not an address the
+// GPU understands: the real device address is looked up once per device and cached here.
+static double* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {nullptr};
+
+// zero-padded copy of the caller's L^-1 (n x n, leading dimension ldz) into the padded layout the
+// sweep reads, plus the start value of the running best
+__global__ void noalloc_pack_kernel(const double* __restrict__ Linv, int n, int ldz, int npad, double* Zpad,
+                                    double* best_val, long long* best_idx) {
+  const int total = npad * npad;
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < total; e += gridDim.x * blockDim.x) {
+    const int i = e / npad, j = e - i * npad;
+    Zpad[e] = (i < n && j <= i) ? Linv[static_cast<size_t>(i) * ldz + j] : 0.0;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) { *best_val = -INFINITY; *best_idx = 0x7fffffffffffffffLL; }
+}
+
+static int noalloc_fail(int code, const char* msg) { g_create_error = msg; return code; }
+
+extern "C" int plx_acq_sweep_noalloc(int device, void* stream, const double* Xc_dev, long long N,
+                                     long long idx_base, const double* X_dev, const double* alpha_dev,
+                                     const double* Linv_dev, int ldz, int n, int d, int kernel, double nu,
+                                     double theta, int acq, double kappa, double eps, double y_max,
+                                     double* best_value_dev, long long* best_index_dev) {
+  if (device < 0 || device >= NOALLOC_MAX_DEVICES) return noalloc_fail(PLX_ERR_INVALID, "sweep_noalloc: device index out of range");
+  if (n > NOALLOC_MAX_OBS)
+    return noalloc_fail(PLX_ERR_INVALID, "sweep_noalloc: n_obs exceeds the static scratch (max 256 observations); "
+                                         "use plx_acq_sweep_dev for larger problems");
+  if (n <= 0 || d <= 0 || N < 0 || ldz < n || acq < 0 || acq > 2 || !X_dev || !alpha_dev || !Linv_dev ||
+      !best_value_dev || !best_index_dev || (N > 0 && !Xc_dev))
+    return noalloc_fail(PLX_ERR_INVALID, "sweep_noalloc: bad arguments");
+  int kind;
+  if (kernel_kind(kernel, nu, &kind) != PLX_OK) return noalloc_fail(PLX_ERR_UNSUPPORTED, "sweep_noalloc: unsupported kernel / nu");
+  if (cudaSetDevice(device) != cudaSuccess) return noalloc_fail(PLX_ERR_CUDA, "sweep_noalloc: cudaSetDevice failed");
+  if (g_noalloc_ptr[device] == nullptr) {
+    // once per device, with that device current
+    double* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_noalloc_scratch);
+    if (e != cudaSuccess || ptr == nullptr) return noalloc_fail(PLX_ERR_CUDA, "sweep_noalloc: cudaGetSymbolAddress failed");
+    e = cudaFuncSetAttribute(sweep_simple_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SWEEP_SIMPLE_SMEM);
+    if (e != cudaSuccess) return noalloc_fail(PLX_ERR_CUDA, "sweep_noalloc: cudaFuncSetAttribute failed");
+    g_noalloc_ptr[device] = ptr;
+  }
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  double* base = g_noalloc_ptr[device];
+  double* Zpad = base;
+  double* Ks = base + NOALLOC_Z;
+  double* blk_val = Ks + NOALLOC_KS;
+  long long* blk_idx = reinterpret_cast<long long*>(blk_val + NOALLOC_GRID);
+  const int npad = (n + 127) / 128 * 128;
+  noalloc_pack_kernel<<<64, 256, 0, st>>>(Linv_dev, n, ldz, npad, Zpad, best_value_dev, best_index_dev);
+  if (cudaGetLastError() != cudaSuccess) return noalloc_fail(PLX_ERR_CUDA, "sweep_noalloc: launch of the pack kernel failed");
+  if (N == 0) return PLX_OK;                    // outputs hold (-inf, INT64_MAX): no candidate
+  SweepParams p;
+  p.Xc = Xc_dev; p.N = N; p.idx_base = idx_base;
+  p.d = d; p.n = n; p.npad = npad; p.n16 = (n + 15) / 16 * 16;
+  p.X = X_dev; p.alpha = alpha_dev; p.Z = Zpad; p.ell = std::exp(theta);
+  p.kind = kind; p.acq = acq; p.kappa = kappa; p.eps = eps; p.y_max = y_max;
+  p.Ks = Ks; p.out_mean = p.out_std = p.out_acq = nullptr;
+  p.blk_val = blk_val; p.blk_idx = blk_idx;
+  const long long ntiles = (N + 127) / 128;
+  const int grid = static_cast<int>(std::min<long long>(ntiles, NOALLOC_GRID));
+  sweep_simple_kernel<<<grid, 256, SWEEP_SIMPLE_SMEM, st>>>(p);
+  if (cudaGetLastError() != cudaSuccess) return noalloc_fail(PLX_ERR_CUDA, "sweep_noalloc: launch of the sweep kernel failed");
+  sweep_merge_kernel<<<1, 32, 0, st>>>(blk_val, blk_idx, grid, best_value_dev, best_index_dev);
+  if (cudaGetLastError() != cudaSuccess) return noalloc_fail(PLX_ERR_CUDA, "sweep_noalloc: launch of the merge kernel failed");
+  return PLX_OK;
+}
