@@ -98,6 +98,24 @@ int plx_last_sweep_stats(plx_bo_handle h, double* kernel_ms, long long* launches
 /* Total number of kernels this handle has launched since creation. */
 long long plx_launch_count(plx_bo_handle h);
 
+/* Refinement stage.  Replaces the loop of scipy.optimize.minimize(method="L-BFGS-B") calls in
+ * UtilityFunction.max_compute (acquisition_function.py:95-111): every seed (S x d, clipped into the
+ * box like scipy clips x0) is refined by a bounded limited-memory BFGS with analytic gradients, all
+ * seeds in lock step on the device.  bounds is d x 2 (low, high) as SearchSpace.bounds.  Outputs per
+ * seed: refined point (S x d), acquisition value there (the reference's -res.fun), success flag
+ * (the reference's res.success: converged, not a line-search failure or an iteration limit) and the
+ * number of evaluations (nullable).  max_iter <= 0 means scipy's default 15000.  d <= 128.
+ * The caller applies the acceptance rule of :105-111 (skip failures; `>=`, so a later seed wins ties). */
+int plx_acq_refine(plx_bo_handle h, const double* seeds, int S, const double* bounds, int acq, double kappa,
+                   double eps, double y_max, int max_iter, double* x_out, double* acq_out, int* success_out,
+                   int* nfev_out);
+
+/* Acquisition value and analytic gradient at S points (S x d): what one compute() call of the
+ * reference returns (acquisition_function.py:62-68) plus d/dx, which the reference obtains by finite
+ * differences inside scipy.  grads is S x d. */
+int plx_acq_value_grad(plx_bo_handle h, const double* Xp, int S, int acq, double kappa, double eps, double y_max,
+                       double* values, double* grads);
+
 /* Warm-up sweep that allocates nothing.  No counterpart in the reference: it exists for host
  * applications that own the GPU memory budget themselves (all memory handed to their own pool, or a
  * fixed MPS / container limit) and so cannot let a library call cudaMalloc, and for latency-critical

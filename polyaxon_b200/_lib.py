@@ -38,6 +38,10 @@ SIGNATURES = {
                                   c_double, _dp, POINTER(c_longlong), c_void_p]),
     'plx_last_sweep_stats': (c_int, [c_void_p, _dp, POINTER(c_longlong)]),
     'plx_launch_count': (c_longlong, [c_void_p]),
+    'plx_acq_refine': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_double, c_double, c_double, c_int,
+                               c_void_p, c_void_p, c_void_p, c_void_p]),
+    'plx_acq_value_grad': (c_int, [c_void_p, c_void_p, c_int, c_int, c_double, c_double, c_double, c_void_p,
+                                   c_void_p]),
     'plx_acq_sweep_noalloc': (c_int, [c_int, c_void_p, c_void_p, c_longlong, c_longlong, c_void_p, c_void_p,
                                       c_void_p, c_int, c_int, c_int, c_int, c_double, c_double, c_int,
                                       c_double, c_double, c_double, c_void_p, c_void_p]),
@@ -174,6 +178,32 @@ class Handle(object):
                                                float(kappa), float(eps), float(y_max), ctypes.byref(bv),
                                                ctypes.byref(bi), _ptr(bx)))
         return bv.value, bi.value, bx
+
+    def refine(self, seeds, bounds, acq, y_max, kappa=0.0, eps=0.0, max_iter=0, want_nfev=False):
+        """Batched bounded quasi-Newton refinement of every seed.  Returns (x[S,d], acq[S], success[S])."""
+        seeds = _f64(np.atleast_2d(seeds))
+        bounds = _f64(bounds)
+        S = seeds.shape[0]
+        if seeds.shape[1] != self.d or bounds.shape != (self.d, 2):
+            raise ValueError('seeds must be (S, {0}) and bounds ({0}, 2)'.format(self.d))
+        x = np.empty((S, self.d))
+        vals = np.empty(S)
+        ok = np.zeros(S, dtype=np.int32)
+        nfev = np.zeros(S, dtype=np.int32)
+        self._check(self.lib.plx_acq_refine(self._h, _ptr(seeds), S, _ptr(bounds), int(acq), float(kappa),
+                                            float(eps), float(y_max), int(max_iter), _ptr(x), _ptr(vals),
+                                            _ptr(ok), _ptr(nfev)))
+        if want_nfev:
+            return x, vals, ok.astype(bool), nfev
+        return x, vals, ok.astype(bool)
+
+    def acq_value_grad(self, points, acq, y_max, kappa=0.0, eps=0.0):
+        pts = _f64(np.atleast_2d(points))
+        vals = np.empty(pts.shape[0])
+        grads = np.empty_like(pts)
+        self._check(self.lib.plx_acq_value_grad(self._h, _ptr(pts), pts.shape[0], int(acq), float(kappa),
+                                                float(eps), float(y_max), _ptr(vals), _ptr(grads)))
+        return vals, grads
 
     def last_sweep_stats(self):
         ms, nl = c_double(), c_longlong()

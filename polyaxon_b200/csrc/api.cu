@@ -1,8 +1,7 @@
 // C ABI of libplxbo.so: handle, workspace management and launch sequences.
 // Declarations and the reference call site each entry point replaces: include/plxbo.h.
 #include "../../include/plxbo.h"
-#include "sweep.cuh"
-#include "lbfgsb1d.h"
+#include "refine.cuh"
 
 #include <cstdio>
 #include <cstring>
@@ -58,6 +57,14 @@ struct plx_bo {
   std::vector<cudaEvent_t> ev_pool;
   int sweep_impl = 1;
   double last_ms = 0.0; long long last_launches = 0;
+
+  // refinement workspace
+  int rf_cap_s = 0, rf_cap_npad = 0, rf_cap_d = 0;
+  double *rf_kv = nullptr, *rf_kp = nullptr, *rf_v = nullptr, *rf_w = nullptr, *rf_vec = nullptr,
+         *rf_bounds = nullptr, *rf_val = nullptr, *rf_grad = nullptr;
+  RefineScalars* rf_sc = nullptr;
+  int* rf_active = nullptr;
+  long long last_refine_rounds = 0;
 };
 
 #define CK(call)                                                                            \
@@ -165,7 +172,8 @@ extern "C" void plx_bo_destroy(plx_bo_handle h) {
   void* ptrs[] = {h->dX, h->dy, h->bp.A, h->bp.L, h->bp.U, h->bp.W, h->bp.T, h->d_thetas, h->d_logdet, h->d_w,
                   h->d_alpha, h->d_partial, h->d_lml, h->d_grad, h->d_info, h->dZ, h->d_alpha_state, h->dKs,
                   h->d_blk_val, h->d_blk_idx, h->d_best_val, h->d_best_idx, h->dcand[0], h->dcand[1],
-                  h->d_out[0], h->d_out[1], h->d_out[2]};
+                  h->d_out[0], h->d_out[1], h->d_out[2], h->rf_kv, h->rf_kp, h->rf_v, h->rf_w, h->rf_vec,
+                  h->rf_bounds, h->rf_val, h->rf_grad, h->rf_sc, h->rf_active};
   for (void* p : ptrs) if (p) cudaFree(p);
   for (int i = 0; i < 2; ++i) { if (h->ev_copy[i]) cudaEventDestroy(h->ev_copy[i]); if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]); }
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
@@ -556,6 +564,131 @@ extern "C" int plx_lbfgsb1d_minimize(plx_fg_callback fg, void* user, double x0, 
   if (n_evals) *n_evals = m.nfev;
   if (n_iters) *n_iters = m.iter;
   if (status) *status = m.status;
+  return PLX_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// refinement (acquisition_function.py:95-111) and point-wise acquisition value + gradient
+// ---------------------------------------------------------------------------------------------
+static int ensure_refine(plx_bo* h, int S) {
+  if (S <= h->rf_cap_s && h->npad == h->rf_cap_npad && h->d == h->rf_cap_d) return PLX_OK;
+  void* old[] = {h->rf_kv, h->rf_kp, h->rf_v, h->rf_w, h->rf_vec, h->rf_bounds, h->rf_val, h->rf_grad, h->rf_sc, h->rf_active};
+  for (void* p : old) if (p) CK(cudaFree(p));
+  h->rf_kv = h->rf_kp = h->rf_v = h->rf_w = h->rf_vec = h->rf_bounds = h->rf_val = h->rf_grad = nullptr;
+  h->rf_sc = nullptr; h->rf_active = nullptr; h->rf_cap_s = 0;
+  const size_t sn = static_cast<size_t>(S) * h->npad;
+  CK(cudaMalloc(&h->rf_kv, sizeof(double) * sn));
+  CK(cudaMalloc(&h->rf_kp, sizeof(double) * sn));
+  CK(cudaMalloc(&h->rf_v, sizeof(double) * sn));
+  CK(cudaMalloc(&h->rf_w, sizeof(double) * sn));
+  CK(cudaMalloc(&h->rf_vec, sizeof(double) * rf_vec_stride(h->d) * S));
+  CK(cudaMalloc(&h->rf_bounds, sizeof(double) * 2 * h->d));
+  CK(cudaMalloc(&h->rf_val, sizeof(double) * S));
+  CK(cudaMalloc(&h->rf_grad, sizeof(double) * S * h->d));
+  CK(cudaMalloc(&h->rf_sc, sizeof(RefineScalars) * S));
+  CK(cudaMalloc(&h->rf_active, sizeof(int)));
+  h->rf_cap_s = S; h->rf_cap_npad = h->npad; h->rf_cap_d = h->d;
+  return PLX_OK;
+}
+
+static void fill_refine(plx_bo* h, RefineParams& p, int S, int acq, double kappa, double eps, double y_max, int max_iter) {
+  p.S = S; p.d = h->d; p.n = h->n; p.npad = h->npad; p.kind = h->kind; p.acq = acq; p.max_iter = max_iter;
+  p.ell = std::exp(h->theta); p.kappa = kappa; p.eps = eps; p.y_max = y_max;
+  p.X = h->dX; p.alpha = h->d_alpha_state; p.Z = h->dZ; p.bounds = h->rf_bounds;
+  p.kv = h->rf_kv; p.kp = h->rf_kp; p.v = h->rf_v; p.w = h->rf_w;
+  p.vec = h->rf_vec; p.vec_stride = rf_vec_stride(h->d); p.sc = h->rf_sc;
+  p.val_out = nullptr; p.grad_out = nullptr; p.active = h->rf_active;
+}
+
+// one round: everything a seed needs to evaluate the acquisition and its gradient at its trial point
+static int launch_refine_round(plx_bo* h, const RefineParams& p) {
+  cudaStream_t st = h->stream;
+  refine_kstar_kernel<<<dim3((p.npad + 127) / 128, p.S), 128, 0, st>>>(p);
+  LAUNCH_CHECK("refine_kstar_kernel");
+  refine_v_kernel<<<(p.n + 7) / 8, 256, 0, st>>>(p);
+  LAUNCH_CHECK("refine_v_kernel");
+  refine_w_kernel<<<(p.n + 31) / 32, 256, 0, st>>>(p);
+  LAUNCH_CHECK("refine_w_kernel");
+  refine_step_kernel<<<p.S, 128, 0, st>>>(p);
+  LAUNCH_CHECK("refine_step_kernel");
+  return PLX_OK;
+}
+
+static int upload_points(plx_bo* h, const double* pts, int S, const double* bounds) {
+  // each seed's block starts with its current point x
+  const size_t stride = rf_vec_stride(h->d);
+  CK(cudaMemcpy2DAsync(h->rf_vec, stride * 8, pts, static_cast<size_t>(h->d) * 8, static_cast<size_t>(h->d) * 8, S,
+                       cudaMemcpyHostToDevice, h->stream));
+  if (bounds) CK(cudaMemcpyAsync(h->rf_bounds, bounds, sizeof(double) * 2 * h->d, cudaMemcpyHostToDevice, h->stream));
+  return PLX_OK;
+}
+
+extern "C" int plx_acq_value_grad(plx_bo_handle h, const double* Xp, int S, int acq, double kappa, double eps,
+                                  double y_max, double* values, double* grads) {
+  if (!h || !Xp || S <= 0 || acq < 0 || acq > 2 || !values || !grads) return h ? fail(h, PLX_ERR_INVALID, "acq_value_grad: bad arguments") : PLX_ERR_INVALID;
+  if (!h->have_state) return fail(h, PLX_ERR_STATE, "acq_value_grad: no posterior state");
+  if (h->d > RF_DMAX) return fail(h, PLX_ERR_UNSUPPORTED, "acq_value_grad: d exceeds 128");
+  CK(cudaSetDevice(h->device));
+  int r;
+  if ((r = ensure_refine(h, S)) != PLX_OK) return r;
+  if ((r = upload_points(h, Xp, S, nullptr)) != PLX_OK) return r;
+  RefineParams p;
+  fill_refine(h, p, S, acq, kappa, eps, y_max, 0);
+  p.val_out = h->rf_val; p.grad_out = h->rf_grad;
+  if ((r = launch_refine_round(h, p)) != PLX_OK) return r;
+  CK(cudaMemcpyAsync(values, h->rf_val, sizeof(double) * S, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaMemcpyAsync(grads, h->rf_grad, sizeof(double) * S * h->d, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return PLX_OK;
+}
+
+extern "C" int plx_acq_refine(plx_bo_handle h, const double* seeds, int S, const double* bounds, int acq,
+                              double kappa, double eps, double y_max, int max_iter, double* x_out, double* acq_out,
+                              int* success_out, int* nfev_out) {
+  if (!h || S < 0 || (S > 0 && (!seeds || !x_out || !acq_out || !success_out)) || !bounds || acq < 0 || acq > 2)
+    return h ? fail(h, PLX_ERR_INVALID, "acq_refine: bad arguments") : PLX_ERR_INVALID;
+  if (!h->have_state) return fail(h, PLX_ERR_STATE, "acq_refine: no posterior state");
+  if (h->d > RF_DMAX) return fail(h, PLX_ERR_UNSUPPORTED, "acq_refine: d exceeds 128");
+  h->last_refine_rounds = 0;
+  if (S == 0) return PLX_OK;
+  CK(cudaSetDevice(h->device));
+  if (max_iter <= 0) max_iter = 15000;                 // scipy's maxiter
+  const int d = h->d;
+  for (int q = 0; q < d; ++q)
+    if (!(bounds[2 * q] <= bounds[2 * q + 1])) return fail(h, PLX_ERR_INVALID, "acq_refine: lower bound above upper bound");
+  int r;
+  if ((r = ensure_refine(h, S)) != PLX_OK) return r;
+  // scipy clips x0 into the box before the first evaluation
+  std::vector<double> x0(static_cast<size_t>(S) * d);
+  for (int s = 0; s < S; ++s)
+    for (int q = 0; q < d; ++q)
+      x0[static_cast<size_t>(s) * d + q] = std::min(std::max(seeds[static_cast<size_t>(s) * d + q], bounds[2 * q]), bounds[2 * q + 1]);
+  if ((r = upload_points(h, x0.data(), S, bounds)) != PLX_OK) return r;
+  CK(cudaMemsetAsync(h->rf_sc, 0, sizeof(RefineScalars) * S, h->stream));
+  CK(cudaMemcpyAsync(h->rf_active, &S, sizeof(int), cudaMemcpyHostToDevice, h->stream));
+  RefineParams p;
+  fill_refine(h, p, S, acq, kappa, eps, y_max, max_iter);
+  const long long max_rounds = 15000;                  // scipy's maxfun
+  int active = S;
+  long long rounds = 0;
+  while (active > 0 && rounds < max_rounds) {
+    for (int k = 0; k < 4 && rounds < max_rounds; ++k, ++rounds)
+      if ((r = launch_refine_round(h, p)) != PLX_OK) return r;
+    CK(cudaMemcpyAsync(&active, h->rf_active, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+  }
+  h->last_refine_rounds = rounds;
+  std::vector<RefineScalars> sc(S);
+  const size_t stride = rf_vec_stride(d);
+  CK(cudaMemcpyAsync(sc.data(), h->rf_sc, sizeof(RefineScalars) * S, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaMemcpy2DAsync(x_out, static_cast<size_t>(d) * 8, h->rf_vec, stride * 8, static_cast<size_t>(d) * 8, S,
+                       cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  for (int s = 0; s < S; ++s) {
+    acq_out[s] = -sc[s].f;
+    success_out[s] = (sc[s].phase == 2 && sc[s].status == 0) ? 1 : 0;
+    if (nfev_out) nfev_out[s] = sc[s].nfev;
+  }
   return PLX_OK;
 }
 

@@ -19,7 +19,17 @@
 #include <cmath>
 #include <algorithm>
 
+#ifdef __CUDACC__
+#define PLX_HD __host__ __device__
+#else
+#define PLX_HD
+#endif
+
 namespace plx {
+
+PLX_HD inline double hd_abs(double a) { return a < 0.0 ? -a : a; }
+PLX_HD inline double hd_max(double a, double b) { return a < b ? b : a; }   // exactly std::max / std::min,
+PLX_HD inline double hd_min(double a, double b) { return b < a ? b : a; }   // including their NaN behaviour
 
 struct Dcsrch {
   // persistent state of one line search
@@ -27,34 +37,34 @@ struct Dcsrch {
   double ginit, gtest, gx, gy, finit, fx, fy, stx, sty, stmin, stmax, width, width1;
   enum Task { START, FG, CONVERGENCE, WARNING, ERROR } task;
 
-  static void dcstep(double& stx, double& fx, double& dx, double& sty, double& fy, double& dy, double& stp,
+  PLX_HD static void dcstep(double& stx, double& fx, double& dx, double& sty, double& fy, double& dy, double& stp,
                      double fp, double dp, bool& brackt, double stpmin, double stpmax) {
-    const double sgnd = dp * (dx / std::fabs(dx));
+    const double sgnd = dp * (dx / hd_abs(dx));
     double stpf;
     if (fp > fx) {                                   // case 1: higher value -> minimum bracketed
       const double theta = 3.0 * (fx - fp) / (stp - stx) + dx + dp;
-      const double s = std::max(std::fabs(theta), std::max(std::fabs(dx), std::fabs(dp)));
-      double gamma = s * std::sqrt((theta / s) * (theta / s) - (dx / s) * (dp / s));
+      const double s = hd_max(hd_abs(theta), hd_max(hd_abs(dx), hd_abs(dp)));
+      double gamma = s * sqrt((theta / s) * (theta / s) - (dx / s) * (dp / s));
       if (stp < stx) gamma = -gamma;
       const double p = (gamma - dx) + theta, q = ((gamma - dx) + gamma) + dp, r = p / q;
       const double stpc = stx + r * (stp - stx);
       const double stpq = stx + ((dx / ((fx - fp) / (stp - stx) + dx)) / 2.0) * (stp - stx);
-      stpf = (std::fabs(stpc - stx) < std::fabs(stpq - stx)) ? stpc : stpc + (stpq - stpc) / 2.0;
+      stpf = (hd_abs(stpc - stx) < hd_abs(stpq - stx)) ? stpc : stpc + (stpq - stpc) / 2.0;
       brackt = true;
     } else if (sgnd < 0.0) {                         // case 2: derivatives of opposite sign
       const double theta = 3.0 * (fx - fp) / (stp - stx) + dx + dp;
-      const double s = std::max(std::fabs(theta), std::max(std::fabs(dx), std::fabs(dp)));
-      double gamma = s * std::sqrt((theta / s) * (theta / s) - (dx / s) * (dp / s));
+      const double s = hd_max(hd_abs(theta), hd_max(hd_abs(dx), hd_abs(dp)));
+      double gamma = s * sqrt((theta / s) * (theta / s) - (dx / s) * (dp / s));
       if (stp > stx) gamma = -gamma;
       const double p = (gamma - dp) + theta, q = ((gamma - dp) + gamma) + dx, r = p / q;
       const double stpc = stp + r * (stx - stp);
       const double stpq = stp + (dp / (dp - dx)) * (stx - stp);
-      stpf = (std::fabs(stpc - stp) > std::fabs(stpq - stp)) ? stpc : stpq;
+      stpf = (hd_abs(stpc - stp) > hd_abs(stpq - stp)) ? stpc : stpq;
       brackt = true;
-    } else if (std::fabs(dp) < std::fabs(dx)) {      // case 3: derivative magnitude decreases
+    } else if (hd_abs(dp) < hd_abs(dx)) {      // case 3: derivative magnitude decreases
       const double theta = 3.0 * (fx - fp) / (stp - stx) + dx + dp;
-      const double s = std::max(std::fabs(theta), std::max(std::fabs(dx), std::fabs(dp)));
-      double gamma = s * std::sqrt(std::max(0.0, (theta / s) * (theta / s) - (dx / s) * (dp / s)));
+      const double s = hd_max(hd_abs(theta), hd_max(hd_abs(dx), hd_abs(dp)));
+      double gamma = s * sqrt(hd_max(0.0, (theta / s) * (theta / s) - (dx / s) * (dp / s)));
       if (stp > stx) gamma = -gamma;
       const double p = (gamma - dp) + theta, q = (gamma + (dx - dp)) + gamma, r = p / q;
       double stpc;
@@ -62,19 +72,19 @@ struct Dcsrch {
       else stpc = (stp > stx) ? stpmax : stpmin;
       const double stpq = stp + (dp / (dp - dx)) * (stx - stp);
       if (brackt) {
-        stpf = (std::fabs(stpc - stp) < std::fabs(stpq - stp)) ? stpc : stpq;
-        if (stp > stx) stpf = std::min(stp + 0.66 * (sty - stp), stpf);
-        else stpf = std::max(stp + 0.66 * (sty - stp), stpf);
+        stpf = (hd_abs(stpc - stp) < hd_abs(stpq - stp)) ? stpc : stpq;
+        if (stp > stx) stpf = hd_min(stp + 0.66 * (sty - stp), stpf);
+        else stpf = hd_max(stp + 0.66 * (sty - stp), stpf);
       } else {
-        stpf = (std::fabs(stpc - stp) > std::fabs(stpq - stp)) ? stpc : stpq;
-        stpf = std::min(stpmax, stpf);
-        stpf = std::max(stpmin, stpf);
+        stpf = (hd_abs(stpc - stp) > hd_abs(stpq - stp)) ? stpc : stpq;
+        stpf = hd_min(stpmax, stpf);
+        stpf = hd_max(stpmin, stpf);
       }
     } else {                                          // case 4: derivative does not decrease
       if (brackt) {
         const double theta = 3.0 * (fp - fy) / (sty - stp) + dy + dp;
-        const double s = std::max(std::fabs(theta), std::max(std::fabs(dy), std::fabs(dp)));
-        double gamma = s * std::sqrt((theta / s) * (theta / s) - (dy / s) * (dp / s));
+        const double s = hd_max(hd_abs(theta), hd_max(hd_abs(dy), hd_abs(dp)));
+        double gamma = s * sqrt((theta / s) * (theta / s) - (dy / s) * (dp / s));
         if (stp > sty) gamma = -gamma;
         const double p = (gamma - dp) + theta, q = ((gamma - dp) + gamma) + dy, r = p / q;
         stpf = stp + r * (sty - stp);
@@ -91,7 +101,7 @@ struct Dcsrch {
   }
 
   // one call of dcsrch; `first` distinguishes the START entry
-  void step(bool first, double f, double g, double& stp, double ftol, double gtol, double xtol,
+  PLX_HD void step(bool first, double f, double g, double& stp, double ftol, double gtol, double xtol,
             double stpmin, double stpmax) {
     const double xtrapl = 1.1, xtrapu = 4.0;
     if (first) {
@@ -109,7 +119,7 @@ struct Dcsrch {
     if (brackt && stmax - stmin <= xtol * stmax) task = WARNING;
     if (stp == stpmax && f <= ftest && g <= gtest) task = WARNING;
     if (stp == stpmin && (f > ftest || g >= gtest)) task = WARNING;
-    if (f <= ftest && std::fabs(g) <= gtol * (-ginit)) task = CONVERGENCE;
+    if (f <= ftest && hd_abs(g) <= gtol * (-ginit)) task = CONVERGENCE;
     if (task == WARNING || task == CONVERGENCE) return;
     if (stage == 1 && f <= fx && f > ftest) {
       const double fm = f - stp * gtest; double fxm = fx - stx * gtest, fym = fy - sty * gtest;
@@ -120,13 +130,13 @@ struct Dcsrch {
       dcstep(stx, fx, gx, sty, fy, gy, stp, f, g, brackt, stmin, stmax);
     }
     if (brackt) {
-      if (std::fabs(sty - stx) >= 0.66 * width1) stp = stx + 0.5 * (sty - stx);
-      width1 = width; width = std::fabs(sty - stx);
+      if (hd_abs(sty - stx) >= 0.66 * width1) stp = stx + 0.5 * (sty - stx);
+      width1 = width; width = hd_abs(sty - stx);
     }
-    if (brackt) { stmin = std::min(stx, sty); stmax = std::max(stx, sty); }
+    if (brackt) { stmin = hd_min(stx, sty); stmax = hd_max(stx, sty); }
     else { stmin = stp + xtrapl * (stp - stx); stmax = stp + xtrapu * (stp - stx); }
-    stp = std::max(stp, stpmin);
-    stp = std::min(stp, stpmax);
+    stp = hd_max(stp, stpmin);
+    stp = hd_min(stp, stpmax);
     if ((brackt && (stp <= stmin || stp >= stmax)) || (brackt && stmax - stmin <= xtol * stmax)) stp = stx;
     task = FG;
   }

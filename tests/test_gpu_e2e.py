@@ -1,0 +1,117 @@
+"""GPU: the drop-in classes end to end (BOSearchManager -> BOOptimizer -> UtilityFunction) against
+what the real reference suggested for the same config, observations and seed (tests/golden)."""
+import warnings
+
+import numpy as np
+import pytest
+
+from conftest import load_golden
+from oracle import gp_numpy as G
+
+pytestmark = pytest.mark.gpu
+
+
+def _config(g, matrix, optimization='maximize'):
+    from polyaxon_b200.schemas.hptuning import HPTuningConfig
+    acq = {0: 'ucb', 1: 'ei', 2: 'poi'}[int(g['acq'])]
+    uf = {'acquisition_function': acq,
+          'gaussian_process': {'kernel': 'rbf' if int(g['kernel']) == 0 else 'matern',
+                               'length_scale': float(g['length_scale']), 'nu': float(g['nu']),
+                               'n_restarts_optimizer': int(g['n_restarts'])},
+          'n_warmup': int(g['n_warmup']), 'n_iter': int(g['n_iter'])}
+    if acq == 'ucb':
+        uf['kappa'] = float(g['kappa'])
+    else:
+        uf['eps'] = float(g['eps'])
+    return HPTuningConfig.from_dict({
+        'seed': int(g['seed']), 'concurrency': 2,
+        'bo': {'n_iterations': 5, 'n_initial_trials': 5, 'metric': {'name': 'm', 'optimization': optimization},
+               'utility_function': uf},
+        'matrix': matrix})
+
+
+def _acq_at(g, theta, x):
+    L, a = G.posterior_state(g['X'], g['y'], theta, int(g['kernel']), float(g['nu']))
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        m, s = G.predict(np.atleast_2d(x), g['X'], L, a, theta, int(g['kernel']), float(g['nu']))
+    return float(G.acquisition(m, s, int(g['acq']), float(g['y_max']), float(np.nan_to_num(g['kappa'])),
+                               float(np.nan_to_num(g['eps'])))[0])
+
+
+@pytest.mark.parametrize('name', ['c1_d2_n15_m25_ucb', 'c3_d32_n512_m15_poi', 'c5_d16_n128_m05_ucb',
+                                  'c5_d16_n128_m25_ei'])
+def test_continuous_spaces_through_the_manager(name):
+    from polyaxon_b200.hpsearch.schemas.bayesian_optimization import BOIterationConfig
+    from polyaxon_b200.hpsearch.search_managers import get_search_algorithm_manager
+    g = load_golden(name)
+    d = g['X'].shape[1]
+    keys = ['x%03d' % i for i in range(d)]
+    cfg = _config(g, {k: {'uniform': [0, 1]} for k in keys})
+    manager = get_search_algorithm_manager(cfg)
+    n = g['X'].shape[0]
+    iteration = BOIterationConfig.from_dict({
+        'iteration': 1, 'experiment_ids': list(range(n)),
+        'experiments_configs': [[i, dict(zip(keys, row.tolist()))] for i, row in enumerate(g['X'])],
+        'experiments_metrics': [[i, float(v)] for i, v in enumerate(g['y'])]})
+    out = manager.get_suggestions(iteration)
+    assert isinstance(out, list) and len(out) == 1
+    suggestion = out[0]
+    assert sorted(suggestion) == keys
+    x = np.array([suggestion[k] for k in keys])
+    assert all(isinstance(suggestion[k], np.float64) for k in keys)
+    assert np.all(x >= 0) and np.all(x <= 1)
+    # same GP (theta* within optimiser tolerance) and an acquisition value no worse than the reference's
+    theta = float(g['theta'])
+    ref_best = _acq_at(g, theta, g['x_star'])
+    mine = _acq_at(g, theta, x)
+    assert mine >= ref_best - 1e-6 * max(1.0, abs(ref_best))
+
+
+def test_mixed_space_decodes_like_the_reference():
+    """C2: 3 continuous + 2 discrete + one 3-way categorical, RBF, EI."""
+    from polyaxon_b200.hpsearch.search_managers.bayesian_optimization.optimizer import BOOptimizer
+    g = load_golden('c2_d8_n256_rbf_ei')
+    acts = ['relu', 'tanh', 'gelu']
+    matrix = {'a_lr': {'uniform': [0, 1]}, 'b_mom': {'uniform': [0, 1]}, 'c_wd': {'uniform': [0, 1]},
+              'd_layers': {'range': [1, 9, 1]}, 'e_width': {'linspace': [0, 1, 11]},
+              'f_act': {'values': acts}}
+    cfg = _config(g, matrix)
+    configs = [{'a_lr': r[0], 'b_mom': r[1], 'c_wd': r[2], 'd_layers': int(r[3]), 'e_width': float(r[4]),
+                'f_act': acts[int(np.argmax(r[5:8]))]} for r in g['X']]
+    optimizer = BOOptimizer(hptuning_config=cfg)
+    optimizer.add_observations(configs=configs, metrics=g['y'].tolist())
+    assert np.array_equal(optimizer.space.x, g['X'])
+    assert np.array_equal(optimizer.space.bounds, g['bounds'])
+    x = optimizer._maximize()
+    gp = optimizer.utility_function.gaussian_process
+    assert gp.theta_ == pytest.approx(float(g['theta']), abs=1e-6)
+    assert gp.log_marginal_likelihood_value_ == pytest.approx(float(g['lml']), rel=1e-9)
+    theta = float(g['theta'])
+    assert _acq_at(g, theta, x) >= _acq_at(g, theta, g['x_star']) - 1e-6
+    suggestion = optimizer.space.get_suggestion(x)
+    assert suggestion['f_act'] in acts
+    assert suggestion['d_layers'] in list(range(1, 9))
+    assert any(abs(suggestion['e_width'] - v) < 1e-12 for v in np.linspace(0, 1, 11))
+    assert 0 <= suggestion['a_lr'] <= 1
+
+
+def test_reference_fixture_sets_run_and_stay_in_bounds():
+    """The observation sets of test_search_managers.py:894-1063 (closed-form nu instead of 1.9):
+    same assertions as the reference's own tests -- bounds membership."""
+    from polyaxon_b200.hpsearch.search_managers.bayesian_optimization.optimizer import BOOptimizer
+    g = load_golden('ref10_m15_ucb')
+    matrix = {'learning_rate': {'uniform': [0.001, 0.01]}, 'dropout': {'values': [0.25, 0.3]},
+              'activation': {'values': ['relu', 'sigmoid']}}
+    cfg = _config(g, matrix, optimization='minimize')
+    # columns: activation one-hot (relu, sigmoid), dropout, learning_rate
+    configs = [{'activation': ['relu', 'sigmoid'][int(np.argmax(r[0:2]))], 'dropout': float(r[2]),
+                'learning_rate': float(r[3])} for r in g['X']]
+    optimizer = BOOptimizer(hptuning_config=cfg)
+    optimizer.add_observations(configs=configs, metrics=(-g['y']).tolist())
+    assert np.array_equal(optimizer.space.x, g['X'])
+    suggestion = optimizer.get_suggestion()
+    assert 0.001 <= suggestion['learning_rate'] <= 0.01
+    assert suggestion['dropout'] in [0.25, 0.3]
+    assert suggestion['activation'] in ['relu', 'sigmoid']
+    assert optimizer.utility_function.gaussian_process.theta_ == pytest.approx(float(g['theta']), abs=1e-6)
