@@ -34,6 +34,8 @@ sys.path.insert(0, ROOT)
 D, N_OBS, NU = 32, 2048, 1.5
 THETA = 1.2                      # log length-scale of the benchmark state (near the fitted optimum)
 METRIC = 'acquisition evals/sec (FP64) at d=32,n_obs=2048'
+# dram__bytes_read.sum + dram__bytes_write.sum of sweep_tma_kernel per candidate (profiles/r01_ncu_sweep_tma_*.csv)
+DRAM_BYTES_PER_CANDIDATE = (18.718e9 + 2.488e9) / 151552
 UNIT = 'evals/s'
 
 
@@ -107,14 +109,17 @@ def reference_arm(args, rank):
         ys = R.acquisition(gp, xc, G.ACQ_POI, y_max, 0.0, 0.0)
         return int(ys.argmax())
 
-    for _ in range(min(args.warmup, 1)):
-        step()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        step()
-    dt = (time.perf_counter() - t0) / args.steps
-    value = sample / dt
+    # torchrun exports OMP_NUM_THREADS=1; the baseline is entitled to every host core
+    from threadpoolctl import threadpool_limits
     cores = os.cpu_count()
+    with threadpool_limits(limits=cores):
+        for _ in range(min(args.warmup, 1)):
+            step()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            step()
+        dt = (time.perf_counter() - t0) / args.steps
+    value = sample / dt
     line = {
         'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
         'steps': args.steps, 'warmup': min(args.warmup, 1), 'ms_per_step': dt * 1e3,
@@ -127,6 +132,68 @@ def reference_arm(args, rank):
         'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
     }
     print(json.dumps(line))
+
+
+def latency_configs():
+    """C1 and C2 of BASELINE.json as hptuning sections + observations (for get_suggestions latency)."""
+    from oracle.reference_path import synthetic_problem
+    out = []
+    X, y, _ = synthetic_problem(15, 2)
+    out.append(('C1 d=2 n=15 matern2.5 ucb N=1e5 S=10',
+                dict(kernel='matern', nu=2.5, acq='ucb', kappa=2.576, eps=None, n_warmup=100000, n_iter=10,
+                     restarts=0), X, y))
+    X, y, _ = synthetic_problem(256, 8)
+    out.append(('C2 d=8 n=256 rbf ei N=1e6 S=10',
+                dict(kernel='rbf', nu=1.5, acq='ei', kappa=None, eps=0.0, n_warmup=1000000, n_iter=10,
+                     restarts=0), X, y))
+    return out
+
+
+def measure_latency(reps_gpu=7):
+    """p50 of BOOptimizer.get_suggestion() through the drop-in Python classes, and the same call on
+    the CPU reference path (oracle/reference_path.py), same seed and observations."""
+    import warnings
+    from oracle import gp_numpy as G
+    from oracle import reference_path as R
+    from polyaxon_b200.hpsearch.search_managers.bayesian_optimization.optimizer import BOOptimizer
+    from polyaxon_b200.schemas.hptuning import HPTuningConfig
+    from threadpoolctl import threadpool_limits
+    results = []
+    for label, c, X, y in latency_configs():
+        d = X.shape[1]
+        keys = ['x%03d' % i for i in range(d)]
+        uf = {'acquisition_function': c['acq'], 'n_warmup': c['n_warmup'], 'n_iter': c['n_iter'],
+              'gaussian_process': {'kernel': c['kernel'], 'length_scale': 1.0, 'nu': c['nu'],
+                                   'n_restarts_optimizer': c['restarts']}}
+        uf['kappa' if c['acq'] == 'ucb' else 'eps'] = c['kappa'] if c['acq'] == 'ucb' else c['eps']
+        cfg = HPTuningConfig.from_dict({
+            'seed': 17, 'concurrency': 1,
+            'bo': {'n_iterations': 5, 'n_initial_trials': 5, 'metric': {'name': 'm', 'optimization': 'maximize'},
+                   'utility_function': uf},
+            'matrix': {k: {'uniform': [0, 1]} for k in keys}})
+        configs = [dict(zip(keys, row.tolist())) for row in X]
+        times = []
+        for _ in range(reps_gpu + 1):
+            t0 = time.perf_counter()
+            opt = BOOptimizer(hptuning_config=cfg)
+            opt.add_observations(configs=configs, metrics=y.tolist())
+            suggestion = opt.get_suggestion()
+            times.append((time.perf_counter() - t0) * 1e3)
+        gpu_ms = float(np.median(times[1:]))
+        bounds = np.tile(np.array([[0.0, 1.0]]), (d, 1))
+        cpu = []
+        with threadpool_limits(limits=os.cpu_count()), warnings.catch_warnings():
+            warnings.simplefilter('ignore')
+            for _ in range(2 if c['n_warmup'] <= 100000 else 1):
+                t0 = time.perf_counter()
+                R.suggest(X, y, bounds, G.KERNEL_RBF if c['kernel'] == 'rbf' else G.KERNEL_MATERN, 1.0, c['nu'],
+                          c['restarts'], {'ucb': 0, 'ei': 1, 'poi': 2}[c['acq']], c['kappa'] or 0.0, c['eps'] or 0.0,
+                          17, c['n_warmup'], c['n_iter'], chunk=65536)
+                cpu.append((time.perf_counter() - t0) * 1e3)
+        results.append({'config': label, 'get_suggestions_p50_ms': gpu_ms, 'cpu_reference_ms': float(np.median(cpu)),
+                        'includes': 'host RandomState draws of all candidates (reference RNG contract), H2D, fit, '
+                                    'sweep, refinement, decode'})
+    return results
 
 
 def workload_config(args, world):
@@ -265,8 +332,10 @@ def main():
             'gpu_launches': launches,
             'clocks': clocks,
             'roofline': {'bound': 'tensor', 'achieved': achieved, 'peak': peak, 'unit': 'TFLOP/s',
-                         'frac': achieved / peak, 'traffic': None,
+                         'frac': achieved / peak, 'traffic': DRAM_BYTES_PER_CANDIDATE * n_local,
                          'kernel': 'sweep_tma_kernel' if args.sweep_impl == 1 else 'sweep_simple_kernel',
+                         'traffic_note': 'DRAM bytes of this kernel from profiles/ (ncu --set full at 151552 '
+                                         'candidates), scaled per candidate: the K* slab round trip, by design',
                          'kernel_ms_per_launch': kernel_ms,
                          'flops_per_eval': fpe,
                          'peak_source': 'cuBLAS DGEMM 8192^3 FP64 measured in this run (best of 6); '
@@ -287,6 +356,12 @@ def main():
         except Exception as exc:  # the baseline must never hide the GPU numbers
             line['cpu_baseline'] = {'value': None, 'unit': UNIT, 'cores': os.cpu_count(), 'kind': 'port',
                                     'sample': 'failed: %r' % (exc,)}
+        if world == 1 and not args.skip_latency:
+            try:
+                h.set_stream(None)
+                line['latency'] = measure_latency()
+            except Exception as exc:
+                line['latency'] = 'failed: %r' % (exc,)
         print(json.dumps(line))
     h.close()
     if world > 1:

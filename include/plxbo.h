@@ -47,7 +47,8 @@ const char* plx_version(void);
 /* Use the caller's CUDA stream (a cudaStream_t passed as void*); NULL restores the handle's own. */
 int plx_bo_set_stream(plx_bo_handle h, void* stream);
 
-/* Options: "sweep_impl" (1 = TMA ring [default], 0 = plain-load cross-check). */
+/* Options: "sweep_impl" (1 = TMA ring [default], 0 = plain-load cross-check); "sweep_dbg" (profiling
+ * only: bit 0 skips the cross-kernel build after the first tile, bit 1 skips the tensor-pipe work). */
 int plx_bo_set_option(plx_bo_handle h, const char* name, long long value);
 
 /* Observations.  Replaces the arguments of GaussianProcessRegressor.fit(X, y) at optimizer.py:21

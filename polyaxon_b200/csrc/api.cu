@@ -46,6 +46,7 @@ struct plx_bo {
   double* dZ = nullptr; size_t z_cap = 0;
   double* d_alpha_state = nullptr; size_t as_cap = 0;
   double* dKs = nullptr; size_t ks_cap = 0;
+  double* dXt = nullptr; size_t xt_cap = 0;
   CUtensorMap tmZ, tmK;
 
   // sweep buffers
@@ -55,7 +56,7 @@ struct plx_bo {
   double* d_out[3] = {nullptr, nullptr, nullptr}; size_t out_cap = 0;
   cudaEvent_t ev_copy[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
   std::vector<cudaEvent_t> ev_pool;
-  int sweep_impl = 1;
+  int sweep_impl = 1, sweep_dbg = 0;
   double last_ms = 0.0; long long last_launches = 0;
 
   // refinement workspace
@@ -170,7 +171,7 @@ extern "C" void plx_bo_destroy(plx_bo_handle h) {
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
   void* ptrs[] = {h->dX, h->dy, h->bp.A, h->bp.L, h->bp.U, h->bp.W, h->bp.T, h->d_thetas, h->d_logdet, h->d_w,
-                  h->d_alpha, h->d_partial, h->d_lml, h->d_grad, h->d_info, h->dZ, h->d_alpha_state, h->dKs,
+                  h->d_alpha, h->d_partial, h->d_lml, h->d_grad, h->d_info, h->dZ, h->d_alpha_state, h->dKs, h->dXt,
                   h->d_blk_val, h->d_blk_idx, h->d_best_val, h->d_best_idx, h->dcand[0], h->dcand[1],
                   h->d_out[0], h->d_out[1], h->d_out[2], h->rf_kv, h->rf_kp, h->rf_v, h->rf_w, h->rf_vec,
                   h->rf_bounds, h->rf_val, h->rf_grad, h->rf_sc, h->rf_active};
@@ -191,6 +192,7 @@ extern "C" int plx_bo_set_stream(plx_bo_handle h, void* stream) {
 extern "C" int plx_bo_set_option(plx_bo_handle h, const char* name, long long value) {
   if (!h || !name) return PLX_ERR_INVALID;
   if (std::strcmp(name, "sweep_impl") == 0 && (value == 0 || value == 1)) { h->sweep_impl = static_cast<int>(value); return PLX_OK; }
+  if (std::strcmp(name, "sweep_dbg") == 0) { h->sweep_dbg = static_cast<int>(value); return PLX_OK; }
   return fail(h, PLX_ERR_INVALID, std::string("unknown option or value: ") + name);
 }
 
@@ -337,6 +339,10 @@ extern "C" int plx_gp_set_theta(plx_bo_handle h, double theta) {
   if ((r = ensure(h, h->dZ, h->z_cap, mat)) != PLX_OK) return r;
   if ((r = ensure(h, h->d_alpha_state, h->as_cap, static_cast<size_t>(h->npad))) != PLX_OK) return r;
   if ((r = ensure(h, h->dKs, h->ks_cap, static_cast<size_t>(h->num_sms) * 128 * h->npad)) != PLX_OK) return r;
+  if ((r = ensure(h, h->dXt, h->xt_cap, static_cast<size_t>(h->d) * h->npad)) != PLX_OK) return r;
+  scale_transpose_x_kernel<<<dim3((h->npad + 255) / 256, h->d), 256, 0, h->stream>>>(h->dX, h->n, h->d, h->npad,
+                                                                                   std::exp(theta), h->dXt);
+  LAUNCH_CHECK("scale_transpose_x_kernel");
   transpose_kernel<<<dim3(h->npad / 32, h->npad / 32), 256, 0, h->stream>>>(h->bp.U, h->dZ, h->npad);
   LAUNCH_CHECK("transpose_kernel");
   CK(cudaMemcpyAsync(h->d_alpha_state, h->d_alpha, sizeof(double) * h->npad, cudaMemcpyDeviceToDevice, h->stream));
@@ -409,10 +415,10 @@ static void fill_params(plx_bo* h, SweepParams& p, const double* Xc_dev, long lo
                         double kappa, double eps, double y_max) {
   p.Xc = Xc_dev; p.N = N; p.idx_base = idx_base;
   p.d = h->d; p.n = h->n; p.npad = h->npad; p.n16 = (h->n + 15) / 16 * 16;
-  p.X = h->dX; p.alpha = h->d_alpha_state; p.Z = h->dZ; p.ell = std::exp(h->theta);
+  p.X = h->dX; p.Xt = h->dXt; p.alpha = h->d_alpha_state; p.Z = h->dZ; p.ell = std::exp(h->theta);
   p.kind = h->kind; p.acq = acq; p.kappa = kappa; p.eps = eps; p.y_max = y_max;
   p.Ks = h->dKs; p.out_mean = p.out_std = p.out_acq = nullptr;
-  p.blk_val = h->d_blk_val; p.blk_idx = h->d_blk_idx;
+  p.blk_val = h->d_blk_val; p.blk_idx = h->d_blk_idx; p.dbg = h->sweep_dbg;
 }
 
 static int launch_sweep(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cudaEvent_t e1) {
@@ -780,10 +786,10 @@ extern "C" int plx_acq_sweep_noalloc(int device, void* stream, const double* Xc_
   SweepParams p;
   p.Xc = Xc_dev; p.N = N; p.idx_base = idx_base;
   p.d = d; p.n = n; p.npad = npad; p.n16 = (n + 15) / 16 * 16;
-  p.X = X_dev; p.alpha = alpha_dev; p.Z = Zpad; p.ell = std::exp(theta);
+  p.X = X_dev; p.Xt = nullptr; p.alpha = alpha_dev; p.Z = Zpad; p.ell = std::exp(theta);
   p.kind = kind; p.acq = acq; p.kappa = kappa; p.eps = eps; p.y_max = y_max;
   p.Ks = Ks; p.out_mean = p.out_std = p.out_acq = nullptr;
-  p.blk_val = blk_val; p.blk_idx = blk_idx;
+  p.blk_val = blk_val; p.blk_idx = blk_idx; p.dbg = 0;
   const long long ntiles = (N + 127) / 128;
   const int grid = static_cast<int>(std::min<long long>(ntiles, NOALLOC_GRID));
   sweep_simple_kernel<<<grid, 256, SWEEP_SIMPLE_SMEM, st>>>(p);

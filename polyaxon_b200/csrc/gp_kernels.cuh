@@ -31,6 +31,16 @@ __device__ __forceinline__ double kern_value(int kind, double r2) {
   return (1.0 + t + t * t / 3.0) * exp(-t);
 }
 
+template <int KIND>
+__device__ __forceinline__ double kern_value_t(double r2) {
+  if (KIND == K_RBF) return exp(-0.5 * r2);
+  const double r = sqrt(r2);
+  if (KIND == K_M05) return exp(-r);
+  if (KIND == K_M15) { const double t = r * 1.7320508075688772; return (1.0 + t) * exp(-t); }
+  const double t = r * 2.23606797749979;
+  return (1.0 + t + t * t / 3.0) * exp(-t);
+}
+
 // dK/dtheta for theta = log(length_scale) as sklearn forms it (kernels.py:1575, :1752-1773)
 __device__ __forceinline__ double kern_dtheta(int kind, double r2) {
   if (kind == K_RBF) return exp(-0.5 * r2) * r2;

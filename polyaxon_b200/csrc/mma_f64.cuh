@@ -38,6 +38,15 @@ __device__ __forceinline__ double2 lds128(uint32_t addr) {
   return v;
 }
 
+__device__ __forceinline__ double lds64(uint32_t addr) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1];\n" : "=d"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts64(uint32_t addr, double v) {
+  asm volatile("st.shared.f64 [%0], %1;\n" :: "r"(addr), "d"(v));
+}
+
 // coherent 16-byte global load (never the non-coherent path: several kernels re-read scratch that
 // the same CTA wrote earlier in the launch)
 __device__ __forceinline__ double2 ldg128(const double* p) {

@@ -30,6 +30,7 @@ struct SweepParams {
   long long idx_base;      // global index of candidate 0 of this launch
   int d, n, npad, n16;     // observations, padded to 128, padded to 16
   const double* X;         // observations [n][d]
+  const double* Xt;        // X / length_scale transposed to [d][npad] (TMA-ring kernel only)
   const double* alpha;     // [npad]
   const double* Z;         // L^-1, row-major [npad][npad]
   double ell;              // length scale
@@ -38,6 +39,7 @@ struct SweepParams {
   double* Ks;              // scratch [gridDim.x * 128][npad]
   double* out_mean; double* out_std; double* out_acq;   // optional per-candidate dumps [N]
   double* blk_val; long long* blk_idx;                  // per-CTA best
+  int dbg;                 // profiling only: bit 0 = build K* for the first tile only, bit 1 = skip the DMMA work
 };
 
 struct Best { double v; long long i; };
@@ -240,6 +242,159 @@ __device__ __forceinline__ int tri_skip(int j0, int ib, int wn) {
 }
 
 // ------------------------------------------------------------------------------------------
+// Phase A for the TMA-ring kernel.  Same arithmetic as phase_a, organised so that the code stays
+// small (the straight-line version is ~11k instructions and thrashes the instruction cache):
+//   1. distances: thread (tx = tid & 15, ty = tid >> 4) accumulates r^2 for 8 candidates x 4
+//      observations of a 64-observation block from shared tiles (observations come pre-scaled and
+//      transposed, Xt[q][j], the next block is prefetched into registers meanwhile) and parks the 32
+//      values in a shared tile R2s[128][65];
+//   2. kernel values: warp w walks candidates 16w .. 16w+15 in a compact loop, lane = observation
+//      (two per lane): k(r^2), coalesced store into the K* slab, and the posterior-mean partial into
+//      the thread's own slot of Macc[128][32] (deterministic, no atomics).
+// Shared staging (aliases the pipeline stages): Cs[32][130] | Xs[32][65] | R2s[128][65] | Macc[128][32].
+// ------------------------------------------------------------------------------------------
+constexpr int R2_LD = 65;
+constexpr int PA_CS = 0, PA_XS = 32 * CS_LD, PA_R2 = PA_XS + 32 * XS_LD, PA_MACC = PA_R2 + 128 * R2_LD;
+constexpr int PA_DOUBLES = PA_MACC + 128 * 32;
+static_assert(PA_DOUBLES * 8 <= 5 * 2 * TILE_BYTES, "phase A staging must fit in the pipeline stages");
+
+template <int KIND>
+__device__ __forceinline__ void kern_rows(const SweepParams& p, uint32_t sm, double* Kslab, int jb, int warp, int lane) {
+  const int j0 = jb * 64 + lane, j1 = j0 + 32;
+  const bool real0 = j0 < p.n, real1 = j1 < p.n;
+  const double a0 = real0 ? p.alpha[j0] : 0.0, a1 = real1 ? p.alpha[j1] : 0.0;
+  const bool st0 = j0 < p.n16, st1 = j1 < p.n16;
+#pragma unroll 4
+  for (int ci = 0; ci < 16; ++ci) {
+    const int c = warp * 16 + ci;
+    const uint32_t r2a = sm + static_cast<uint32_t>((PA_R2 + c * R2_LD + lane) * 8);
+    const double k0 = real0 ? kern_value_t<KIND>(lds64(r2a)) : 0.0;
+    const double k1 = real1 ? kern_value_t<KIND>(lds64(r2a + 32 * 8)) : 0.0;
+    double* row = Kslab + static_cast<size_t>(c) * p.npad;
+    if (st0) row[j0] = k0;
+    if (st1) row[j1] = k1;
+    const uint32_t ma = sm + static_cast<uint32_t>((PA_MACC + c * 32 + lane) * 8);
+    sts64(ma, lds64(ma) + (k0 * a0 + k1 * a1));
+  }
+}
+
+__device__ __forceinline__ void phase_a3(const SweepParams& p, long long tile, double* Kslab, uint32_t sm,
+                                         double* mean_s, int tid) {
+  const int tx = tid & 15, ty = tid >> 4, warp = tid >> 5, lane = tid & 31;
+  const long long c_base = tile * 128;
+  const int nchunk_d = (p.d + 31) / 32;
+  const int nblk = (p.n16 + 63) / 64;
+
+  for (int e = tid; e < 128 * 32; e += 256) sts64(sm + static_cast<uint32_t>((PA_MACC + e) * 8), 0.0);
+
+  double pre[8];                      // element e = tid + 256 r of a 32 x 64 block: q = e >> 6, j = e & 63
+  auto fetch = [&](int jb, int dc) {
+    const int d0 = dc * 32, dn = min(32, p.d - d0);
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      const int e = tid + 256 * r, q = e >> 6, j = e & 63;
+      pre[r] = (q < dn) ? p.Xt[static_cast<size_t>(d0 + q) * p.npad + jb * 64 + j] : 0.0;
+    }
+  };
+
+  fetch(0, 0);
+  for (int jb = 0; jb < nblk; ++jb) {
+    double r2[8][4];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) r2[i][j] = 0.0;
+    for (int dc = 0; dc < nchunk_d; ++dc) {
+      const int d0 = dc * 32, dn = min(32, p.d - d0);
+      if (dc > 0) named_bar_sync(1, 256);                   // readers of the previous dimension chunk are done
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {
+        const int e = tid + 256 * r;
+        sts64(sm + static_cast<uint32_t>((PA_XS + (e >> 6) * XS_LD + (e & 63)) * 8), pre[r]);
+      }
+      if (jb == 0 || nchunk_d > 1) {
+        for (int e = tid; e < 128 * 32; e += 256) {
+          const int c = e >> 5, q = e & 31;
+          double v = 0.0;
+          if (q < dn && c_base + c < p.N) v = p.Xc[(c_base + c) * p.d + d0 + q] / p.ell;
+          sts64(sm + static_cast<uint32_t>((PA_CS + q * CS_LD + c) * 8), v);
+        }
+      }
+      named_bar_sync(1, 256);
+      {                                                       // prefetch the next (jb, dc)
+        int njb = jb, ndc = dc + 1;
+        if (ndc == nchunk_d) { ndc = 0; ++njb; }
+        if (njb < nblk) fetch(njb, ndc);
+      }
+      const uint32_t cs = sm + static_cast<uint32_t>((PA_CS + ty * 8) * 8);
+      const uint32_t xs = sm + static_cast<uint32_t>((PA_XS + tx) * 8);
+#pragma unroll 2
+      for (int q = 0; q < dn; ++q) {
+        double cv[8], xv[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { const double2 t2 = lds128(cs + (q * CS_LD + 2 * i) * 8); cv[2 * i] = t2.x; cv[2 * i + 1] = t2.y; }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) xv[j] = lds64(xs + (q * XS_LD + 16 * j) * 8);
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) { const double df = cv[i] - xv[j]; r2[i][j] += df * df; }
+      }
+    }
+    // park r^2 (previous block's readers passed the barrier above before anyone got here)
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        sts64(sm + static_cast<uint32_t>((PA_R2 + (ty * 8 + i) * R2_LD + tx + 16 * j) * 8), r2[i][j]);
+    named_bar_sync(1, 256);
+    switch (p.kind) {
+      case K_RBF: kern_rows<K_RBF>(p, sm, Kslab, jb, warp, lane); break;
+      case K_M05: kern_rows<K_M05>(p, sm, Kslab, jb, warp, lane); break;
+      case K_M15: kern_rows<K_M15>(p, sm, Kslab, jb, warp, lane); break;
+      default: kern_rows<K_M25>(p, sm, Kslab, jb, warp, lane); break;
+    }
+    // no barrier here: the next block re-writes Xs (free since the barrier above) and parks into R2s only
+    // after its own barrier, which every thread reaches after finishing this kern_rows
+  }
+  named_bar_sync(1, 256);
+  if (tid < 128) {
+    double m = 0.0;
+    for (int l = 0; l < 32; ++l) m += lds64(sm + static_cast<uint32_t>((PA_MACC + tid * 32 + l) * 8));
+    mean_s[tid] = m;
+  }
+}
+
+// mma_chunk with the next B fragment in flight while the current one feeds the tensor pipe
+__device__ __forceinline__ void mma_chunk_pf(WarpAcc& acc, uint32_t sA, uint32_t sB, int warp, int lane, int nf_begin) {
+  const int g = lane >> 2, t = lane & 3;
+  const int wm = (warp & 3) * 32, wn = (warp >> 2) * 64;
+  const uint32_t rowA = sA + static_cast<uint32_t>((wm + g) * 128);
+  const uint32_t rowB = sB + static_cast<uint32_t>((wn + g) * 128);
+  const uint32_t c0 = static_cast<uint32_t>(((2 * t) ^ g) << 4), c1 = c0 ^ 16u;
+  double2 a0[4], a1[4];
+#pragma unroll
+  for (int mf = 0; mf < 4; ++mf) { a0[mf] = lds128(rowA + mf * 1024 + c0); a1[mf] = lds128(rowA + mf * 1024 + c1); }
+  const int first = nf_begin < 8 ? nf_begin : 7;
+  double2 b0 = lds128(rowB + first * 1024 + c0), b1 = lds128(rowB + first * 1024 + c1);
+#pragma unroll
+  for (int nf = 0; nf < 8; ++nf) {
+    if (nf < nf_begin) continue;
+    double2 n0 = b0, n1 = b1;
+    if (nf + 1 < 8) { n0 = lds128(rowB + (nf + 1) * 1024 + c0); n1 = lds128(rowB + (nf + 1) * 1024 + c1); }
+#pragma unroll
+    for (int mf = 0; mf < 4; ++mf) dmma(acc.c[mf][nf][0], acc.c[mf][nf][1], a0[mf].x, b0.x);
+#pragma unroll
+    for (int mf = 0; mf < 4; ++mf) dmma(acc.c[mf][nf][0], acc.c[mf][nf][1], a0[mf].y, b0.y);
+#pragma unroll
+    for (int mf = 0; mf < 4; ++mf) dmma(acc.c[mf][nf][0], acc.c[mf][nf][1], a1[mf].x, b1.x);
+#pragma unroll
+    for (int mf = 0; mf < 4; ++mf) dmma(acc.c[mf][nf][0], acc.c[mf][nf][1], a1[mf].y, b1.y);
+    b0 = n0; b1 = n1;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // Variant 1: TMA + mbarrier ring.  384 threads: warps 0-7 (two warpgroups) compute with 232
 // registers each, warps 8-11 form the producer warpgroup (40 registers; one elected lane issues
 // every TMA load).  No CTA-wide barrier inside the tile loop: the roles meet only through
@@ -308,7 +463,7 @@ __global__ void __launch_bounds__(384, 1) sweep_tma_kernel(const __grid_constant
   const int wn = (warp >> 2) * 64;
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     // every TMA load of the previous tile has been waited for, so the stage memory is free
-    phase_a(p, tile, Kslab, reinterpret_cast<double*>(smem), tail->mean_s, tid);
+    if (!(p.dbg & 1) || tile == blockIdx.x) phase_a3(p, tile, Kslab, s0, tail->mean_s, tid);
     __threadfence();
     asm volatile("fence.proxy.async;\n" ::: "memory");     // generic-proxy stores -> visible to TMA
     __syncwarp();
@@ -323,7 +478,7 @@ __global__ void __launch_bounds__(384, 1) sweep_tma_kernel(const __grid_constant
         const uint32_t s = it % SWEEP_STAGES, ph = (it / SWEEP_STAGES) & 1;
         mbar_wait(bar0 + 8 * s, ph);
         const int skip = tri_skip(j0, ib, wn);
-        if (skip < 8) mma_chunk(acc, s0 + s * 2 * TILE_BYTES, s0 + s * 2 * TILE_BYTES + TILE_BYTES, warp, lane, skip);
+        if (skip < 8 && !(p.dbg & 2)) mma_chunk_pf(acc, s0 + s * 2 * TILE_BYTES, s0 + s * 2 * TILE_BYTES + TILE_BYTES, warp, lane, skip);
         __syncwarp();
         if (lane == 0) mbar_arrive(bar0 + 8 * (SWEEP_STAGES + s));
       }
@@ -371,6 +526,14 @@ __global__ void __launch_bounds__(256, 1) sweep_simple_kernel(const SweepParams 
     __syncthreads();
   }
   block_best(p, best, tail->sval, tail->sidx, tid);
+}
+
+// X / length_scale, transposed to [d][npad] (zero in the padding), for the builders' coalesced reads
+__global__ void scale_transpose_x_kernel(const double* __restrict__ X, int n, int d, int npad, double ell,
+                                         double* __restrict__ Xt) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x, q = blockIdx.y;
+  if (j >= npad) return;
+  Xt[static_cast<size_t>(q) * npad + j] = (j < n) ? X[static_cast<size_t>(j) * d + q] / ell : 0.0;
 }
 
 // Merge the per-CTA bests into the running best of the whole sweep (one thread; grid <= #SMs).

@@ -30,7 +30,7 @@ print(' mean err', np.abs(mean[:4096] - m).max(), ' var err', np.abs(std[:4096] 
 lml, grad = h.lml([0.3, 0.8])
 print(' lml', lml, grad, [G.log_marginal_likelihood(X, y, t, G.KERNEL_MATERN, 1.5) for t in (0.3, 0.8)])
 '''
-for impl, n, d in [(0, 100, 5), (1, 100, 5), (0, 600, 32), (1, 600, 32), (1, 2048, 32)]:
+for impl, n, d in [(0, 100, 5), (1, 100, 5), (1, 600, 32), (1, 2048, 32), (1, 300, 70)]:
     try:
         r = subprocess.run([sys.executable, '-c', CODE, str(impl), str(n), str(d)], timeout=120,
                            stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
