@@ -92,6 +92,15 @@ int plx_acq_sweep_dev(plx_bo_handle h, const double* Xc_dev, long long N, long l
                       double kappa, double eps, double y_max, double* best_value, long long* best_index,
                       double* best_x);
 
+/* Resident candidates.  A seeded experiment group re-creates RandomState(seed) on every call
+ * (manager.py:30, acquisition_function.py:27), so `x_tries` (acquisition_function.py:88-89) is the
+ * same matrix on every BO iteration; plx_candidates_set keeps one N x d copy in device memory and
+ * plx_acq_sweep_resident sweeps it without drawing or copying it again.  The host layer decides when
+ * the copy is still valid (same generator state, bounds and sizes). */
+int plx_candidates_set(plx_bo_handle h, const double* Xc, long long N, int d);
+int plx_acq_sweep_resident(plx_bo_handle h, long long idx_base, int acq, double kappa, double eps, double y_max,
+                           double* best_value, long long* best_index, double* best_x);
+
 /* Device time in milliseconds of the main sweep kernel(s) of the last plx_acq_sweep* call, measured
  * with CUDA events on the launching stream, and how many kernels that call launched. */
 int plx_last_sweep_stats(plx_bo_handle h, double* kernel_ms, long long* launches);

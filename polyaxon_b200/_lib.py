@@ -36,6 +36,9 @@ SIGNATURES = {
                               _dp, POINTER(c_longlong), c_void_p, c_void_p, c_void_p, c_void_p]),
     'plx_acq_sweep_dev': (c_int, [c_void_p, c_void_p, c_longlong, c_longlong, c_int, c_double, c_double,
                                   c_double, _dp, POINTER(c_longlong), c_void_p]),
+    'plx_candidates_set': (c_int, [c_void_p, c_void_p, c_longlong, c_int]),
+    'plx_acq_sweep_resident': (c_int, [c_void_p, c_longlong, c_int, c_double, c_double, c_double, _dp,
+                                       POINTER(c_longlong), c_void_p]),
     'plx_last_sweep_stats': (c_int, [c_void_p, _dp, POINTER(c_longlong)]),
     'plx_launch_count': (c_longlong, [c_void_p]),
     'plx_acq_refine': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_double, c_double, c_double, c_int,
@@ -97,6 +100,7 @@ class Handle(object):
             raise PlxError(rc, msg)
         self.device = int(device)
         self.n = self.d = 0
+        self.resident_key = None
 
     def close(self):
         if getattr(self, '_h', None):
@@ -204,6 +208,20 @@ class Handle(object):
         self._check(self.lib.plx_acq_value_grad(self._h, _ptr(pts), pts.shape[0], int(acq), float(kappa),
                                                 float(eps), float(y_max), _ptr(vals), _ptr(grads)))
         return vals, grads
+
+    def candidates_set(self, Xc, key=None):
+        """Keep a device-resident copy of the candidate matrix; `key` is remembered for the caller."""
+        Xc = _f64(Xc)
+        self.resident_key = None
+        self._check(self.lib.plx_candidates_set(self._h, _ptr(Xc), Xc.shape[0], Xc.shape[1]))
+        self.resident_key = key
+
+    def sweep_resident(self, acq, y_max, kappa=0.0, eps=0.0, idx_base=0):
+        bv, bi = c_double(), c_longlong()
+        bx = np.empty(self.d)
+        self._check(self.lib.plx_acq_sweep_resident(self._h, int(idx_base), int(acq), float(kappa), float(eps),
+                                                    float(y_max), ctypes.byref(bv), ctypes.byref(bi), _ptr(bx)))
+        return bv.value, bi.value, bx
 
     def last_sweep_stats(self):
         ms, nl = c_double(), c_longlong()

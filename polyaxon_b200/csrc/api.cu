@@ -59,6 +59,9 @@ struct plx_bo {
   int sweep_impl = 1, sweep_dbg = 0;
   double last_ms = 0.0; long long last_launches = 0;
 
+  // resident candidate matrix (iteration-invariant for a seeded group)
+  double* d_resident = nullptr; size_t resident_cap = 0; long long resident_n = 0; int resident_d = 0;
+
   // refinement workspace
   int rf_cap_s = 0, rf_cap_npad = 0, rf_cap_d = 0;
   double *rf_kv = nullptr, *rf_kp = nullptr, *rf_v = nullptr, *rf_w = nullptr, *rf_vec = nullptr,
@@ -174,7 +177,7 @@ extern "C" void plx_bo_destroy(plx_bo_handle h) {
                   h->d_alpha, h->d_partial, h->d_lml, h->d_grad, h->d_info, h->dZ, h->d_alpha_state, h->dKs, h->dXt,
                   h->d_blk_val, h->d_blk_idx, h->d_best_val, h->d_best_idx, h->dcand[0], h->dcand[1],
                   h->d_out[0], h->d_out[1], h->d_out[2], h->rf_kv, h->rf_kp, h->rf_v, h->rf_w, h->rf_vec,
-                  h->rf_bounds, h->rf_val, h->rf_grad, h->rf_sc, h->rf_active};
+                  h->rf_bounds, h->rf_val, h->rf_grad, h->rf_sc, h->rf_active, h->d_resident};
   for (void* p : ptrs) if (p) cudaFree(p);
   for (int i = 0; i < 2; ++i) { if (h->ev_copy[i]) cudaEventDestroy(h->ev_copy[i]); if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]); }
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
@@ -545,6 +548,26 @@ extern "C" int plx_acq_sweep(plx_bo_handle h, const double* Xc, long long N, lon
   h->last_ms = total; h->last_launches = h->launches - l0;
   if (best_x) std::memcpy(best_x, Xc + (*best_index - idx_base) * d, sizeof(double) * d);
   return PLX_OK;
+}
+
+extern "C" int plx_candidates_set(plx_bo_handle h, const double* Xc, long long N, int d) {
+  if (!h || N < 0 || d <= 0 || (N > 0 && !Xc)) return h ? fail(h, PLX_ERR_INVALID, "candidates_set: bad arguments") : PLX_ERR_INVALID;
+  CK(cudaSetDevice(h->device));
+  h->resident_n = 0;
+  int r;
+  if ((r = ensure(h, h->d_resident, h->resident_cap, static_cast<size_t>(std::max<long long>(N, 1)) * d)) != PLX_OK) return r;
+  if (N > 0) CK(cudaMemcpyAsync(h->d_resident, Xc, sizeof(double) * N * d, cudaMemcpyHostToDevice, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  h->resident_n = N; h->resident_d = d;
+  return PLX_OK;
+}
+
+extern "C" int plx_acq_sweep_resident(plx_bo_handle h, long long idx_base, int acq, double kappa, double eps,
+                                      double y_max, double* best_value, long long* best_index, double* best_x) {
+  if (!h) return PLX_ERR_INVALID;
+  if (h->resident_d != h->d || (h->resident_n > 0 && !h->d_resident))
+    return fail(h, PLX_ERR_STATE, "acq_sweep_resident: no resident candidates of this dimension (call plx_candidates_set)");
+  return plx_acq_sweep_dev(h, h->d_resident, h->resident_n, idx_base, acq, kappa, eps, y_max, best_value, best_index, best_x);
 }
 
 extern "C" int plx_last_sweep_stats(plx_bo_handle h, double* kernel_ms, long long* launches) {

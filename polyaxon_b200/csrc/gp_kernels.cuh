@@ -169,6 +169,7 @@ __global__ void __launch_bounds__(256) potf2_inv_kernel(BatchPtrs bp, int k, int
   }
   __shared__ int bad;
   if (tid == 0) bad = 0;
+  const int lane = tid & 31, warp = tid >> 5;
   for (int j = 0; j < 128; ++j) {
     __syncthreads();                    // trailing update of column j-1 is complete
     double ajj = S[j * POTF_LD + j];    // stays untouched during this step (dl holds the root)
@@ -177,8 +178,9 @@ __global__ void __launch_bounds__(256) potf2_inv_kernel(BatchPtrs bp, int k, int
       ajj = 1.0;
     }
     const double ljj = sqrt(ajj);
-    if (tid == 0) dl[j] = ljj;
-    for (int i = j + 1 + tid; i < 128; i += 256) S[i * POTF_LD + j] /= ljj;
+    const double inv = 1.0 / ljj;       // LAPACK dpotf2 scales the column by the reciprocal too
+    if (tid == 0) { dl[j] = ljj; wdiag[j] = inv; }
+    for (int i = j + 1 + tid; i < 128; i += 256) S[i * POTF_LD + j] *= inv;
     __syncthreads();
     // trailing update of the lower triangle: S[i][c] -= S[i][j] * S[c][j], j < c <= i
     for (int i = j + 1 + (tid >> 4); i < 128; i += 16) {
@@ -187,17 +189,26 @@ __global__ void __launch_bounds__(256) potf2_inv_kernel(BatchPtrs bp, int k, int
     }
   }
   __syncthreads();
+  // W = L^-1 by forward substitution on all columns of the identity at once (right-looking):
+  // W[i][c] (i > c) lives in the strict upper triangle at S[c][i], its diagonal in wdiag.
+  for (int e = tid; e < 128 * 128; e += 256) {
+    const int r = e >> 7, c = e & 127;
+    if (c > r) S[r * POTF_LD + c] = 0.0;
+  }
   if (tid < 128) S[tid * POTF_LD + tid] = dl[tid];
-  __syncthreads();
-  // inverse: thread c owns column c of W; W[i][c] (i > c) kept in the strict upper triangle S[c][i]
-  if (tid < 128) {
-    const int c = tid;
-    const double wcc = 1.0 / S[c * POTF_LD + c];
-    wdiag[c] = wcc;
-    for (int i = c + 1; i < 128; ++i) {
-      double s = S[i * POTF_LD + c] * wcc;
-      for (int m = c + 1; m < i; ++m) s += S[i * POTF_LD + m] * S[c * POTF_LD + m];
-      S[c * POTF_LD + i] = -s / S[i * POTF_LD + i];
+  for (int j = 0; j < 128; ++j) {
+    __syncthreads();
+    const double wjj = wdiag[j];
+    // row j of W becomes final: W[j][c] = acc / L[j][j]
+    for (int c = tid; c < j; c += 256) S[c * POTF_LD + j] *= wjj;
+    __syncthreads();
+    // rows below: W[i][c] -= L[i][j] * W[j][c] for c <= j  (lane <-> i, warp <-> c)
+    for (int i = j + 1 + lane; i < 128; i += 32) {
+      const double lij = S[i * POTF_LD + j];
+      for (int c = warp; c <= j; c += 8) {
+        const double wjc = (c == j) ? wjj : S[c * POTF_LD + j];
+        S[c * POTF_LD + i] -= lij * wjc;
+      }
     }
   }
   __syncthreads();

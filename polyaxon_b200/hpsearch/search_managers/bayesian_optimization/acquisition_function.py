@@ -17,6 +17,9 @@ Random numbers are drawn on the host from the reference's own ``RandomState`` in
 order (restart thetas during fit -> x_tries -> x_seeds), so a seeded group sees bit-identical
 candidate matrices.
 """
+import hashlib
+import os
+
 import numpy as np
 
 from polyaxon_b200 import _lib, device
@@ -29,6 +32,7 @@ from polyaxon_b200.schemas.hptuning import (
 )
 
 THETA_BOUNDS = (float(np.log(1e-5)), float(np.log(1e5)))      # sklearn's default length_scale_bounds
+_SEED_CACHE = {}          # key -> (x_seeds, generator state after the draws); see UtilityFunction._warmup
 
 
 def _acq_id(name):
@@ -125,6 +129,38 @@ class UtilityFunction(object):
         return acq, dict(y_max=float(y_max if y_max is not None else 0.0),
                          kappa=float(self.kappa or 0.0), eps=float(self.eps or 0.0))
 
+    def _warmup(self, h, acq, args, bounds, n_warmup, n_iter):
+        """Sampling stage.  The draws depend only on the generator state on entry, the bounds and
+        the two counts; a seeded group re-creates the same state on every call (manager.py:30), so
+        the candidate matrix of the previous call is still in device memory and neither the
+        numpy draw nor the host->device copy is repeated.  On a hit the generator is moved to the
+        state it would have reached, so everything downstream sees the reference's stream."""
+        rng = self.random_generator
+        d = bounds.shape[0]
+        key = None
+        if os.environ.get('PLX_BO_CANDIDATE_CACHE', '1') != '0' and hasattr(rng, 'get_state'):
+            state = rng.get_state()
+            digest = hashlib.sha1(state[1].tobytes())
+            digest.update(repr((state[0], state[2], state[3], state[4], n_warmup, n_iter)).encode())
+            digest.update(bounds.tobytes())
+            key = digest.hexdigest()
+        cached = _SEED_CACHE.get(key) if key is not None else None
+        if cached is not None and h.resident_key == key:
+            x_seeds, state_after = cached
+            rng.set_state(state_after)
+            max_acq, _, x_max = h.sweep_resident(acq, **args)
+            return max_acq, x_max, x_seeds.copy()
+        x_tries = rng.uniform(bounds[:, 0], bounds[:, 1], size=(n_warmup, d))
+        x_seeds = rng.uniform(bounds[:, 0], bounds[:, 1], size=(n_iter, d))
+        if key is None:
+            max_acq, _, x_max = h.sweep(x_tries, acq, **args)
+            return max_acq, x_max, x_seeds
+        h.candidates_set(x_tries, key=key)
+        _SEED_CACHE.clear()                      # one resident matrix per process
+        _SEED_CACHE[key] = (x_seeds.copy(), rng.get_state())
+        max_acq, _, x_max = h.sweep_resident(acq, **args)
+        return max_acq, x_max, x_seeds
+
     def compute(self, x, y_max):
         """Acquisition values of the rows of x (acquisition_function.py:62-68)."""
         acq, args = self._acq_args(y_max)
@@ -139,11 +175,7 @@ class UtilityFunction(object):
         acq, args = self._acq_args(y_max)
         bounds = np.asarray(bounds, dtype=np.float64)
         h = self.gaussian_process.handle
-        x_tries = self.random_generator.uniform(bounds[:, 0], bounds[:, 1],
-                                                size=(n_warmup, bounds.shape[0]))
-        max_acq, _, x_max = h.sweep(x_tries, acq, **args)
-        x_seeds = self.random_generator.uniform(bounds[:, 0], bounds[:, 1],
-                                                size=(n_iter, bounds.shape[0]))
+        max_acq, x_max, x_seeds = self._warmup(h, acq, args, bounds, n_warmup, n_iter)
         if n_iter > 0:
             xs, values, success = h.refine(x_seeds, bounds, acq, **args)
             for x_ref, value, ok in zip(xs, values, success):

@@ -115,3 +115,43 @@ def test_reference_fixture_sets_run_and_stay_in_bounds():
     assert suggestion['dropout'] in [0.25, 0.3]
     assert suggestion['activation'] in ['relu', 'sigmoid']
     assert optimizer.utility_function.gaussian_process.theta_ == pytest.approx(float(g['theta']), abs=1e-6)
+
+
+def test_resident_candidate_cache_is_transparent(monkeypatch):
+    """Second call of a seeded group reuses the device-resident candidate matrix: same suggestion,
+    same generator state afterwards, as with the cache switched off."""
+    from polyaxon_b200 import device
+    from polyaxon_b200.hpsearch.search_managers.bayesian_optimization import acquisition_function as af
+    from polyaxon_b200.hpsearch.search_managers.bayesian_optimization.optimizer import BOOptimizer
+    g = load_golden('c5_d16_n128_m25_ei')
+    d = g['X'].shape[1]
+    keys = ['x%03d' % i for i in range(d)]
+    cfg = _config(g, {k: {'uniform': [0, 1]} for k in keys})
+    configs = [dict(zip(keys, row.tolist())) for row in g['X']]
+
+    def run():
+        opt = BOOptimizer(hptuning_config=cfg)
+        opt.add_observations(configs=configs, metrics=g['y'].tolist())
+        s = opt.get_suggestion()
+        return s, opt.utility_function.random_generator.get_state()[1].copy()
+
+    af._SEED_CACHE.clear()
+    device.get_handle().resident_key = None
+    first, state1 = run()
+    key = device.get_handle().resident_key
+    assert key is not None and key in af._SEED_CACHE
+    uploads = {'n': 0}
+    from polyaxon_b200 import _lib
+    real_set = _lib.Handle.candidates_set
+
+    def counting_set(self, *a, **k):
+        uploads['n'] += 1
+        return real_set(self, *a, **k)
+    monkeypatch.setattr(_lib.Handle, 'candidates_set', counting_set)
+    second, state2 = run()
+    assert uploads['n'] == 0                           # neither drawn nor copied again
+    assert device.get_handle().resident_key == key
+    monkeypatch.setenv('PLX_BO_CANDIDATE_CACHE', '0')
+    third, state3 = run()
+    assert first == second == third
+    assert np.array_equal(state1, state2) and np.array_equal(state1, state3)
