@@ -279,7 +279,16 @@ def main():
              hp_config(standin, 4, 'matern', 1.5, 'ucb', 2.576, None, 0, 4096, 10, 5, matrix=m10,
                        optimization='minimize'),
              c10, REF10_Y, thetas, 1024)
-    # the same two sets with the fixture's general nu=1.9 (Bessel K_nu): oracle-only for now
+    # general nu = 1.9 (the value in every reference fixture) on well-conditioned synthetic data
+    c, m = synthetic_configs(15, 2)
+    run_case('c1_d2_n15_m19_ucb', standin, opt_mod,
+             hp_config(standin, 2, 'matern', 1.9, 'ucb', 2.576, None, 0, 8192, 4, 7),
+             c, m, thetas, 1024)
+    c, m = synthetic_configs(128, 16, seed=1240)
+    run_case('c5_d16_n128_m19_ei', standin, opt_mod,
+             hp_config(standin, 16, 'matern', 1.9, 'ei', None, 0.01, 1, 2048, 2, 23),
+             c, m, thetas, 512)
+    # the reference's own two observation sets with the fixture's nu=1.9
     run_case('ref14_m19_ucb', standin, opt_mod,
              hp_config(standin, 3, 'matern', 1.9, 'ucb', 1.2, None, 0, 2048, 5, 3, matrix=m3,
                        optimization='minimize'),

@@ -28,6 +28,7 @@ struct plx_bo {
   // observations
   bool have_data = false;
   int n = 0, d = 0, npad = 0, nb = 0, kind = 0;
+  MaternGen mg{};
   double jitter = 1e-10;
   double* dX = nullptr; size_t x_cap = 0;
   double* dy = nullptr; size_t y_cap = 0;
@@ -109,8 +110,32 @@ static int kernel_kind(int kernel, double nu, int* kind) {
   else if (nu == 1.5) *kind = K_M15;
   else if (nu == 2.5) *kind = K_M25;
   else if (std::isinf(nu) && nu > 0) *kind = K_RBF;
+  else if (nu > 0.0 && nu <= 50.0) *kind = K_GEN;
   else return PLX_ERR_UNSUPPORTED;
   return PLX_OK;
+}
+
+// nu-dependent constants of the general Matern kernel (Temme's Gamma_1 / Gamma_2 etc.)
+static MaternGen make_matern_gen(double nu) {
+  MaternGen m{};
+  m.nu = nu;
+  m.nl = static_cast<int>(nu + 0.5);
+  m.mu = (m.nl == 0) ? -nu : nu - m.nl;
+  m.coef = std::pow(2.0, 1.0 - nu) / std::tgamma(nu);
+  m.s = std::sqrt(2.0 * nu);
+  const long double mu = m.mu;
+  const long double gampl = 1.0L / std::tgamma(1.0L + mu), gammi = 1.0L / std::tgamma(1.0L - mu);
+  m.gampl = static_cast<double>(gampl);
+  m.gammi = static_cast<double>(gammi);
+  m.gam2 = static_cast<double>((gammi + gampl) / 2.0L);
+  if (std::fabs(m.mu) < 1e-3) {
+    // 1/Gamma(1+z) = 1 + g z + c3 z^2 + c4 z^3 + c5 z^4 + c6 z^5 ...; Gamma_1 is minus its odd part over z
+    const double g = 0.5772156649015329, c4 = -0.0420026350340952, c6 = -0.0421977345555443;
+    m.gam1 = -(g + c4 * m.mu * m.mu + c6 * m.mu * m.mu * m.mu * m.mu);
+  } else {
+    m.gam1 = static_cast<double>((gammi - gampl) / (2.0L * mu));
+  }
+  return m;
 }
 
 extern "C" const char* plx_version(void) { return "plxbo 0.1 (sm_100a)"; }
@@ -207,11 +232,13 @@ extern "C" int plx_gp_set_data(plx_bo_handle h, const double* X, const double* y
   int kind;
   const int rc = kernel_kind(kernel, nu, &kind);
   if (rc == PLX_ERR_UNSUPPORTED)
-    return fail(h, rc, "Matern nu must be 0.5, 1.5, 2.5 or inf on the device path (general nu needs Bessel K_nu)");
+    return fail(h, rc, "Matern nu must be positive and at most 50");
   if (rc != PLX_OK) return fail(h, rc, "unknown kernel id");
   CK(cudaSetDevice(h->device));
   h->n = n; h->d = d; h->kind = kind; h->jitter = jitter;
+  h->mg = (kind == K_GEN) ? make_matern_gen(nu) : MaternGen{};
   h->npad = (n + 127) / 128 * 128; h->nb = h->npad / 128;
+  { const int nt32 = (n + 31) / 32; h->ntri = nt32 * (nt32 + 1) / 2; }   // lower 32-tiles that hold observations
   h->have_data = false; h->have_state = false; h->state_factor_valid = false;
   int r;
   if ((r = ensure(h, h->dX, h->x_cap, static_cast<size_t>(n) * d)) != PLX_OK) return r;
@@ -233,8 +260,8 @@ static int ensure_batch(plx_bo* h, int B) {
   h->bp = BatchPtrs{}; h->d_thetas = h->d_logdet = h->d_w = h->d_alpha = h->d_partial = h->d_lml = h->d_grad = nullptr;
   h->d_info = nullptr; h->bcap = 0; h->state_factor_valid = false;
   const size_t mat = static_cast<size_t>(h->npad) * h->npad, blk = static_cast<size_t>(h->nb) * 128 * 128;
-  const int nt32 = (h->n + 31) / 32;
-  h->ntri = nt32 * (nt32 + 1) / 2;
+  const int nt32max = h->npad / 32;                   // partial sums: room for every 32-tile of npad
+  const int ntri_cap = nt32max * (nt32max + 1) / 2;
   CK(cudaMalloc(&h->bp.A, sizeof(double) * mat * cap));
   CK(cudaMalloc(&h->bp.L, sizeof(double) * mat * cap));
   CK(cudaMalloc(&h->bp.U, sizeof(double) * mat * cap));
@@ -244,7 +271,7 @@ static int ensure_batch(plx_bo* h, int B) {
   CK(cudaMalloc(&h->d_logdet, sizeof(double) * cap));
   CK(cudaMalloc(&h->d_w, sizeof(double) * h->npad * cap));
   CK(cudaMalloc(&h->d_alpha, sizeof(double) * h->npad * cap));
-  CK(cudaMalloc(&h->d_partial, sizeof(double) * h->ntri * cap));
+  CK(cudaMalloc(&h->d_partial, sizeof(double) * ntri_cap * cap));
   CK(cudaMalloc(&h->d_lml, sizeof(double) * cap));
   CK(cudaMalloc(&h->d_grad, sizeof(double) * cap));
   CK(cudaMalloc(&h->d_info, sizeof(int) * cap));
@@ -260,7 +287,7 @@ static int launch_lml(plx_bo* h, int B, bool want_grad) {
   CK(cudaMemsetAsync(h->d_logdet, 0, sizeof(double) * B, st));
   CK(cudaMemsetAsync(h->d_info, 0, sizeof(int) * B, st));
   kmat_kernel<0><<<dim3(npad / 32, npad / 32, B), 256, 0, st>>>(h->dX, n, h->d, npad, h->d_thetas, h->kind,
-                                                               h->jitter, h->bp, nullptr, nullptr, 0);
+                                                               h->mg, h->jitter, h->bp, nullptr, nullptr, 0);
   LAUNCH_CHECK("kmat_kernel");
   for (int k = 0; k < nb; ++k) {
     potf2_inv_kernel<<<B, 256, POTF_SMEM, st>>>(h->bp, k, n, npad, h->d_logdet, h->d_info);
@@ -286,7 +313,7 @@ static int launch_lml(plx_bo* h, int B, bool want_grad) {
   if (want_grad) {
     kinv_kernel<<<dim3(nb * (nb + 1) / 2, B), 256, GEMM_SMEM, st>>>(h->bp, npad);
     LAUNCH_CHECK("kinv_kernel");
-    kmat_kernel<1><<<dim3(h->ntri, 1, B), 256, 0, st>>>(h->dX, n, h->d, npad, h->d_thetas, h->kind, h->jitter,
+    kmat_kernel<1><<<dim3(h->ntri, 1, B), 256, 0, st>>>(h->dX, n, h->d, npad, h->d_thetas, h->kind, h->mg, h->jitter,
                                                        h->bp, h->d_alpha, h->d_partial, h->ntri);
     LAUNCH_CHECK("kmat_kernel<grad>");
   }
@@ -419,7 +446,7 @@ static void fill_params(plx_bo* h, SweepParams& p, const double* Xc_dev, long lo
   p.Xc = Xc_dev; p.N = N; p.idx_base = idx_base;
   p.d = h->d; p.n = h->n; p.npad = h->npad; p.n16 = (h->n + 15) / 16 * 16;
   p.X = h->dX; p.Xt = h->dXt; p.alpha = h->d_alpha_state; p.Z = h->dZ; p.ell = std::exp(h->theta);
-  p.kind = h->kind; p.acq = acq; p.kappa = kappa; p.eps = eps; p.y_max = y_max;
+  p.kind = h->kind; p.mg = h->mg; p.acq = acq; p.kappa = kappa; p.eps = eps; p.y_max = y_max;
   p.Ks = h->dKs; p.out_mean = p.out_std = p.out_acq = nullptr;
   p.blk_val = h->d_blk_val; p.blk_idx = h->d_blk_idx; p.dbg = h->sweep_dbg;
 }
@@ -621,7 +648,7 @@ static int ensure_refine(plx_bo* h, int S) {
 }
 
 static void fill_refine(plx_bo* h, RefineParams& p, int S, int acq, double kappa, double eps, double y_max, int max_iter) {
-  p.S = S; p.d = h->d; p.n = h->n; p.npad = h->npad; p.kind = h->kind; p.acq = acq; p.max_iter = max_iter;
+  p.S = S; p.d = h->d; p.n = h->n; p.npad = h->npad; p.kind = h->kind; p.mg = h->mg; p.acq = acq; p.max_iter = max_iter;
   p.ell = std::exp(h->theta); p.kappa = kappa; p.eps = eps; p.y_max = y_max;
   p.X = h->dX; p.alpha = h->d_alpha_state; p.Z = h->dZ; p.bounds = h->rf_bounds;
   p.kv = h->rf_kv; p.kp = h->rf_kp; p.v = h->rf_v; p.w = h->rf_w;
@@ -810,7 +837,7 @@ extern "C" int plx_acq_sweep_noalloc(int device, void* stream, const double* Xc_
   p.Xc = Xc_dev; p.N = N; p.idx_base = idx_base;
   p.d = d; p.n = n; p.npad = npad; p.n16 = (n + 15) / 16 * 16;
   p.X = X_dev; p.Xt = nullptr; p.alpha = alpha_dev; p.Z = Zpad; p.ell = std::exp(theta);
-  p.kind = kind; p.acq = acq; p.kappa = kappa; p.eps = eps; p.y_max = y_max;
+  p.kind = kind; p.mg = (kind == K_GEN) ? make_matern_gen(nu) : MaternGen{}; p.acq = acq; p.kappa = kappa; p.eps = eps; p.y_max = y_max;
   p.Ks = Ks; p.out_mean = p.out_std = p.out_acq = nullptr;
   p.blk_val = blk_val; p.blk_idx = blk_idx; p.dbg = 0;
   const long long ntiles = (N + 127) / 128;

@@ -20,9 +20,90 @@
 
 namespace plx {
 
-enum KernelKind { K_RBF = 0, K_M05 = 1, K_M15 = 2, K_M25 = 3 };
+enum KernelKind { K_RBF = 0, K_M05 = 1, K_M15 = 2, K_M25 = 3, K_GEN = 4 };
 
-__device__ __forceinline__ double kern_value(int kind, double r2) {
+// Matern with a general smoothness nu (sklearn kernels.py:1732-1738: 2^(1-nu)/Gamma(nu) * t^nu * K_nu(t),
+// t = sqrt(2 nu) r, through scipy.special.kv).  Everything that depends on nu alone is prepared once on
+// the host (api.cu: make_matern_gen); the device evaluates the modified Bessel function K by Temme's
+// series for t < 1 and Steed's continued fraction CF2 above, then recurs upward in the order --
+// the published algorithm (Temme 1975; Press et al., `bessik`), checked against mpmath to 3e-15.
+struct MaternGen {
+  double nu, mu, coef, s;                // order, fractional order, 2^(1-nu)/Gamma(nu), sqrt(2 nu)
+  double gam1, gam2, gampl, gammi;       // Temme's Gamma_1, Gamma_2, 1/Gamma(1+mu), 1/Gamma(1-mu)
+  int nl;                                // upward recurrence steps: nu = mu + nl (nl = 0: mu = -nu)
+};
+
+// K_nu(x) and K_{nu-1}(x) for x > 0
+__device__ __forceinline__ void bessel_k_pair(const MaternGen& m, double x, double& k, double& km1) {
+  const double mu = m.mu, mu2 = mu * mu, xi = 1.0 / x, xi2 = 2.0 * xi;
+  double rkmu, rk1;
+  if (x < 1.0) {
+    const double x2 = 0.5 * x, pimu = 3.141592653589793 * mu;
+    double d = -log(x2), e = mu * d;
+    const double fact2 = (fabs(e) < 1e-16) ? 1.0 : sinh(e) / e;
+    const double fact = (fabs(pimu) < 1e-16) ? 1.0 : pimu / sin(pimu);
+    double ff = fact * (m.gam1 * cosh(e) + m.gam2 * fact2 * d);
+    double sum = ff;
+    e = exp(e);
+    double p = 0.5 * e / m.gampl, q = 0.5 / (e * m.gammi), c = 1.0, sum1 = p;
+    d = x2 * x2;
+    for (int i = 1; i < 500; ++i) {
+      ff = (i * ff + p + q) / (i * i - mu2);
+      c *= d / i;
+      p /= (i - mu);
+      q /= (i + mu);
+      const double del = c * ff;
+      sum += del;
+      sum1 += c * (p - i * ff);
+      if (fabs(del) < fabs(sum) * 1e-16) break;
+    }
+    rkmu = sum; rk1 = sum1 * xi2;
+  } else {
+    double b = 2.0 * (1.0 + x), d = 1.0 / b, h = d, delh = d, q1 = 0.0, q2 = 1.0;
+    const double a1 = 0.25 - mu2;
+    double q = a1, c = a1, a = -a1, s = 1.0 + q * delh;
+    for (int i = 2; i < 10000; ++i) {
+      a -= 2 * (i - 1);
+      c = -a * c / i;
+      const double qnew = (q1 - b * q2) / a;
+      q1 = q2; q2 = qnew;
+      q += c * qnew;
+      b += 2.0;
+      d = 1.0 / (b + a * d);
+      delh = (b * d - 1.0) * delh;
+      h += delh;
+      const double dels = q * delh;
+      s += dels;
+      if (fabs(dels / s) < 1e-16) break;
+    }
+    h = a1 * h;
+    rkmu = sqrt(3.141592653589793 / (2.0 * x)) * exp(-x) / s;
+    rk1 = rkmu * (mu + x + 0.5 - h) * xi;
+  }
+  if (m.nl == 0) { k = rkmu; km1 = rk1; return; }      // mu = -nu: K_nu = K_mu, K_{nu-1} = K_{1-nu} = K_{mu+1}
+  double prev = rkmu;
+  for (int i = 1; i <= m.nl; ++i) {
+    const double t = (mu + i) * xi2 * rk1 + rkmu;
+    prev = rkmu; rkmu = rk1; rk1 = t;
+  }
+  k = rkmu; km1 = prev;
+}
+
+// value, d/dtheta and d/d(r^2) of the general-nu Matern kernel at squared scaled distance r2
+__device__ __forceinline__ void matern_gen_eval(const MaternGen& m, double r2, double& val, double& dtheta, double& dr2) {
+  double r = sqrt(r2);
+  if (r == 0.0) r = 2.220446049250313e-16;             // sklearn: K[K == 0.0] += eps
+  const double t = m.s * r;
+  double k, km1;
+  bessel_k_pair(m, t, k, km1);
+  const double tp = m.coef * pow(t, m.nu);
+  val = tp * k;
+  dtheta = tp * t * km1;                                // d/dtheta, theta = log(length_scale): dt/dtheta = -t
+  dr2 = -m.nu * tp / t * km1;                           // d/d(r^2)
+}
+
+__device__ __forceinline__ double kern_value(int kind, double r2, const MaternGen& mg) {
+  if (kind == K_GEN) { double v, a, b; matern_gen_eval(mg, r2, v, a, b); return v; }
   if (kind == K_RBF) return exp(-0.5 * r2);
   const double r = sqrt(r2);
   if (kind == K_M05) return exp(-r);
@@ -32,7 +113,8 @@ __device__ __forceinline__ double kern_value(int kind, double r2) {
 }
 
 template <int KIND>
-__device__ __forceinline__ double kern_value_t(double r2) {
+__device__ __forceinline__ double kern_value_t(double r2, const MaternGen& mg) {
+  if (KIND == K_GEN) { double v, a, b; matern_gen_eval(mg, r2, v, a, b); return v; }
   if (KIND == K_RBF) return exp(-0.5 * r2);
   const double r = sqrt(r2);
   if (KIND == K_M05) return exp(-r);
@@ -42,7 +124,8 @@ __device__ __forceinline__ double kern_value_t(double r2) {
 }
 
 // dK/dtheta for theta = log(length_scale) as sklearn forms it (kernels.py:1575, :1752-1773)
-__device__ __forceinline__ double kern_dtheta(int kind, double r2) {
+__device__ __forceinline__ double kern_dtheta(int kind, double r2, const MaternGen& mg) {
+  if (kind == K_GEN) { double v, a, b; matern_gen_eval(mg, r2, v, a, b); return a; }
   if (kind == K_RBF) return exp(-0.5 * r2) * r2;
   const double r = sqrt(r2);
   const double d2 = r * r;                       // sklearn squares the rooted distance again
@@ -69,8 +152,8 @@ constexpr int DCH = 32;
 
 template <int MODE>
 __global__ void __launch_bounds__(256) kmat_kernel(const double* __restrict__ X, int n, int d, int npad,
-                                                   const double* __restrict__ thetas, int kind, double jitter,
-                                                   BatchPtrs bp, const double* __restrict__ alpha,
+                                                   const double* __restrict__ thetas, int kind, MaternGen mg,
+                                                   double jitter, BatchPtrs bp, const double* __restrict__ alpha,
                                                    double* __restrict__ partial, int ntri) {
   __shared__ double Xi[32][DCH + 1];
   __shared__ double Xj[32][DCH + 1];
@@ -116,7 +199,7 @@ __global__ void __launch_bounds__(256) kmat_kernel(const double* __restrict__ X,
     for (int r = 0; r < 4; ++r) {
       const int i = i0 + ty + 8 * r, j = j0 + tx;
       double v;
-      if (i < n && j < n) v = (i == j) ? 1.0 + jitter : kern_value(kind, r2[r]);
+      if (i < n && j < n) v = (i == j) ? 1.0 + jitter : kern_value(kind, r2[r], mg);
       else v = (i == j) ? 1.0 : 0.0;
       A[i * ld + j] = v;
     }
@@ -128,7 +211,7 @@ __global__ void __launch_bounds__(256) kmat_kernel(const double* __restrict__ X,
     for (int r = 0; r < 4; ++r) {
       const int i = i0 + ty + 8 * r, j = j0 + tx;
       if (i < n && j < n) {
-        const double g = (i == j) ? 0.0 : kern_dtheta(kind, r2[r]);
+        const double g = (i == j) ? 0.0 : kern_dtheta(kind, r2[r], mg);
         s += (al[i] * al[j] - Kinv[i * ld + j]) * g;
       }
     }

@@ -30,7 +30,8 @@ constexpr int RF_DMAX = 128;      // largest encoded dimension the refinement su
 constexpr int RF_SB = 8;          // seeds per register block in the matrix-vector kernels
 
 // d k / d (r^2) for the closed-form kernels (r^2 = squared distance in length-scale units)
-__device__ __forceinline__ double kern_dr2(int kind, double r2) {
+__device__ __forceinline__ double kern_dr2(int kind, double r2, const MaternGen& mg) {
+  if (kind == K_GEN) { double v, a, b; matern_gen_eval(mg, r2, v, a, b); return b; }
   if (kind == K_RBF) return -0.5 * exp(-0.5 * r2);
   const double r = sqrt(r2);
   if (kind == K_M05) return (r > 0.0) ? -exp(-r) / (2.0 * r) : 0.0;
@@ -47,6 +48,7 @@ struct RefineScalars {            // per-seed optimiser state (all lanes of the 
 
 struct RefineParams {
   int S, d, n, npad, kind, acq, max_iter;
+  MaternGen mg;
   double ell, kappa, eps, y_max;
   const double* X; const double* alpha; const double* Z; const double* bounds;   // bounds [d][2]
   double* kv; double* kp; double* v; double* w;     // [S][npad]
@@ -78,8 +80,8 @@ __global__ void __launch_bounds__(128) refine_kstar_kernel(RefineParams p) {
     const double* xj = p.X + static_cast<size_t>(j) * p.d;
     double r2 = 0.0;
     for (int q = 0; q < p.d; ++q) { const double df = x[q] / p.ell - xj[q] / p.ell; r2 += df * df; }
-    kv = kern_value(p.kind, r2);
-    kp = kern_dr2(p.kind, r2);
+    kv = kern_value(p.kind, r2, p.mg);
+    kp = kern_dr2(p.kind, r2, p.mg);
   }
   p.kv[static_cast<size_t>(s) * p.npad + j] = kv;
   p.kp[static_cast<size_t>(s) * p.npad + j] = kp;

@@ -35,6 +35,7 @@ struct SweepParams {
   const double* Z;         // L^-1, row-major [npad][npad]
   double ell;              // length scale
   int kind, acq;
+  MaternGen mg;            // constants of the general-nu Matern kernel (kind == K_GEN)
   double kappa, eps, y_max;
   double* Ks;              // scratch [gridDim.x * 128][npad]
   double* out_mean; double* out_std; double* out_acq;   // optional per-candidate dumps [N]
@@ -170,7 +171,7 @@ __device__ __forceinline__ void phase_a(const SweepParams& p, long long tile, do
         const double aj = real ? p.alpha[jo] : 0.0;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          const double kv = real ? kern_value(p.kind, r2[i][j]) : 0.0;
+          const double kv = real ? kern_value(p.kind, r2[i][j], p.mg) : 0.0;
           mu[i] += kv * aj;
           Kslab[static_cast<size_t>(ty * 8 + i) * p.npad + jo] = kv;
         }
@@ -268,8 +269,8 @@ __device__ __forceinline__ void kern_rows(const SweepParams& p, uint32_t sm, dou
   for (int ci = 0; ci < 16; ++ci) {
     const int c = warp * 16 + ci;
     const uint32_t r2a = sm + static_cast<uint32_t>((PA_R2 + c * R2_LD + lane) * 8);
-    const double k0 = real0 ? kern_value_t<KIND>(lds64(r2a)) : 0.0;
-    const double k1 = real1 ? kern_value_t<KIND>(lds64(r2a + 32 * 8)) : 0.0;
+    const double k0 = real0 ? kern_value_t<KIND>(lds64(r2a), p.mg) : 0.0;
+    const double k1 = real1 ? kern_value_t<KIND>(lds64(r2a + 32 * 8), p.mg) : 0.0;
     double* row = Kslab + static_cast<size_t>(c) * p.npad;
     if (st0) row[j0] = k0;
     if (st1) row[j1] = k1;
@@ -352,6 +353,7 @@ __device__ __forceinline__ void phase_a3(const SweepParams& p, long long tile, d
       case K_RBF: kern_rows<K_RBF>(p, sm, Kslab, jb, warp, lane); break;
       case K_M05: kern_rows<K_M05>(p, sm, Kslab, jb, warp, lane); break;
       case K_M15: kern_rows<K_M15>(p, sm, Kslab, jb, warp, lane); break;
+      case K_GEN: kern_rows<K_GEN>(p, sm, Kslab, jb, warp, lane); break;
       default: kern_rows<K_M25>(p, sm, Kslab, jb, warp, lane); break;
     }
     // no barrier here: the next block re-writes Xs (free since the barrier above) and parks into R2s only

@@ -1,0 +1,123 @@
+"""GPU: Matern with a general smoothness nu (nu = 1.9 is what every fixture and doc example of the
+reference uses: polyaxon/factories/fixtures.py:204).  sklearn evaluates it through scipy.special.kv and
+differences the kernel numerically for the theta-gradient (kernels.py:1774-1779, step 1e-10); the
+device evaluates K_nu itself and uses the analytic derivative, so the gradient is compared with a
+central difference of the oracle's LML rather than with sklearn's noisy value."""
+import warnings
+
+import numpy as np
+import pytest
+
+from conftest import golden_names, load_golden
+from oracle import gp_numpy as G
+
+pytestmark = pytest.mark.gpu
+EPS = np.finfo(float).eps
+GENERAL = [n for n in golden_names() if '_m19_' in n]
+WELL = [n for n in GENERAL if not n.startswith('ref1')]
+
+
+@pytest.fixture(scope='module')
+def handle():
+    from polyaxon_b200 import _lib
+    h = _lib.Handle(0)
+    yield h
+    h.close()
+
+
+def _args(g):
+    return dict(acq=int(g['acq']), y_max=float(g['y_max']), kappa=float(np.nan_to_num(g['kappa'])),
+                eps=float(np.nan_to_num(g['eps'])))
+
+
+@pytest.mark.parametrize('name', GENERAL)
+def test_posterior_and_acquisition(handle, name):
+    g = load_golden(name)
+    handle.set_data(g['X'], g['y'], int(g['kernel']), float(g['nu']))
+    handle.set_theta(float(g['theta']))
+    L, alpha, _ = handle.get_state()
+    cond = float(g['cond'])
+    # the two Bessel implementations (device Temme/Steed, scipy's AMOS) agree to ~1e-13 relative on the
+    # kernel entries; the factorisation amplifies that by cond(K)
+    tol = max(1e-9, 1e-13 * cond)
+    assert np.allclose(np.diag(L), g['L_diag'], rtol=max(1e-10, 1e-14 * cond), atol=0)
+    assert np.abs(alpha - g['alpha']).max() <= tol * np.abs(g['alpha']).max()
+    _, _, _, mean, std, acq = handle.sweep(g['x_tries_head'], dump=True, **_args(g))
+    assert np.abs(mean - g['mean']).max() <= tol * max(np.abs(g['mean']).max(), np.abs(g['y']).max())
+    assert np.abs(std ** 2 - g['std'] ** 2).max() <= tol
+    if cond < 1e8:
+        big = g['std'] ** 2 >= 1e-6
+        # variance agrees to ~1e-13 absolute (above); relative to a std of 1e-3 that is 1e-7
+        assert np.allclose(std[big], g['std'][big], rtol=1e-6, atol=0)
+        assert np.allclose(acq[big], g['ys_head'][big], rtol=0, atol=1e-7 * max(1.0, np.abs(g['ys_head']).max()))
+
+
+@pytest.mark.parametrize('name', WELL)
+def test_argmax_is_bit_exact(handle, name):
+    g = load_golden(name)
+    handle.set_data(g['X'], g['y'], int(g['kernel']), float(g['nu']))
+    handle.set_theta(float(g['theta']))
+    rs = np.random.RandomState(int(g['seed']))
+    for _ in range(int(g['n_restarts'])):
+        rs.uniform(*G.THETA_BOUNDS)
+    b = g['bounds']
+    xt = rs.uniform(b[:, 0], b[:, 1], size=(int(g['n_warmup']), b.shape[0]))
+    val, idx, x = handle.sweep(xt, **_args(g))
+    assert idx == int(g['argmax'])
+    assert val == pytest.approx(float(g['warm_acq']), rel=1e-9)
+
+
+@pytest.mark.parametrize('name', GENERAL)
+def test_lml_matches_and_gradient_is_the_true_derivative(handle, name):
+    g = load_golden(name)
+    handle.set_data(g['X'], g['y'], int(g['kernel']), float(g['nu']))
+    lml, grad = handle.lml(g['fixed_thetas'])
+    for i, th in enumerate(g['fixed_thetas']):
+        K = G.kernel_matrix(g['X'], float(th), int(g['kernel']), float(g['nu']))
+        cond = np.linalg.cond(K + 1e-10 * np.eye(K.shape[0]))
+        tol = max(1e-10, 1e-13 * cond)
+        assert lml[i] == pytest.approx(float(g['lml_fixed'][i]), rel=tol, abs=1e-9)
+        if cond < 1e7:
+            h = 1e-5
+            fd = (G.log_marginal_likelihood(g['X'], g['y'], float(th) + h, 1, float(g['nu']), eval_gradient=False)
+                  - G.log_marginal_likelihood(g['X'], g['y'], float(th) - h, 1, float(g['nu']), eval_gradient=False)) / (2 * h)
+            assert grad[i] == pytest.approx(fd, rel=1e-5, abs=1e-6 * max(1.0, abs(float(g['lml_fixed'][i]))))
+
+
+@pytest.mark.parametrize('name', WELL)
+def test_fit_lands_on_sklearns_optimum(handle, name):
+    g = load_golden(name)
+    handle.set_data(g['X'], g['y'], int(g['kernel']), float(g['nu']))
+    theta, lml, _ = handle.fit(np.log(float(g['length_scale'])), g['theta_inits'])
+    # sklearn's theta-gradient is a forward difference with step 1e-10 and is off by percents where
+    # the LML is flat, so its run stops a little short of the optimum: same basin, and the LML reached
+    # here is at least as high
+    assert theta == pytest.approx(float(g['theta']), abs=2e-3)
+    assert lml >= float(g['lml']) - 1e-9 * max(1.0, abs(float(g['lml'])))
+
+
+@pytest.mark.parametrize('name', WELL)
+def test_refinement_and_gradient(handle, name):
+    g = load_golden(name)
+    handle.set_data(g['X'], g['y'], int(g['kernel']), float(g['nu']))
+    handle.set_theta(float(g['theta']))
+    pts = g['x_seeds']
+    vals, grads = handle.acq_value_grad(pts, **_args(g))
+    h = 1e-6
+    for k in range(min(2, len(pts))):
+        for q in range(pts.shape[1]):
+            e = np.zeros(pts.shape[1])
+            e[q] = h
+            vp, _ = handle.acq_value_grad(pts[k] + e, **_args(g))
+            vm, _ = handle.acq_value_grad(pts[k] - e, **_args(g))
+            assert grads[k, q] == pytest.approx((vp[0] - vm[0]) / (2 * h), rel=2e-5, abs=1e-8)
+    xs, rv, ok = handle.refine(pts, g['bounds'], **_args(g))
+    best = float(g['warm_acq'])
+    for v, s in zip(rv, ok):
+        if s and v >= best:
+            best = v
+    ref = float(g['warm_acq'])
+    for v, s in zip(g['ref_acq'], g['ref_success']):
+        if s and v >= ref:
+            ref = v
+    assert best >= ref - 1e-6 * max(1.0, abs(ref))

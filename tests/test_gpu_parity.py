@@ -201,10 +201,12 @@ def test_not_positive_definite_raises_linalgerror(handle):
     assert lml[0] == -np.inf and grad[0] == 0.0              # sklearn _gpr.py:592-593
 
 
-def test_unsupported_nu_fails_loudly(handle):
+def test_unsupported_kernel_arguments_fail_loudly(handle):
     from polyaxon_b200._lib import PlxError
     with pytest.raises(PlxError):
-        handle.set_data(np.zeros((2, 1)), np.zeros(2), G.KERNEL_MATERN, 1.9)
+        handle.set_data(np.zeros((2, 1)), np.zeros(2), G.KERNEL_MATERN, -1.0)
+    with pytest.raises(PlxError):
+        handle.set_data(np.zeros((2, 1)), np.zeros(2), 7, 1.5)
 
 
 def test_large_problem_against_oracle_and_shard_merge(handle):
