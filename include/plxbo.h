@@ -101,6 +101,11 @@ int plx_candidates_set(plx_bo_handle h, const double* Xc, long long N, int d);
 int plx_acq_sweep_resident(plx_bo_handle h, long long idx_base, int acq, double kappa, double eps, double y_max,
                            double* best_value, long long* best_index, double* best_x);
 
+/* Verification hook: out[i] = k(r2[i]) exactly as the sweep's inner loop evaluates the closed-form
+ * kernels (sklearn kernels.py:1563, :1722-1729 on squared scaled distances), i.e. with the branch-free
+ * sqrt / exp of that loop.  Host arrays of length n. */
+int plx_kernel_values(plx_bo_handle h, int kernel, double nu, const double* r2, int n, double* out);
+
 /* Device time in milliseconds of the main sweep kernel(s) of the last plx_acq_sweep* call, measured
  * with CUDA events on the launching stream, and how many kernels that call launched. */
 int plx_last_sweep_stats(plx_bo_handle h, double* kernel_ms, long long* launches);

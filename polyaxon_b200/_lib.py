@@ -39,6 +39,7 @@ SIGNATURES = {
     'plx_candidates_set': (c_int, [c_void_p, c_void_p, c_longlong, c_int]),
     'plx_acq_sweep_resident': (c_int, [c_void_p, c_longlong, c_int, c_double, c_double, c_double, _dp,
                                        POINTER(c_longlong), c_void_p]),
+    'plx_kernel_values': (c_int, [c_void_p, c_int, c_double, c_void_p, c_int, c_void_p]),
     'plx_last_sweep_stats': (c_int, [c_void_p, _dp, POINTER(c_longlong)]),
     'plx_launch_count': (c_longlong, [c_void_p]),
     'plx_acq_refine': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_double, c_double, c_double, c_int,
@@ -222,6 +223,12 @@ class Handle(object):
         self._check(self.lib.plx_acq_sweep_resident(self._h, int(idx_base), int(acq), float(kappa), float(eps),
                                                     float(y_max), ctypes.byref(bv), ctypes.byref(bi), _ptr(bx)))
         return bv.value, bi.value, bx
+
+    def kernel_values(self, kernel, nu, r2):
+        r2 = _f64(np.ravel(r2))
+        out = np.empty_like(r2)
+        self._check(self.lib.plx_kernel_values(self._h, int(kernel), float(nu), _ptr(r2), r2.size, _ptr(out)))
+        return out
 
     def last_sweep_stats(self):
         ms, nl = c_double(), c_longlong()

@@ -597,6 +597,24 @@ extern "C" int plx_acq_sweep_resident(plx_bo_handle h, long long idx_base, int a
   return plx_acq_sweep_dev(h, h->d_resident, h->resident_n, idx_base, acq, kappa, eps, y_max, best_value, best_index, best_x);
 }
 
+extern "C" int plx_kernel_values(plx_bo_handle h, int kernel, double nu, const double* r2, int n, double* out) {
+  if (!h || !r2 || !out || n <= 0) return h ? fail(h, PLX_ERR_INVALID, "kernel_values: bad arguments") : PLX_ERR_INVALID;
+  int kind;
+  if (kernel_kind(kernel, nu, &kind) != PLX_OK || kind == K_GEN) return fail(h, PLX_ERR_UNSUPPORTED, "kernel_values: closed-form kernels only");
+  CK(cudaSetDevice(h->device));
+  double *d_in = nullptr, *d_out = nullptr;
+  CK(cudaMalloc(&d_in, sizeof(double) * n));
+  CK(cudaMalloc(&d_out, sizeof(double) * n));
+  CK(cudaMemcpyAsync(d_in, r2, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
+  kern_value_probe_kernel<<<(n + 255) / 256, 256, 0, h->stream>>>(d_in, n, kind, d_out);
+  LAUNCH_CHECK("kern_value_probe_kernel");
+  CK(cudaMemcpyAsync(out, d_out, sizeof(double) * n, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  CK(cudaFree(d_in));
+  CK(cudaFree(d_out));
+  return PLX_OK;
+}
+
 extern "C" int plx_last_sweep_stats(plx_bo_handle h, double* kernel_ms, long long* launches) {
   if (!h) return PLX_ERR_INVALID;
   if (kernel_ms) *kernel_ms = h->last_ms;

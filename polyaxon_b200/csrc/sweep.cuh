@@ -265,17 +265,43 @@ __device__ __forceinline__ void kern_rows(const SweepParams& p, uint32_t sm, dou
   const bool real0 = j0 < p.n, real1 = j1 < p.n;
   const double a0 = real0 ? p.alpha[j0] : 0.0, a1 = real1 ? p.alpha[j1] : 0.0;
   const bool st0 = j0 < p.n16, st1 = j1 < p.n16;
-#pragma unroll 4
-  for (int ci = 0; ci < 16; ++ci) {
-    const int c = warp * 16 + ci;
-    const uint32_t r2a = sm + static_cast<uint32_t>((PA_R2 + c * R2_LD + lane) * 8);
-    const double k0 = real0 ? kern_value_t<KIND>(lds64(r2a), p.mg) : 0.0;
-    const double k1 = real1 ? kern_value_t<KIND>(lds64(r2a + 32 * 8), p.mg) : 0.0;
-    double* row = Kslab + static_cast<size_t>(c) * p.npad;
-    if (st0) row[j0] = k0;
-    if (st1) row[j1] = k1;
-    const uint32_t ma = sm + static_cast<uint32_t>((PA_MACC + c * 32 + lane) * 8);
-    sts64(ma, lds64(ma) + (k0 * a0 + k1 * a1));
+  if constexpr (KIND == K_GEN) {
+    for (int ci = 0; ci < 16; ++ci) {
+      const int c = warp * 16 + ci;
+      const uint32_t r2a = sm + static_cast<uint32_t>((PA_R2 + c * R2_LD + lane) * 8);
+      double k0 = kern_value_t<KIND>(lds64(r2a), p.mg);
+      double k1 = kern_value_t<KIND>(lds64(r2a + 32 * 8), p.mg);
+      k0 = real0 ? k0 : 0.0;
+      k1 = real1 ? k1 : 0.0;
+      double* row = Kslab + static_cast<size_t>(c) * p.npad;
+      if (st0) row[j0] = k0;
+      if (st1) row[j1] = k1;
+      const uint32_t ma = sm + static_cast<uint32_t>((PA_MACC + c * 32 + lane) * 8);
+      sts64(ma, lds64(ma) + (k0 * a0 + k1 * a1));
+    }
+  } else {
+  // closed forms: four candidates (eight values) per step, evaluated in lock step (see kern_values_n)
+#pragma unroll 1
+  for (int ci = 0; ci < 16; ci += 4) {
+    double v[8];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const uint32_t r2a = sm + static_cast<uint32_t>((PA_R2 + (warp * 16 + ci + u) * R2_LD + lane) * 8);
+      v[2 * u] = lds64(r2a);
+      v[2 * u + 1] = lds64(r2a + 32 * 8);
+    }
+    kern_values_n<KIND, 8>(v);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int c = warp * 16 + ci + u;
+      const double k0 = real0 ? v[2 * u] : 0.0, k1 = real1 ? v[2 * u + 1] : 0.0;
+      double* row = Kslab + static_cast<size_t>(c) * p.npad;
+      if (st0) row[j0] = k0;
+      if (st1) row[j1] = k1;
+      const uint32_t ma = sm + static_cast<uint32_t>((PA_MACC + c * 32 + lane) * 8);
+      sts64(ma, lds64(ma) + (k0 * a0 + k1 * a1));
+    }
+  }
   }
 }
 
@@ -330,7 +356,7 @@ __device__ __forceinline__ void phase_a3(const SweepParams& p, long long tile, d
       const uint32_t cs = sm + static_cast<uint32_t>((PA_CS + ty * 8) * 8);
       const uint32_t xs = sm + static_cast<uint32_t>((PA_XS + tx) * 8);
 #pragma unroll 2
-      for (int q = 0; q < dn; ++q) {
+      for (int q = 0; q < ((p.dbg & 8) ? 1 : dn); ++q) {
         double cv[8], xv[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) { const double2 t2 = lds128(cs + (q * CS_LD + 2 * i) * 8); cv[2 * i] = t2.x; cv[2 * i + 1] = t2.y; }
@@ -349,7 +375,7 @@ __device__ __forceinline__ void phase_a3(const SweepParams& p, long long tile, d
       for (int j = 0; j < 4; ++j)
         sts64(sm + static_cast<uint32_t>((PA_R2 + (ty * 8 + i) * R2_LD + tx + 16 * j) * 8), r2[i][j]);
     named_bar_sync(1, 256);
-    switch (p.kind) {
+    if (!(p.dbg & 4)) switch (p.kind) {
       case K_RBF: kern_rows<K_RBF>(p, sm, Kslab, jb, warp, lane); break;
       case K_M05: kern_rows<K_M05>(p, sm, Kslab, jb, warp, lane); break;
       case K_M15: kern_rows<K_M15>(p, sm, Kslab, jb, warp, lane); break;

@@ -233,3 +233,30 @@ def test_large_problem_against_oracle_and_shard_merge(handle):
         if v > best[0] or (v == best[0] and i < best[1]):
             best = (v, i)
     assert best == (val, idx)
+
+
+@pytest.mark.parametrize('kernel,nu', [(0, 1.5), (1, 0.5), (1, 1.5), (1, 2.5)])
+def test_inner_loop_kernel_values_to_a_few_ulp(handle, kernel, nu):
+    """The sweep's branch-free sqrt / exp against numpy on squared distances over the whole range the
+    path can produce (0, denormal-small, typical, far beyond underflow)."""
+    rs = np.random.RandomState(0)
+    r2 = np.concatenate([[0.0, 1e-300, 1e-200, 1e-30, 1e-8, 0.5, 1.0, 2.0, 700.0, 5e5, 1e12],
+                         10.0 ** rs.uniform(-12, 6, 20000), rs.uniform(0, 60, 20000)])
+    got = handle.kernel_values(kernel, nu, r2)
+    r = np.sqrt(r2)
+    if kernel == 0:
+        want = np.exp(-0.5 * r2)
+    elif nu == 0.5:
+        want = np.exp(-r)
+    elif nu == 1.5:
+        t = r * np.sqrt(3)
+        want = (1 + t) * np.exp(-t)
+    else:
+        t = r * np.sqrt(5)
+        want = (1 + t + t * t / 3.0) * np.exp(-t)
+    tiny = want < 1e-290                       # flushed to zero below the normal range
+    assert np.all(got[tiny] <= 1e-290)
+    ok = ~tiny
+    ulp = np.abs(got[ok] - want[ok]) / np.spacing(want[ok])
+    assert ulp.max() <= 4.0, ulp.max()
+    assert got[0] == 1.0

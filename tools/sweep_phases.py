@@ -7,7 +7,7 @@ from oracle.reference_path import synthetic_problem
 from polyaxon_b200 import _lib
 import torch
 
-n, d, N = 2048, 32, 148 * 128 * 40
+n, d, N = 2048, 32, 148 * 128 * 80
 X, y, _ = synthetic_problem(n, d)
 h = _lib.Handle(0)
 h.set_data(X, y, _lib.KERNEL_MATERN, 1.5)
@@ -16,7 +16,7 @@ xc = torch.rand(N, d, dtype=torch.float64, device='cuda')
 torch.cuda.synchronize()
 for impl in [int(a) for a in sys.argv[1:]] or [1]:
     h.set_option('sweep_impl', impl)
-    for dbg in (0, 1, 2, 3):
+    for dbg in (0, 1, 2, 3, 2 | 4, 2 | 8, 2 | 4 | 8):
         h.set_option('sweep_dbg', dbg)
         ms = []
         for _ in range(3):
