@@ -146,6 +146,10 @@ def latency_configs():
     out.append(('C2 d=8 n=256 rbf ei N=1e6 S=10',
                 dict(kernel='rbf', nu=1.5, acq='ei', kappa=None, eps=0.0, n_warmup=1000000, n_iter=10,
                      restarts=0), X, y))
+    X, y, _ = synthetic_problem(2048, 32)
+    out.append(('C3 d=32 n=2048 matern1.5 poi N=16M S=10 R=17',
+                dict(kernel='matern', nu=1.5, acq='poi', kappa=None, eps=0.0, n_warmup=1 << 24, n_iter=10,
+                     restarts=16, reps=2, cpu=False), X, y))
     return out
 
 
@@ -173,7 +177,7 @@ def measure_latency(reps_gpu=7):
             'matrix': {k: {'uniform': [0, 1]} for k in keys}})
         configs = [dict(zip(keys, row.tolist())) for row in X]
         times = []
-        for _ in range(reps_gpu + 1):
+        for _ in range(c.get('reps', reps_gpu) + 1):
             t0 = time.perf_counter()
             opt = BOOptimizer(hptuning_config=cfg)
             opt.add_observations(configs=configs, metrics=y.tolist())
@@ -185,14 +189,14 @@ def measure_latency(reps_gpu=7):
         cpu = []
         with threadpool_limits(limits=os.cpu_count()), warnings.catch_warnings():
             warnings.simplefilter('ignore')
-            for _ in range(2 if c['n_warmup'] <= 100000 else 1):
+            for _ in range(0 if not c.get('cpu', True) else (2 if c['n_warmup'] <= 100000 else 1)):
                 t0 = time.perf_counter()
                 R.suggest(X, y, bounds, G.KERNEL_RBF if c['kernel'] == 'rbf' else G.KERNEL_MATERN, 1.0, c['nu'],
                           c['restarts'], {'ucb': 0, 'ei': 1, 'poi': 2}[c['acq']], c['kappa'] or 0.0, c['eps'] or 0.0,
                           17, c['n_warmup'], c['n_iter'], chunk=65536)
                 cpu.append((time.perf_counter() - t0) * 1e3)
         results.append({'config': label, 'get_suggestions_p50_ms': gpu_ms, 'first_call_ms': first_ms,
-                        'cpu_reference_ms': float(np.median(cpu)),
+                        'cpu_reference_ms': float(np.median(cpu)) if cpu else None,
                         'includes': 'fit, sweep, refinement, decode; the first call of the seeded group also draws the '
                                     'candidates with numpy RandomState (reference RNG contract) and uploads them, later '
                                     'calls reuse the device-resident matrix (same generator state => same candidates)'})

@@ -98,6 +98,14 @@ int plx_acq_sweep_dev(plx_bo_handle h, const double* Xc_dev, long long N, long l
  * plx_acq_sweep_resident sweeps it without drawing or copying it again.  The host layer decides when
  * the copy is still valid (same generator state, bounds and sizes). */
 int plx_candidates_set(plx_bo_handle h, const double* Xc, long long N, int d);
+/* Draw the resident candidate matrix on the device, bit-identical to
+ * numpy.random.RandomState.uniform(low, low + range, size=(N, d)) (acquisition_function.py:88-89):
+ * key[624] / pos are the generator's MT19937 state (RandomState.get_state()[1:3]); key_out / pos_out
+ * receive the state after the draw so the host generator can be moved on.  pos must be even. */
+int plx_candidates_draw_mt19937(plx_bo_handle h, const unsigned* key, int pos, const double* low,
+                                const double* range, long long N, int d, unsigned* key_out, int* pos_out);
+/* Copy rows [first, first + count) of the resident matrix back to the host (verification). */
+int plx_candidates_get(plx_bo_handle h, double* out, long long first, long long count);
 int plx_acq_sweep_resident(plx_bo_handle h, long long idx_base, int acq, double kappa, double eps, double y_max,
                            double* best_value, long long* best_index, double* best_x);
 

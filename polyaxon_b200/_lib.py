@@ -37,6 +37,9 @@ SIGNATURES = {
     'plx_acq_sweep_dev': (c_int, [c_void_p, c_void_p, c_longlong, c_longlong, c_int, c_double, c_double,
                                   c_double, _dp, POINTER(c_longlong), c_void_p]),
     'plx_candidates_set': (c_int, [c_void_p, c_void_p, c_longlong, c_int]),
+    'plx_candidates_draw_mt19937': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_longlong, c_int,
+                                            c_void_p, POINTER(c_int)]),
+    'plx_candidates_get': (c_int, [c_void_p, c_void_p, c_longlong, c_longlong]),
     'plx_acq_sweep_resident': (c_int, [c_void_p, c_longlong, c_int, c_double, c_double, c_double, _dp,
                                        POINTER(c_longlong), c_void_p]),
     'plx_kernel_values': (c_int, [c_void_p, c_int, c_double, c_void_p, c_int, c_void_p]),
@@ -216,6 +219,31 @@ class Handle(object):
         self.resident_key = None
         self._check(self.lib.plx_candidates_set(self._h, _ptr(Xc), Xc.shape[0], Xc.shape[1]))
         self.resident_key = key
+
+    def candidates_draw(self, rng, low, high, N, key=None):
+        """Draw rng.uniform(low, high, size=(N, d)) on the device (bit-identical to numpy's MT19937
+        stream) into the resident matrix and move `rng` past the draw.  Returns False -- nothing
+        drawn, nothing changed -- when the generator is not an MT19937 at an even position."""
+        state = rng.get_state()
+        if state[0] != 'MT19937' or int(state[2]) & 1:
+            return False
+        low = _f64(low)
+        rng_range = _f64(np.subtract(high, low))
+        key_in = np.ascontiguousarray(state[1], dtype=np.uint32)
+        key_out = np.empty(624, dtype=np.uint32)
+        pos_out = c_int()
+        self.resident_key = None
+        self._check(self.lib.plx_candidates_draw_mt19937(self._h, _ptr(key_in), int(state[2]), _ptr(low),
+                                                         _ptr(rng_range), int(N), low.size, _ptr(key_out),
+                                                         ctypes.byref(pos_out)))
+        rng.set_state((state[0], key_out, pos_out.value) + tuple(state[3:]))
+        self.resident_key = key
+        return True
+
+    def candidates_get(self, first, count, d):
+        out = np.empty((count, d))
+        self._check(self.lib.plx_candidates_get(self._h, _ptr(out), int(first), int(count)))
+        return out
 
     def sweep_resident(self, acq, y_max, kappa=0.0, eps=0.0, idx_base=0):
         bv, bi = c_double(), c_longlong()

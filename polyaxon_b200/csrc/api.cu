@@ -589,6 +589,44 @@ extern "C" int plx_candidates_set(plx_bo_handle h, const double* Xc, long long N
   return PLX_OK;
 }
 
+extern "C" int plx_candidates_draw_mt19937(plx_bo_handle h, const unsigned* key, int pos, const double* low,
+                                           const double* range, long long N, int d, unsigned* key_out, int* pos_out) {
+  if (!h || !key || !low || !range || !key_out || !pos_out || N < 0 || d <= 0 || pos < 0 || pos > 624)
+    return h ? fail(h, PLX_ERR_INVALID, "candidates_draw_mt19937: bad arguments") : PLX_ERR_INVALID;
+  if (pos & 1) return fail(h, PLX_ERR_UNSUPPORTED, "candidates_draw_mt19937: odd stream position (draw on the host instead)");
+  if (d > 2048) return fail(h, PLX_ERR_UNSUPPORTED, "candidates_draw_mt19937: d exceeds 2048");
+  CK(cudaSetDevice(h->device));
+  h->resident_n = 0;
+  int r;
+  if ((r = ensure(h, h->d_resident, h->resident_cap, static_cast<size_t>(std::max<long long>(N, 1)) * d)) != PLX_OK) return r;
+  unsigned* d_key = nullptr; double* d_lr = nullptr; int* d_pos = nullptr;
+  CK(cudaMalloc(&d_key, sizeof(unsigned) * 1248));
+  CK(cudaMalloc(&d_lr, sizeof(double) * 2 * d));
+  CK(cudaMalloc(&d_pos, sizeof(int)));
+  CK(cudaMemcpyAsync(d_key, key, sizeof(unsigned) * 624, cudaMemcpyHostToDevice, h->stream));
+  CK(cudaMemcpyAsync(d_lr, low, sizeof(double) * d, cudaMemcpyHostToDevice, h->stream));
+  CK(cudaMemcpyAsync(d_lr + d, range, sizeof(double) * d, cudaMemcpyHostToDevice, h->stream));
+  mt19937_uniform_kernel<<<1, 512, sizeof(double) * 2 * d, h->stream>>>(d_key, pos, d_lr, d_lr + d, d, N * d,
+                                                                       h->d_resident, d_key + 624, d_pos);
+  LAUNCH_CHECK("mt19937_uniform_kernel");
+  CK(cudaMemcpyAsync(key_out, d_key + 624, sizeof(unsigned) * 624, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaMemcpyAsync(pos_out, d_pos, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  CK(cudaFree(d_key)); CK(cudaFree(d_lr)); CK(cudaFree(d_pos));
+  h->resident_n = N; h->resident_d = d;
+  return PLX_OK;
+}
+
+extern "C" int plx_candidates_get(plx_bo_handle h, double* out, long long first, long long count) {
+  if (!h || !out || first < 0 || count < 0) return h ? fail(h, PLX_ERR_INVALID, "candidates_get: bad arguments") : PLX_ERR_INVALID;
+  if (first + count > h->resident_n) return fail(h, PLX_ERR_INVALID, "candidates_get: range beyond the resident matrix");
+  CK(cudaSetDevice(h->device));
+  CK(cudaMemcpyAsync(out, h->d_resident + first * h->resident_d, sizeof(double) * count * h->resident_d,
+                     cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return PLX_OK;
+}
+
 extern "C" int plx_acq_sweep_resident(plx_bo_handle h, long long idx_base, int acq, double kappa, double eps,
                                       double y_max, double* best_value, long long* best_index, double* best_x) {
   if (!h) return PLX_ERR_INVALID;

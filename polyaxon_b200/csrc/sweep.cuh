@@ -564,6 +564,83 @@ __global__ void scale_transpose_x_kernel(const double* __restrict__ X, int n, in
   Xt[static_cast<size_t>(q) * npad + j] = (j < n) ? X[static_cast<size_t>(j) * d + q] / ell : 0.0;
 }
 
+// ------------------------------------------------------------------------------------------
+// Candidate draws on the device, bit-identical to the reference's generator.
+//
+// Reference: x_tries = random_generator.uniform(bounds[:, 0], bounds[:, 1], size=(n_warmup, d))
+// (acquisition_function.py:88-89) on numpy.random.RandomState, i.e. MT19937 with
+// next_double = ((w0 >> 5) * 2^26 + (w1 >> 6)) / 2^53 and x = low + (high - low) * next_double, values
+// filled candidate-major.  At C3 that is 1.07e9 32-bit outputs: ~4.5 s of host time per call.
+// The recurrence is sequential over 624-word blocks, but inside a block it splits into three
+// data-parallel sweeps (k < 227 depends on old words only; 227 <= k < 454 and 454 <= k < 624 on words
+// of the previous sweep), so one CTA regenerates a block in three barriers and tempers/scales 312
+// doubles per block with all threads.  Multiplication and addition are kept separate (no FMA), as in
+// numpy's C code.  Requires an even stream position (always true when only doubles were drawn).
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned mt_twist(unsigned a, unsigned b) {
+  const unsigned y = (a & 0x80000000u) | (b & 0x7fffffffu);
+  return (y >> 1) ^ ((0u - (y & 1u)) & 0x9908b0dfu);
+}
+__device__ __forceinline__ unsigned mt_temper(unsigned y) {
+  y ^= (y >> 11);
+  y ^= (y << 7) & 0x9d2c5680u;
+  y ^= (y << 15) & 0xefc60000u;
+  y ^= (y >> 18);
+  return y;
+}
+
+__global__ void __launch_bounds__(512) mt19937_uniform_kernel(const unsigned* __restrict__ key_in, int pos,
+                                                              const double* __restrict__ low,
+                                                              const double* __restrict__ range, int d,
+                                                              long long count, double* __restrict__ out,
+                                                              unsigned* __restrict__ key_out, int* __restrict__ pos_out) {
+  // Threads 0-255 regenerate the NEXT 624-word block (three data-parallel sweeps, barriers among
+  // themselves only) while threads 256-511 temper, scale and store the doubles of the CURRENT block;
+  // one CTA-wide barrier per block.
+  __shared__ unsigned buf[2][624];
+  extern __shared__ double lr[];                 // low[d], range[d]
+  const int tid = threadIdx.x;
+  for (int i = tid; i < 624; i += 512) buf[0][i] = key_in[i];
+  for (int i = tid; i < d; i += 512) { lr[i] = low[i]; lr[d + i] = range[i]; }
+  __syncthreads();
+  int cur = 0, p = pos;
+  int qbase = 0;                                 // (doubles produced so far) mod d
+  long long produced = 0;
+  while (produced < count) {
+    const long long left = count - produced;
+    const int pairs = (p >= 624) ? 0 : static_cast<int>(min(static_cast<long long>((624 - p) / 2), left));
+    const bool more = left > pairs;              // another block will be needed after this one
+    if (tid < 256) {
+      if (more) {
+        const unsigned* o = buf[cur];
+        unsigned* nw = buf[cur ^ 1];
+        if (tid < 227) nw[tid] = o[tid + 397] ^ mt_twist(o[tid], o[tid + 1]);
+        named_bar_sync(3, 256);
+        if (tid < 227) { const int k = tid + 227; nw[k] = nw[k - 227] ^ mt_twist(o[k], o[k + 1]); }
+        named_bar_sync(3, 256);
+        if (tid < 169) { const int k = tid + 454; nw[k] = nw[k - 227] ^ mt_twist(o[k], o[k + 1]); }
+        named_bar_sync(3, 256);
+        if (tid == 0) nw[623] = nw[396] ^ mt_twist(o[623], nw[0]);
+      }
+    } else {
+      const unsigned* w = buf[cur];
+      for (int t = tid - 256; t < pairs; t += 256) {
+        const unsigned a = mt_temper(w[p + 2 * t]) >> 5, b = mt_temper(w[p + 2 * t + 1]) >> 6;
+        const double u = (a * 67108864.0 + b) / 9007199254740992.0;
+        const int q = (qbase + t) % d;
+        out[produced + t] = __dadd_rn(lr[q], __dmul_rn(lr[d + q], u));
+      }
+    }
+    produced += pairs;
+    qbase = (qbase + pairs) % d;
+    p += 2 * pairs;
+    __syncthreads();
+    if (more) { cur ^= 1; p = 0; }
+  }
+  for (int i = tid; i < 624; i += 512) key_out[i] = buf[cur][i];
+  if (tid == 0) *pos_out = p;
+}
+
 // Merge the per-CTA bests into the running best of the whole sweep (one thread; grid <= #SMs).
 __global__ void sweep_merge_kernel(const double* __restrict__ blk_val, const long long* __restrict__ blk_idx,
                                    int nblk, double* best_val, long long* best_idx) {

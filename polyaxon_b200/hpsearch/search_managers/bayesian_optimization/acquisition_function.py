@@ -150,12 +150,18 @@ class UtilityFunction(object):
             rng.set_state(state_after)
             max_acq, _, x_max = h.sweep_resident(acq, **args)
             return max_acq, x_max, x_seeds.copy()
-        x_tries = rng.uniform(bounds[:, 0], bounds[:, 1], size=(n_warmup, d))
+        drawn_on_device = False
+        if key is not None and os.environ.get('PLX_BO_DEVICE_RNG', '1') != '0':
+            # numpy's MT19937 stream regenerated on the GPU, bit for bit (sweep.cuh); rng is moved on
+            drawn_on_device = h.candidates_draw(rng, bounds[:, 0], bounds[:, 1], n_warmup, key=key)
+        if not drawn_on_device:
+            x_tries = rng.uniform(bounds[:, 0], bounds[:, 1], size=(n_warmup, d))
         x_seeds = rng.uniform(bounds[:, 0], bounds[:, 1], size=(n_iter, d))
         if key is None:
             max_acq, _, x_max = h.sweep(x_tries, acq, **args)
             return max_acq, x_max, x_seeds
-        h.candidates_set(x_tries, key=key)
+        if not drawn_on_device:
+            h.candidates_set(x_tries, key=key)
         _SEED_CACHE.clear()                      # one resident matrix per process
         _SEED_CACHE[key] = (x_seeds.copy(), rng.get_state())
         max_acq, _, x_max = h.sweep_resident(acq, **args)

@@ -155,3 +155,51 @@ def test_resident_candidate_cache_is_transparent(monkeypatch):
     third, state3 = run()
     assert first == second == third
     assert np.array_equal(state1, state2) and np.array_equal(state1, state3)
+
+
+@pytest.mark.parametrize('d,n_cand,pre_draws', [(1, 1, 0), (2, 1000, 0), (7, 12345, 3), (32, 40000, 16), (5, 311, 1)])
+def test_device_mt19937_reproduces_numpy_bit_for_bit(d, n_cand, pre_draws):
+    """x_tries drawn on the GPU == RandomState.uniform(low, high, size=(N, d)) (acquisition_function.py:88-89),
+    and the host generator is left in the state numpy would have reached."""
+    from polyaxon_b200 import _lib
+    h = _lib.Handle(0)
+    try:
+        lo = np.linspace(-3.0, 2.0, d)
+        hi = lo + np.linspace(0.5, 7.0, d)
+        a = np.random.RandomState(4242)
+        b = np.random.RandomState(4242)
+        for _ in range(pre_draws):                        # e.g. restart thetas drawn during fit
+            a.uniform(-11.5, 11.5)
+            b.uniform(-11.5, 11.5)
+        want = a.uniform(lo, hi, size=(n_cand, d))
+        assert h.candidates_draw(b, lo, hi, n_cand)
+        got = h.candidates_get(0, n_cand, d)
+        assert np.array_equal(got, want)
+        sa, sb = a.get_state(), b.get_state()
+        assert np.array_equal(sa[1], sb[1]) and sa[2] == sb[2]
+        assert np.array_equal(a.uniform(size=5), b.uniform(size=5))
+        # an odd stream position (a 32-bit draw happened) is refused: the caller draws on the host
+        c = np.random.RandomState(1)
+        c.randint(0, 10)
+        if c.get_state()[2] & 1:
+            assert not h.candidates_draw(c, lo, hi, n_cand)
+    finally:
+        h.close()
+
+
+def test_device_rng_and_host_rng_give_the_same_suggestion(monkeypatch):
+    from polyaxon_b200.hpsearch.search_managers.bayesian_optimization import acquisition_function as af
+    from polyaxon_b200.hpsearch.search_managers.bayesian_optimization.optimizer import BOOptimizer
+    g = load_golden('c1_d2_n15_m25_ucb')
+    keys = ['x000', 'x001']
+    cfg = _config(g, {k: {'uniform': [0, 1]} for k in keys})
+    configs = [dict(zip(keys, row.tolist())) for row in g['X']]
+    out = []
+    for flag in ('1', '0'):
+        monkeypatch.setenv('PLX_BO_DEVICE_RNG', flag)
+        af._SEED_CACHE.clear()
+        opt = BOOptimizer(hptuning_config=cfg)
+        opt.add_observations(configs=configs, metrics=g['y'].tolist())
+        out.append((opt.get_suggestion(), opt.utility_function.random_generator.get_state()[1].copy()))
+    assert out[0][0] == out[1][0]
+    assert np.array_equal(out[0][1], out[1][1])
