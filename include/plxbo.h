@@ -114,6 +114,13 @@ int plx_acq_sweep_resident(plx_bo_handle h, long long idx_base, int acq, double 
  * sqrt / exp of that loop.  Host arrays of length n. */
 int plx_kernel_values(plx_bo_handle h, int kernel, double nu, const double* r2, int n, double* out);
 
+/* Sweep rows [first, first + count) of the resident matrix; best_index is the row number in the whole
+ * matrix.  This is the per-rank call of the multi-GPU path: every rank holds the same matrix, sweeps
+ * its contiguous slice, and the (value, index) records are merged with numpy.argmax semantics. */
+int plx_acq_sweep_resident_range(plx_bo_handle h, long long first, long long count, int acq, double kappa,
+                                 double eps, double y_max, double* best_value, long long* best_index,
+                                 double* best_x);
+
 /* Device time in milliseconds of the main sweep kernel(s) of the last plx_acq_sweep* call, measured
  * with CUDA events on the launching stream, and how many kernels that call launched. */
 int plx_last_sweep_stats(plx_bo_handle h, double* kernel_ms, long long* launches);

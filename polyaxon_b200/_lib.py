@@ -43,6 +43,8 @@ SIGNATURES = {
     'plx_acq_sweep_resident': (c_int, [c_void_p, c_longlong, c_int, c_double, c_double, c_double, _dp,
                                        POINTER(c_longlong), c_void_p]),
     'plx_kernel_values': (c_int, [c_void_p, c_int, c_double, c_void_p, c_int, c_void_p]),
+    'plx_acq_sweep_resident_range': (c_int, [c_void_p, c_longlong, c_longlong, c_int, c_double, c_double, c_double,
+                                             _dp, POINTER(c_longlong), c_void_p]),
     'plx_last_sweep_stats': (c_int, [c_void_p, _dp, POINTER(c_longlong)]),
     'plx_launch_count': (c_longlong, [c_void_p]),
     'plx_acq_refine': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_double, c_double, c_double, c_int,
@@ -257,6 +259,14 @@ class Handle(object):
         out = np.empty_like(r2)
         self._check(self.lib.plx_kernel_values(self._h, int(kernel), float(nu), _ptr(r2), r2.size, _ptr(out)))
         return out
+
+    def sweep_resident_range(self, first, count, acq, y_max, kappa=0.0, eps=0.0):
+        bv, bi = c_double(), c_longlong()
+        bx = np.empty(self.d)
+        self._check(self.lib.plx_acq_sweep_resident_range(self._h, int(first), int(count), int(acq), float(kappa),
+                                                          float(eps), float(y_max), ctypes.byref(bv),
+                                                          ctypes.byref(bi), _ptr(bx)))
+        return bv.value, bi.value, bx
 
     def last_sweep_stats(self):
         ms, nl = c_double(), c_longlong()

@@ -627,6 +627,18 @@ extern "C" int plx_candidates_get(plx_bo_handle h, double* out, long long first,
   return PLX_OK;
 }
 
+extern "C" int plx_acq_sweep_resident_range(plx_bo_handle h, long long first, long long count, int acq, double kappa,
+                                            double eps, double y_max, double* best_value, long long* best_index,
+                                            double* best_x) {
+  if (!h) return PLX_ERR_INVALID;
+  if (h->resident_d != h->d || (h->resident_n > 0 && !h->d_resident))
+    return fail(h, PLX_ERR_STATE, "acq_sweep_resident_range: no resident candidates of this dimension");
+  if (first < 0 || count < 0 || first + count > h->resident_n)
+    return fail(h, PLX_ERR_INVALID, "acq_sweep_resident_range: rows outside the resident matrix");
+  return plx_acq_sweep_dev(h, h->d_resident + first * h->d, count, first, acq, kappa, eps, y_max, best_value,
+                           best_index, best_x);
+}
+
 extern "C" int plx_acq_sweep_resident(plx_bo_handle h, long long idx_base, int acq, double kappa, double eps,
                                       double y_max, double* best_value, long long* best_index, double* best_x) {
   if (!h) return PLX_ERR_INVALID;

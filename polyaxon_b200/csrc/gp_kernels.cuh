@@ -384,7 +384,10 @@ __global__ void __launch_bounds__(256) potf2_inv_kernel(BatchPtrs bp, int k, int
   __shared__ int bad;
   if (tid == 0) bad = 0;
   const int lane = tid & 31, warp = tid >> 5;
-  for (int j = 0; j < 128; ++j) {
+  // rows / columns beyond the observations are identity padding: the factor and its inverse are the
+  // identity there, so every loop stops at the last real row of this block
+  const int m = min(128, max(0, n - k * 128));
+  for (int j = 0; j < m; ++j) {
     __syncthreads();                    // trailing update of column j-1 is complete
     double ajj = S[j * POTF_LD + j];    // stays untouched during this step (dl holds the root)
     if (!(ajj > 0.0)) {                 // non-positive or NaN pivot: not positive definite
@@ -394,34 +397,64 @@ __global__ void __launch_bounds__(256) potf2_inv_kernel(BatchPtrs bp, int k, int
     const double ljj = sqrt(ajj);
     const double inv = 1.0 / ljj;       // LAPACK dpotf2 scales the column by the reciprocal too
     if (tid == 0) { dl[j] = ljj; wdiag[j] = inv; }
-    for (int i = j + 1 + tid; i < 128; i += 256) S[i * POTF_LD + j] *= inv;
+    for (int i = j + 1 + tid; i < m; i += 256) S[i * POTF_LD + j] *= inv;
     __syncthreads();
     // trailing update of the lower triangle: S[i][c] -= S[i][j] * S[c][j], j < c <= i
-    for (int i = j + 1 + (tid >> 4); i < 128; i += 16) {
+    // (loads of a whole batch are issued before its stores: the compiler may not move a load across
+    //  a store to the same array, and one shared-memory round trip per element made this loop the
+    //  slowest part of the factorisation)
+    for (int i = j + 1 + (tid >> 4); i < m; i += 16) {
       const double lij = S[i * POTF_LD + j];
-      for (int c = j + 1 + (tid & 15); c <= i; c += 16) S[i * POTF_LD + c] -= lij * S[c * POTF_LD + j];
+      const int c0 = j + 1 + (tid & 15);
+      double sv[8], lv[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int c = c0 + 16 * u;
+        const bool on = c <= i;
+        sv[u] = on ? S[i * POTF_LD + c] : 0.0;
+        lv[u] = on ? S[c * POTF_LD + j] : 0.0;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int c = c0 + 16 * u;
+        if (c <= i) S[i * POTF_LD + c] = fma(-lij, lv[u], sv[u]);
+      }
     }
   }
   __syncthreads();
+  if (tid >= m && tid < 128) { dl[tid] = 1.0; wdiag[tid] = 1.0; }
   // W = L^-1 by forward substitution on all columns of the identity at once (right-looking):
   // W[i][c] (i > c) lives in the strict upper triangle at S[c][i], its diagonal in wdiag.
   for (int e = tid; e < 128 * 128; e += 256) {
     const int r = e >> 7, c = e & 127;
     if (c > r) S[r * POTF_LD + c] = 0.0;
+    else if (c < r && r >= m) S[r * POTF_LD + c] = 0.0;       // padding rows of L
   }
+  __syncthreads();
   if (tid < 128) S[tid * POTF_LD + tid] = dl[tid];
-  for (int j = 0; j < 128; ++j) {
+  for (int j = 0; j < m; ++j) {
     __syncthreads();
     const double wjj = wdiag[j];
     // row j of W becomes final: W[j][c] = acc / L[j][j]
     for (int c = tid; c < j; c += 256) S[c * POTF_LD + j] *= wjj;
     __syncthreads();
     // rows below: W[i][c] -= L[i][j] * W[j][c] for c <= j  (lane <-> i, warp <-> c)
-    for (int i = j + 1 + lane; i < 128; i += 32) {
+    for (int i = j + 1 + lane; i < m; i += 32) {
       const double lij = S[i * POTF_LD + j];
-      for (int c = warp; c <= j; c += 8) {
-        const double wjc = (c == j) ? wjj : S[c * POTF_LD + j];
-        S[c * POTF_LD + i] -= lij * wjc;
+      for (int cb = warp; cb <= j; cb += 64) {
+        double sv[8], wv[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int c = cb + 8 * u;
+          const bool on = c <= j;
+          sv[u] = on ? S[c * POTF_LD + i] : 0.0;
+          wv[u] = on ? ((c == j) ? wjj : S[c * POTF_LD + j]) : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int c = cb + 8 * u;
+          if (c <= j) S[c * POTF_LD + i] = fma(-lij, wv[u], sv[u]);
+        }
       }
     }
   }

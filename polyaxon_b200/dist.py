@@ -78,3 +78,37 @@ def merge_refined(value, seed_order, device=None, group=None):
         if best[1] < 0 or val >= best[0]:
             best = (val, order)
     return best
+
+
+def world():
+    """(rank, world_size) of the default process group, (0, 1) when torch.distributed is not in use."""
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+def gather_refined(xs, values, success, n_seeds, device=None, group=None):
+    """Each rank refined seeds rank, rank + world, ...; return the three arrays for ALL seeds in seed
+    order on every rank (so the acceptance rule of acquisition_function.py:105-111 runs unchanged)."""
+    import numpy as np
+    rank, size = world()
+    if size == 1:
+        return xs, values, success
+    dev = device if device is not None else torch.device('cpu')
+    d = xs.shape[1] if xs.ndim == 2 else 0
+    per = (n_seeds + size - 1) // size
+    pack = torch.zeros(per, d + 2, dtype=torch.float64, device=dev)
+    if len(values):
+        pack[:len(values), :d] = torch.from_numpy(np.ascontiguousarray(xs)).to(dev)
+        pack[:len(values), d] = torch.from_numpy(np.ascontiguousarray(values, dtype=np.float64)).to(dev)
+        pack[:len(values), d + 1] = torch.from_numpy(np.asarray(success, dtype=np.float64)).to(dev)
+    out = torch.empty(size * per, d + 2, dtype=torch.float64, device=dev)
+    dist.all_gather_into_tensor(out, pack, group=group)
+    out = out.cpu().numpy().reshape(size, per, d + 2)
+    all_x = np.empty((n_seeds, d))
+    all_v = np.empty(n_seeds)
+    all_s = np.zeros(n_seeds, dtype=bool)
+    for s in range(n_seeds):
+        r, k = s % size, s // size
+        all_x[s], all_v[s], all_s[s] = out[r, k, :d], out[r, k, d], out[r, k, d + 1] > 0.5
+    return all_x, all_v, all_s

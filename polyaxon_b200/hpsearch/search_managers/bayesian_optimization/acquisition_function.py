@@ -22,7 +22,7 @@ import os
 
 import numpy as np
 
-from polyaxon_b200 import _lib, device
+from polyaxon_b200 import _lib, device, dist as pdist
 from polyaxon_b200.hpsearch.search_managers.utils import get_random_generator
 from polyaxon_b200.schemas.hptuning import (
     AcquisitionFunctions,
@@ -148,7 +148,7 @@ class UtilityFunction(object):
         if cached is not None and h.resident_key == key:
             x_seeds, state_after = cached
             rng.set_state(state_after)
-            max_acq, _, x_max = h.sweep_resident(acq, **args)
+            max_acq, x_max = self._sweep_resident(h, acq, args, n_warmup)
             return max_acq, x_max, x_seeds.copy()
         drawn_on_device = False
         if key is not None and os.environ.get('PLX_BO_DEVICE_RNG', '1') != '0':
@@ -164,8 +164,23 @@ class UtilityFunction(object):
             h.candidates_set(x_tries, key=key)
         _SEED_CACHE.clear()                      # one resident matrix per process
         _SEED_CACHE[key] = (x_seeds.copy(), rng.get_state())
-        max_acq, _, x_max = h.sweep_resident(acq, **args)
+        max_acq, x_max = self._sweep_resident(h, acq, args, n_warmup)
         return max_acq, x_max, x_seeds
+
+    @staticmethod
+    def _sweep_resident(h, acq, args, n_warmup):
+        """Sweep of the resident matrix.  Under torch.distributed (one process per GPU, every rank
+        holding the same generator state and therefore the same matrix) each rank sweeps a
+        contiguous slice and one all-gather of {value, index} merges the bests; the winning row is
+        then read from the rank's own copy, so no candidate data crosses the links."""
+        rank, size = pdist.world()
+        if size == 1 or os.environ.get('PLX_BO_DISTRIBUTED', '1') == '0':
+            value, _, x = h.sweep_resident(acq, **args)
+            return value, x
+        lo, hi = pdist.shard_range(n_warmup, rank, size)
+        value, index, _ = h.sweep_resident_range(lo, hi - lo, acq, **args)
+        value, index = pdist.merge_best(value, index if hi > lo else -1, device=pdist.torch.device('cuda', h.device))
+        return value, h.candidates_get(index, 1, h.d)[0]
 
     def compute(self, x, y_max):
         """Acquisition values of the rows of x (acquisition_function.py:62-68)."""
@@ -183,7 +198,14 @@ class UtilityFunction(object):
         h = self.gaussian_process.handle
         max_acq, x_max, x_seeds = self._warmup(h, acq, args, bounds, n_warmup, n_iter)
         if n_iter > 0:
-            xs, values, success = h.refine(x_seeds, bounds, acq, **args)
+            rank, size = pdist.world()
+            if size > 1 and os.environ.get('PLX_BO_DISTRIBUTED', '1') != '0':
+                # seeds are dealt round-robin to the ranks, results gathered back in seed order
+                xs, values, success = h.refine(x_seeds[rank::size], bounds, acq, **args)
+                xs, values, success = pdist.gather_refined(xs, values, success, n_iter,
+                                                           device=pdist.torch.device('cuda', h.device))
+            else:
+                xs, values, success = h.refine(x_seeds, bounds, acq, **args)
             for x_ref, value, ok in zip(xs, values, success):
                 if not ok:
                     continue

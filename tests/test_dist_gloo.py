@@ -57,11 +57,18 @@ def _worker(rank, world, port, ys, out):
     else:
         v, i = pd.merge_best(float('nan'), -1)
     rv, ri = pd.merge_refined(float(rank == 0) * 2.0 + 1.0 * (rank == 1) * 2.0, rank)
+    # refinement results of 5 seeds dealt round-robin: rank r holds seeds r, r + 2, ...
+    seeds = np.arange(5)
+    mine = seeds[rank::world]
+    gx, gv, gs = pd.gather_refined(np.stack([mine * 1.0, mine * 10.0], axis=1), mine * 0.5, mine % 2 == 0, 5)
+    assert np.array_equal(gx, np.stack([seeds * 1.0, seeds * 10.0], axis=1))
+    assert np.array_equal(gv, seeds * 0.5) and np.array_equal(gs, seeds % 2 == 0)
+    assert pd.world() == (rank, world)
     out[rank] = (v, i, rv, ri)
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize('case', ['plain', 'nan', 'tie', 'short'])
+@pytest.mark.parametrize('case', ['nan', 'tie', 'short'])
 def test_two_rank_merge_over_gloo(case):
     rs = np.random.RandomState(1)
     ys = rs.randn(1001)
