@@ -79,7 +79,7 @@ class DeviceGaussianProcess(object):
         # (sklearn _gpr.py:329-333); same calls here so the stream stays aligned
         lo, hi = np.array([THETA_BOUNDS[0]]), np.array([THETA_BOUNDS[1]])
         restarts = [float(self.random_state.uniform(lo, hi)[0]) for _ in range(self.n_restarts_optimizer)]
-        theta, lml, per_run = self.handle.fit(np.log(self.length_scale), restarts, THETA_BOUNDS)
+        theta, lml, per_run = self._fit_runs(np.log(self.length_scale), restarts)
         self.theta_ = theta
         self.length_scale_ = float(np.exp(theta))
         self.log_marginal_likelihood_value_ = lml
@@ -87,6 +87,37 @@ class DeviceGaussianProcess(object):
         self.X_train_, self.y_train_ = X, y
         self.fitted = True
         return self
+
+    def _fit_runs(self, theta0, restarts):
+        """All optimiser runs (the configured length scale first, then the restarts).  Under
+        torch.distributed the runs are dealt round-robin to the ranks, each rank advances its share in
+        lock step on its GPU, one all-gather of {theta*, LML*} per run follows, and every rank rebuilds
+        the posterior state at the winning theta locally (cheaper than shipping the n x n factor).
+        The winner is the first maximum of LML in run order, as numpy.argmin over sklearn's list of
+        -LML values (sklearn _gpr.py:336-337)."""
+        rank, size = pdist.world()
+        starts = [float(theta0)] + [float(t) for t in restarts]
+        if size == 1 or len(starts) == 1 or os.environ.get('PLX_BO_DISTRIBUTED', '1') == '0':
+            return self.handle.fit(theta0, restarts, THETA_BOUNDS)
+        mine = starts[rank::size]
+        if mine:
+            _, _, part = self.handle.fit(mine[0], mine[1:], THETA_BOUNDS)
+        else:
+            part = np.zeros((0, 4))
+        per = (len(starts) + size - 1) // size
+        torch = pdist.torch
+        dev = torch.device('cuda', self.handle.device)
+        pack = torch.full((per, 4), float('nan'), dtype=torch.float64, device=dev)
+        if len(part):
+            pack[:len(part)] = torch.from_numpy(np.ascontiguousarray(part)).to(dev)
+        out = torch.empty(size * per, 4, dtype=torch.float64, device=dev)
+        pdist.dist.all_gather_into_tensor(out, pack)
+        out = out.cpu().numpy().reshape(size, per, 4)
+        per_run = np.array([out[i % size, i // size] for i in range(len(starts))])
+        best = int(np.argmin(-per_run[:, 2]))
+        theta = float(per_run[best, 1])
+        self.handle.set_theta(theta)
+        return theta, float(per_run[best, 2]), per_run
 
     @property
     def L_(self):

@@ -23,7 +23,7 @@ cfg = HPTuningConfig.from_dict({
     'bo': {'n_iterations': 5, 'n_initial_trials': 5, 'metric': {'name': 'm', 'optimization': 'maximize'},
            'utility_function': {'acquisition_function': 'ei', 'eps': 0.0, 'n_warmup': N, 'n_iter': 7,
                                 'gaussian_process': {'kernel': 'matern', 'length_scale': 1.0, 'nu': 2.5,
-                                                     'n_restarts_optimizer': 2}}},
+                                                     'n_restarts_optimizer': 5}}},
     'matrix': {k: {'uniform': [0, 1]} for k in keys}})
 configs = [dict(zip(keys, row.tolist())) for row in X]
 
