@@ -382,81 +382,106 @@ __global__ void __launch_bounds__(256) potf2_inv_kernel(BatchPtrs bp, int k, int
     S[i * POTF_LD + j] = A[i * ld + j];
   }
   __shared__ int bad;
+  __shared__ double colbuf[2][128];
   if (tid == 0) bad = 0;
-  const int lane = tid & 31, warp = tid >> 5;
   // rows / columns beyond the observations are identity padding: the factor and its inverse are the
   // identity there, so every loop stops at the last real row of this block
   const int m = min(128, max(0, n - k * 128));
+  // Register-tiled right-looking factorisation: thread (ti, tc) keeps the 8 x 8 strided sub-block
+  // A[ti + 16 a][tc + 16 b] in registers for the whole factorisation; per column only the column
+  // itself crosses shared memory (double-buffered, one barrier per column).  Entries left of / above
+  // the current column are dead and receive harmless garbage updates.
+  const int tc = tid & 15, ti = tid >> 4;
+  double acc[8][8];
+  __syncthreads();
+#pragma unroll
+  for (int a = 0; a < 8; ++a)
+#pragma unroll
+    for (int q = 0; q < 8; ++q) acc[a][q] = S[(ti + 16 * a) * POTF_LD + tc + 16 * q];
   for (int j = 0; j < m; ++j) {
-    __syncthreads();                    // trailing update of column j-1 is complete
-    double ajj = S[j * POTF_LD + j];    // stays untouched during this step (dl holds the root)
+    const int bj = j >> 4;
+    double* cb = colbuf[j & 1];
+    if (tc == (j & 15)) {
+#pragma unroll
+      for (int a = 0; a < 8; ++a) {
+        double v = acc[a][0];
+#pragma unroll
+        for (int q = 1; q < 8; ++q) v = (q == bj) ? acc[a][q] : v;
+        cb[ti + 16 * a] = v;
+      }
+    }
+    __syncthreads();
+    double ajj = cb[j];
     if (!(ajj > 0.0)) {                 // non-positive or NaN pivot: not positive definite
       if (tid == 0 && bad == 0) bad = k * 128 + j + 1;
       ajj = 1.0;
     }
-    const double ljj = sqrt(ajj);
-    const double inv = 1.0 / ljj;       // LAPACK dpotf2 scales the column by the reciprocal too
-    if (tid == 0) { dl[j] = ljj; wdiag[j] = inv; }
-    for (int i = j + 1 + tid; i < m; i += 256) S[i * POTF_LD + j] *= inv;
-    __syncthreads();
-    // trailing update of the lower triangle: S[i][c] -= S[i][j] * S[c][j], j < c <= i
-    // (loads of a whole batch are issued before its stores: the compiler may not move a load across
-    //  a store to the same array, and one shared-memory round trip per element made this loop the
-    //  slowest part of the factorisation)
-    for (int i = j + 1 + (tid >> 4); i < m; i += 16) {
-      const double lij = S[i * POTF_LD + j];
-      const int c0 = j + 1 + (tid & 15);
-      double sv[8], lv[8];
+    // root and reciprocal root from one hardware seed and a coupled Newton step (<= 2 ulp): the
+    // pivot -> sqrt -> divide chain is on the critical path of every column
+    double y0;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y0) : "d"(ajj));
+    const double e0 = fma(ajj, -(y0 * y0), 1.0);
+    double inv = fma(fma(e0, 0.375, 0.5), y0 * e0, y0);
+    double ljj = ajj * inv;
+    ljj = fma(fma(ljj, -ljj, ajj), 0.5 * inv, ljj);
+    inv = fma(fma(-ljj, inv, 1.0), inv, inv);            // 1 / ljj (LAPACK dpotf2 scales by the reciprocal too)
+    double li[8], lc[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int c = c0 + 16 * u;
-        const bool on = c <= i;
-        sv[u] = on ? S[i * POTF_LD + c] : 0.0;
-        lv[u] = on ? S[c * POTF_LD + j] : 0.0;
-      }
+    for (int a = 0; a < 8; ++a) { li[a] = cb[ti + 16 * a] * inv; lc[a] = cb[tc + 16 * a] * inv; }
+    if (tc == (j & 15)) {
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int c = c0 + 16 * u;
-        if (c <= i) S[i * POTF_LD + c] = fma(-lij, lv[u], sv[u]);
-      }
+      for (int a = 0; a < 8; ++a) { const int i = ti + 16 * a; if (i > j) S[i * POTF_LD + j] = li[a]; }
     }
+    if (tid == 0) { dl[j] = ljj; wdiag[j] = inv; }
+#pragma unroll
+    for (int a = 0; a < 8; ++a)
+#pragma unroll
+      for (int q = 0; q < 8; ++q) acc[a][q] = fma(-li[a], lc[q], acc[a][q]);
   }
   __syncthreads();
   if (tid >= m && tid < 128) { dl[tid] = 1.0; wdiag[tid] = 1.0; }
-  // W = L^-1 by forward substitution on all columns of the identity at once (right-looking):
-  // W[i][c] (i > c) lives in the strict upper triangle at S[c][i], its diagonal in wdiag.
+  // strict upper triangle will receive W^T; padding rows of L are zero
   for (int e = tid; e < 128 * 128; e += 256) {
     const int r = e >> 7, c = e & 127;
     if (c > r) S[r * POTF_LD + c] = 0.0;
-    else if (c < r && r >= m) S[r * POTF_LD + c] = 0.0;       // padding rows of L
+    else if (c < r && r >= m) S[r * POTF_LD + c] = 0.0;
   }
   __syncthreads();
   if (tid < 128) S[tid * POTF_LD + tid] = dl[tid];
+  // W = L^-1 by right-looking forward substitution on all columns of the identity at once, same
+  // register tiling: acc[a][q] = W[ti + 16 a][tc + 16 q]; per step only the finished row crosses
+  // shared memory.  W[j][c] (c < j) is parked at S[c][j], the diagonal in wdiag.
+#pragma unroll
+  for (int a = 0; a < 8; ++a)
+#pragma unroll
+    for (int q = 0; q < 8; ++q) acc[a][q] = (ti + 16 * a == tc + 16 * q) ? 1.0 : 0.0;
   for (int j = 0; j < m; ++j) {
-    __syncthreads();
-    const double wjj = wdiag[j];
-    // row j of W becomes final: W[j][c] = acc / L[j][j]
-    for (int c = tid; c < j; c += 256) S[c * POTF_LD + j] *= wjj;
-    __syncthreads();
-    // rows below: W[i][c] -= L[i][j] * W[j][c] for c <= j  (lane <-> i, warp <-> c)
-    for (int i = j + 1 + lane; i < m; i += 32) {
-      const double lij = S[i * POTF_LD + j];
-      for (int cb = warp; cb <= j; cb += 64) {
-        double sv[8], wv[8];
+    const int aj = j >> 4;
+    double* rb = colbuf[j & 1];
+    __syncthreads();                    // everyone is done with the buffer of step j - 2 ... and S reads
+    if (ti == (j & 15)) {
+      const double wjj = wdiag[j];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const int c = cb + 8 * u;
-          const bool on = c <= j;
-          sv[u] = on ? S[c * POTF_LD + i] : 0.0;
-          wv[u] = on ? ((c == j) ? wjj : S[c * POTF_LD + j]) : 0.0;
-        }
+      for (int q = 0; q < 8; ++q) {
+        double v = acc[0][q];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const int c = cb + 8 * u;
-          if (c <= j) S[c * POTF_LD + i] = fma(-lij, wv[u], sv[u]);
-        }
+        for (int a = 1; a < 8; ++a) v = (a == aj) ? acc[a][q] : v;
+        rb[tc + 16 * q] = v * wjj;
       }
     }
+    __syncthreads();
+    double wr[8], lcol[8];
+#pragma unroll
+    for (int a = 0; a < 8; ++a) {
+      wr[a] = rb[tc + 16 * a];
+      const int i = ti + 16 * a;
+      lcol[a] = (i > j && i < m) ? S[i * POTF_LD + j] : 0.0;
+    }
+#pragma unroll
+    for (int a = 0; a < 8; ++a)
+#pragma unroll
+      for (int q = 0; q < 8; ++q) acc[a][q] = fma(-lcol[a], wr[q], acc[a][q]);
+    if (tid < j) S[tid * POTF_LD + j] = rb[tid];
   }
   __syncthreads();
   double* Lo = bp.L + b * bp.mat_stride + (static_cast<size_t>(k) * 128) * ld + k * 128;
