@@ -343,10 +343,10 @@ extern "C" int plx_gp_lml(plx_bo_handle h, const double* thetas, int B, double* 
   return eval_lml(h, thetas, B, lml, grad);
 }
 
-static int make_map(plx_bo* h, CUtensorMap* map, double* base, size_t rows, size_t cols) {
+static int make_map(plx_bo* h, CUtensorMap* map, double* base, size_t rows, size_t cols, int box_rows = TILE) {
   cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
   cuuint64_t strides[1] = {static_cast<cuuint64_t>(cols) * 8};
-  cuuint32_t box[2] = {KCH, TILE};
+  cuuint32_t box[2] = {KCH, static_cast<cuuint32_t>(box_rows)};
   cuuint32_t estr[2] = {1, 1};
   const CUresult r = h->encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, base, dims, strides, box, estr,
                                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
