@@ -87,3 +87,41 @@ def test_full_size_interpolation_property(handle):
     _, alpha, _ = handle.get_state(want_L=False)
     assert np.abs(mean - (y[:512] - 1e-10 * alpha[:512])).max() <= 1e-9 * max(1.0, np.abs(y).max())
     assert std.max() <= 1e-4                                       # sqrt(jitter-level variance)
+
+
+def test_sweep_beyond_2048_observations(handle):
+    """n_obs = 3000 (not a multiple of the 128-row blocks), d = 16, against the oracle."""
+    X, y, _ = synthetic_problem(3000, 16)
+    theta = 0.9
+    handle.set_data(X, y, G.KERNEL_MATERN, 2.5)
+    handle.set_theta(theta)
+    L, a = G.posterior_state(X, y, theta, G.KERNEL_MATERN, 2.5)
+    xc = np.random.RandomState(8).uniform(0, 1, (777, 16))
+    val, idx, _, mean, std, acq = handle.sweep(xc, G.ACQ_EI, float(y.max()), eps=0.0, dump=True)
+    m, s = G.predict(xc, X, L, a, theta, G.KERNEL_MATERN, 2.5)
+    ref = G.acquisition(m, s, G.ACQ_EI, float(y.max()), 0.0, 0.0)
+    assert np.abs(mean - m).max() <= 1e-9 * max(1.0, np.abs(m).max())
+    assert np.abs(std ** 2 - s ** 2).max() <= 1e-9
+    assert idx == int(np.argmax(ref))
+
+
+def test_host_sweep_across_chunk_boundaries_matches_resident_sweep(handle):
+    """The host-buffer entry point streams candidates in double-buffered chunks (a whole number of
+    128-candidate waves, ~64 MiB); N = chunk + 1 exercises the ragged last chunk and the running
+    arg-max across chunks."""
+    X = np.array([[0.1], [0.35], [0.5], [0.8], [0.95]])
+    y = np.array([0.2, 0.9, 0.1, 0.7, 0.3])
+    handle.set_data(X, y, G.KERNEL_MATERN, 1.5)
+    handle.set_theta(np.log(0.2))
+    wave = 128 * 148
+    chunk = wave * ((64 << 20) // (8 * 1 * wave))
+    N = chunk + 1
+    xc = np.random.RandomState(2).uniform(0, 1, (N, 1))
+    xc[-1, 0] = 0.35                      # the best candidate sits alone in the last chunk
+    val, idx, x = handle.sweep(xc, G.ACQ_UCB, 0.9, kappa=0.0)
+    handle.candidates_set(xc)
+    val2, idx2, x2 = handle.sweep_resident(G.ACQ_UCB, 0.9, kappa=0.0)
+    assert (val, idx) == (val2, idx2) and np.array_equal(x, x2)
+    L, a = G.posterior_state(X, y, np.log(0.2), G.KERNEL_MATERN, 1.5)
+    m, _ = G.predict(xc[-5:], X, L, a, np.log(0.2), G.KERNEL_MATERN, 1.5)
+    assert val >= m.max() - 1e-12
