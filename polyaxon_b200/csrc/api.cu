@@ -63,6 +63,9 @@ struct plx_bo {
   // resident candidate matrix (iteration-invariant for a seeded group)
   double* d_resident = nullptr; size_t resident_cap = 0; long long resident_n = 0; int resident_d = 0;
 
+  // small persistent scratch (generator state + bounds of the device draw; verification probe)
+  double* d_misc = nullptr; size_t misc_cap = 0;
+
   // refinement workspace
   int rf_cap_s = 0, rf_cap_npad = 0, rf_cap_d = 0;
   double *rf_kv = nullptr, *rf_kp = nullptr, *rf_v = nullptr, *rf_w = nullptr, *rf_vec = nullptr,
@@ -202,7 +205,7 @@ extern "C" void plx_bo_destroy(plx_bo_handle h) {
                   h->d_alpha, h->d_partial, h->d_lml, h->d_grad, h->d_info, h->dZ, h->d_alpha_state, h->dKs, h->dXt,
                   h->d_blk_val, h->d_blk_idx, h->d_best_val, h->d_best_idx, h->dcand[0], h->dcand[1],
                   h->d_out[0], h->d_out[1], h->d_out[2], h->rf_kv, h->rf_kp, h->rf_v, h->rf_w, h->rf_vec,
-                  h->rf_bounds, h->rf_val, h->rf_grad, h->rf_sc, h->rf_active, h->d_resident};
+                  h->rf_bounds, h->rf_val, h->rf_grad, h->rf_sc, h->rf_active, h->d_resident, h->d_misc};
   for (void* p : ptrs) if (p) cudaFree(p);
   for (int i = 0; i < 2; ++i) { if (h->ev_copy[i]) cudaEventDestroy(h->ev_copy[i]); if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]); }
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
@@ -266,7 +269,7 @@ static int ensure_batch(plx_bo* h, int B) {
   CK(cudaMalloc(&h->bp.L, sizeof(double) * mat * cap));
   CK(cudaMalloc(&h->bp.U, sizeof(double) * mat * cap));
   CK(cudaMalloc(&h->bp.W, sizeof(double) * blk * cap));
-  CK(cudaMalloc(&h->bp.T, sizeof(double) * blk * cap));
+  CK(cudaMalloc(&h->bp.T, sizeof(double) * mat * cap));
   CK(cudaMalloc(&h->d_thetas, sizeof(double) * cap));
   CK(cudaMalloc(&h->d_logdet, sizeof(double) * cap));
   CK(cudaMalloc(&h->d_w, sizeof(double) * h->npad * cap));
@@ -300,10 +303,11 @@ static int launch_lml(plx_bo* h, int B, bool want_grad) {
       LAUNCH_CHECK("chol_syrk_kernel");
     }
   }
-  for (int j = 1; j < nb; ++j) {
-    trtri_t_kernel<<<dim3(j, B), 256, GEMM_SMEM, st>>>(h->bp, j, npad);
+  for (int s = 1; s < nb; s *= 2) {               // recursive doubling: 2 launches per level
+    const int tiles = ((nb + 2 * s - 1) / (2 * s)) * s * s;
+    trtri_t_kernel<<<dim3(tiles, B), 256, GEMM_SMEM, st>>>(h->bp, s, nb, npad);
     LAUNCH_CHECK("trtri_t_kernel");
-    trtri_u_kernel<<<dim3(j, B), 256, GEMM_SMEM, st>>>(h->bp, j, npad);
+    trtri_u_kernel<<<dim3(tiles, B), 256, GEMM_SMEM, st>>>(h->bp, s, nb, npad);
     LAUNCH_CHECK("trtri_u_kernel");
   }
   uty_kernel<<<dim3(npad / 32, B), 256, 0, st>>>(h->bp, h->dy, npad, h->d_w);
@@ -599,10 +603,11 @@ extern "C" int plx_candidates_draw_mt19937(plx_bo_handle h, const unsigned* key,
   h->resident_n = 0;
   int r;
   if ((r = ensure(h, h->d_resident, h->resident_cap, static_cast<size_t>(std::max<long long>(N, 1)) * d)) != PLX_OK) return r;
-  unsigned* d_key = nullptr; double* d_lr = nullptr; int* d_pos = nullptr;
-  CK(cudaMalloc(&d_key, sizeof(unsigned) * 1248));
-  CK(cudaMalloc(&d_lr, sizeof(double) * 2 * d));
-  CK(cudaMalloc(&d_pos, sizeof(int)));
+  // scratch layout (doubles): [0, 2d) low | range, then 1248 words of generator state, then the position
+  if ((r = ensure(h, h->d_misc, h->misc_cap, static_cast<size_t>(2 * d) + 640)) != PLX_OK) return r;
+  double* d_lr = h->d_misc;
+  unsigned* d_key = reinterpret_cast<unsigned*>(h->d_misc + 2 * d);
+  int* d_pos = reinterpret_cast<int*>(d_key + 1248);
   CK(cudaMemcpyAsync(d_key, key, sizeof(unsigned) * 624, cudaMemcpyHostToDevice, h->stream));
   CK(cudaMemcpyAsync(d_lr, low, sizeof(double) * d, cudaMemcpyHostToDevice, h->stream));
   CK(cudaMemcpyAsync(d_lr + d, range, sizeof(double) * d, cudaMemcpyHostToDevice, h->stream));
@@ -612,7 +617,6 @@ extern "C" int plx_candidates_draw_mt19937(plx_bo_handle h, const unsigned* key,
   CK(cudaMemcpyAsync(key_out, d_key + 624, sizeof(unsigned) * 624, cudaMemcpyDeviceToHost, h->stream));
   CK(cudaMemcpyAsync(pos_out, d_pos, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
-  CK(cudaFree(d_key)); CK(cudaFree(d_lr)); CK(cudaFree(d_pos));
   h->resident_n = N; h->resident_d = d;
   return PLX_OK;
 }
@@ -652,16 +656,14 @@ extern "C" int plx_kernel_values(plx_bo_handle h, int kernel, double nu, const d
   int kind;
   if (kernel_kind(kernel, nu, &kind) != PLX_OK || kind == K_GEN) return fail(h, PLX_ERR_UNSUPPORTED, "kernel_values: closed-form kernels only");
   CK(cudaSetDevice(h->device));
-  double *d_in = nullptr, *d_out = nullptr;
-  CK(cudaMalloc(&d_in, sizeof(double) * n));
-  CK(cudaMalloc(&d_out, sizeof(double) * n));
+  int r;
+  if ((r = ensure(h, h->d_misc, h->misc_cap, static_cast<size_t>(2) * n)) != PLX_OK) return r;
+  double *d_in = h->d_misc, *d_out = h->d_misc + n;
   CK(cudaMemcpyAsync(d_in, r2, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
   kern_value_probe_kernel<<<(n + 255) / 256, 256, 0, h->stream>>>(d_in, n, kind, d_out);
   LAUNCH_CHECK("kern_value_probe_kernel");
   CK(cudaMemcpyAsync(out, d_out, sizeof(double) * n, cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
-  CK(cudaFree(d_in));
-  CK(cudaFree(d_out));
   return PLX_OK;
 }
 

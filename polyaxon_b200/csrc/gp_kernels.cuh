@@ -9,11 +9,11 @@
 //
 // HBM layout per batch member b (npad = n rounded up to 128, leading dimension ld = npad):
 //   A[b]  npad x ld  K + jitter*I (symmetric, identity in the padding); trailing updates in place;
-//                    reused for K^-1 once the factor exists
+//                    then Z = L^-1 (lower) during the triangular inverse, finally K^-1
 //   L[b]  npad x ld  lower Cholesky factor (row-major)
 //   U[b]  npad x ld  U = L^-T, upper triangular (row-major), i.e. U[c][r] = (L^-1)[r][c]
 //   W[b]  nb x 128 x 128  inverses of the diagonal blocks of L (lower)
-//   T[b]  nb x 128 x 128  scratch for the triangular-inverse recurrence
+//   T[b]  npad x ld  scratch of the triangular inverse
 #pragma once
 #include "mma_f64.cuh"
 #include <math.h>
@@ -487,6 +487,8 @@ __global__ void __launch_bounds__(256) potf2_inv_kernel(BatchPtrs bp, int k, int
   double* Lo = bp.L + b * bp.mat_stride + (static_cast<size_t>(k) * 128) * ld + k * 128;
   double* Uo = bp.U + b * bp.mat_stride + (static_cast<size_t>(k) * 128) * ld + k * 128;
   double* Wo = bp.W + b * bp.blk_stride + static_cast<size_t>(k) * 128 * 128;
+  // the block's inverse also goes where its input came from: A doubles as Z = L^-1 (lower) from here on
+  double* Zo = bp.A + b * bp.mat_stride + (static_cast<size_t>(k) * 128) * ld + k * 128;
   for (int e = tid; e < 128 * 128; e += 256) {
     const int i = e >> 7, j = e & 127;
     double l, w;
@@ -495,6 +497,7 @@ __global__ void __launch_bounds__(256) potf2_inv_kernel(BatchPtrs bp, int k, int
     else { l = 0.0; w = 0.0; }
     Lo[i * ld + j] = l;
     Wo[i * 128 + j] = w;
+    Zo[i * ld + j] = w;
     // U_kk = W^T: element (i, j) of U is W[j][i]
     double u;
     if (j > i) u = S[i * POTF_LD + j]; else if (i == j) u = wdiag[i]; else u = 0.0;
@@ -573,30 +576,60 @@ __global__ void __launch_bounds__(256, 1) chol_syrk_kernel(BatchPtrs bp, int k, 
   store_tile<false, true>(acc, bp.A + b * bp.mat_stride + (static_cast<size_t>(i) * 128) * ld + j * 128, ld);
 }
 
-// triangular inverse, step j, part 1: T[k] = sum_{m in [k*128, j*128)} U[k-rows][m] * L[j-rows][m]
-__global__ void __launch_bounds__(256, 1) trtri_t_kernel(BatchPtrs bp, int j, int npad) {
-  extern __shared__ unsigned char smem_raw[];
-  unsigned char* smem = align1k(smem_raw);
-  const int b = blockIdx.y, k = blockIdx.x;
-  const size_t ld = npad;
-  const double* Uk = bp.U + b * bp.mat_stride + (static_cast<size_t>(k) * 128) * ld;
-  const double* Lj = bp.L + b * bp.mat_stride + (static_cast<size_t>(j) * 128) * ld;
-  WarpAcc acc; acc.zero();
-  mainloop_nt(acc, Uk, ld, Lj, ld, k * 128, j * 128, smem);
-  store_tile<false, false>(acc, bp.T + b * bp.blk_stride + static_cast<size_t>(k) * 128 * 128, 128);
+// Triangular inverse by recursive doubling.  With L = [[L11, 0], [L21, L22]] and both diagonal
+// inverses known, the off-diagonal block of the inverse is Z21 = -Z22 L21 Z11, i.e. for U = L^-T
+//   U12 = -U11 L21^T U22.
+// Level s (in 128-blocks) joins every aligned pair of s-block inverses into a 2s-block inverse:
+// two launches per level (T = U11 L21^T, then U12 = -T Z22^T), log2(nb) levels, every tile of a
+// level in parallel.  Both U (upper) and Z = U^T (lower, kept in A's storage, which the
+// factorisation no longer needs) are maintained so that every product is K-major on both sides.
+// T is a full npad x ld scratch matrix per batch member.
+__device__ __forceinline__ bool trtri_tile(int t, int s, int nb, int& left0, int& right0, int& a, int& c) {
+  const int p = t / (s * s), rem = t - p * s * s;
+  left0 = p * 2 * s; right0 = left0 + s;
+  if (right0 >= nb) return false;
+  a = rem / s; c = rem - a * s;
+  return c < min(s, nb - right0);
 }
 
-// part 2: U[k][j] = -T[k] * W_j^T
-__global__ void __launch_bounds__(256, 1) trtri_u_kernel(BatchPtrs bp, int j, int npad) {
+// part 1: T[left0+a][right0+c] = sum_{m in left block, m >= a} U[left0+a][m] * L[right0+c][m]^T
+__global__ void __launch_bounds__(256, 1) trtri_t_kernel(BatchPtrs bp, int s, int nb, int npad) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = align1k(smem_raw);
-  const int b = blockIdx.y, k = blockIdx.x;
+  const int b = blockIdx.y;
+  int left0, right0, a, c;
+  if (!trtri_tile(blockIdx.x, s, nb, left0, right0, a, c)) return;
   const size_t ld = npad;
-  const double* Tk = bp.T + b * bp.blk_stride + static_cast<size_t>(k) * 128 * 128;
-  const double* Wj = bp.W + b * bp.blk_stride + static_cast<size_t>(j) * 128 * 128;
+  const double* Ua = bp.U + b * bp.mat_stride + (static_cast<size_t>(left0 + a) * 128) * ld;
+  const double* Lc = bp.L + b * bp.mat_stride + (static_cast<size_t>(right0 + c) * 128) * ld;
   WarpAcc acc; acc.zero();
-  mainloop_nt(acc, Tk, 128, Wj, 128, 0, 128, smem);
-  store_tile<true, false>(acc, bp.U + b * bp.mat_stride + (static_cast<size_t>(k) * 128) * ld + j * 128, ld);
+  mainloop_nt(acc, Ua, ld, Lc, ld, (left0 + a) * 128, (left0 + s) * 128, smem);
+  store_tile<false, false>(acc, bp.T + b * bp.mat_stride + (static_cast<size_t>(left0 + a) * 128) * ld + (right0 + c) * 128, ld);
+}
+
+// part 2: U[left0+a][right0+c] = -sum_{q in right block, q <= c} T[left0+a][q] * Z[right0+c][q]^T, and Z = U^T
+__global__ void __launch_bounds__(256, 1) trtri_u_kernel(BatchPtrs bp, int s, int nb, int npad) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = align1k(smem_raw);
+  const int b = blockIdx.y;
+  int left0, right0, a, c;
+  if (!trtri_tile(blockIdx.x, s, nb, left0, right0, a, c)) return;
+  const size_t ld = npad;
+  const double* Ta = bp.T + b * bp.mat_stride + (static_cast<size_t>(left0 + a) * 128) * ld;
+  const double* Zc = bp.A + b * bp.mat_stride + (static_cast<size_t>(right0 + c) * 128) * ld;
+  WarpAcc acc; acc.zero();
+  mainloop_nt(acc, Ta, ld, Zc, ld, right0 * 128, (right0 + c + 1) * 128, smem);
+  store_tile<true, false>(acc, bp.U + b * bp.mat_stride + (static_cast<size_t>(left0 + a) * 128) * ld + (right0 + c) * 128, ld);
+  // transposed copy into Z[right0+c][left0+a]
+  double* Zt = bp.A + b * bp.mat_stride + (static_cast<size_t>(right0 + c) * 128) * ld + (left0 + a) * 128;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int mf = 0; mf < 4; ++mf)
+#pragma unroll
+    for (int nf = 0; nf < 8; ++nf)
+#pragma unroll
+      for (int e = 0; e < 2; ++e)
+        Zt[static_cast<size_t>(acc_col(warp, lane, nf, e)) * ld + acc_row(warp, lane, mf)] = -acc.c[mf][nf][e];
 }
 
 // K^-1 = U U^T on the lower 128-tiles (diagonal tiles in full), written over A.
