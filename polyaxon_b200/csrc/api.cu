@@ -37,7 +37,8 @@ struct plx_bo {
   int bcap = 0, wnpad = 0;
   BatchPtrs bp{};
   double *d_thetas = nullptr, *d_logdet = nullptr, *d_w = nullptr, *d_alpha = nullptr, *d_partial = nullptr,
-         *d_lml = nullptr, *d_grad = nullptr;
+         *d_lml = nullptr, *d_grad = nullptr, *d_xs = nullptr;
+  size_t xs_cap = 0;
   int* d_info = nullptr;
   int ntri = 0;
 
@@ -202,7 +203,7 @@ extern "C" void plx_bo_destroy(plx_bo_handle h) {
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
   void* ptrs[] = {h->dX, h->dy, h->bp.A, h->bp.L, h->bp.U, h->bp.W, h->bp.T, h->d_thetas, h->d_logdet, h->d_w,
-                  h->d_alpha, h->d_partial, h->d_lml, h->d_grad, h->d_info, h->dZ, h->d_alpha_state, h->dKs, h->dXt,
+                  h->d_alpha, h->d_partial, h->d_lml, h->d_grad, h->d_xs, h->d_info, h->dZ, h->d_alpha_state, h->dKs, h->dXt,
                   h->d_blk_val, h->d_blk_idx, h->d_best_val, h->d_best_idx, h->dcand[0], h->dcand[1],
                   h->d_out[0], h->d_out[1], h->d_out[2], h->rf_kv, h->rf_kp, h->rf_v, h->rf_w, h->rf_vec,
                   h->rf_bounds, h->rf_val, h->rf_grad, h->rf_sc, h->rf_active, h->d_resident, h->d_misc};
@@ -289,8 +290,15 @@ static int launch_lml(plx_bo* h, int B, bool want_grad) {
   const int npad = h->npad, nb = h->nb, n = h->n;
   CK(cudaMemsetAsync(h->d_logdet, 0, sizeof(double) * B, st));
   CK(cudaMemsetAsync(h->d_info, 0, sizeof(int) * B, st));
-  kmat_kernel<0><<<dim3(npad / 32, npad / 32, B), 256, 0, st>>>(h->dX, n, h->d, npad, h->d_thetas, h->kind,
-                                                               h->mg, h->jitter, h->bp, nullptr, nullptr, 0);
+  {
+    int r;
+    if ((r = ensure(h, h->d_xs, h->xs_cap, static_cast<size_t>(B) * n * h->d)) != PLX_OK) return r;
+  }
+  scale_x_batch_kernel<<<dim3((n * h->d + 255) / 256, B), 256, 0, st>>>(h->dX, n * h->d, h->d_thetas, h->d_xs);
+  LAUNCH_CHECK("scale_x_batch_kernel");
+  const int t32 = npad / 32;
+  kmat_kernel<0><<<dim3(t32 * (t32 + 1) / 2, 1, B), 256, 0, st>>>(h->d_xs, n, h->d, npad, h->kind, h->mg, h->jitter,
+                                                                 h->bp, nullptr, nullptr, 0);
   LAUNCH_CHECK("kmat_kernel");
   for (int k = 0; k < nb; ++k) {
     potf2_inv_kernel<<<B, 256, POTF_SMEM, st>>>(h->bp, k, n, npad, h->d_logdet, h->d_info);
@@ -317,8 +325,8 @@ static int launch_lml(plx_bo* h, int B, bool want_grad) {
   if (want_grad) {
     kinv_kernel<<<dim3(nb * (nb + 1) / 2, B), 256, GEMM_SMEM, st>>>(h->bp, npad);
     LAUNCH_CHECK("kinv_kernel");
-    kmat_kernel<1><<<dim3(h->ntri, 1, B), 256, 0, st>>>(h->dX, n, h->d, npad, h->d_thetas, h->kind, h->mg, h->jitter,
-                                                       h->bp, h->d_alpha, h->d_partial, h->ntri);
+    kmat_kernel<1><<<dim3(h->ntri, 1, B), 256, 0, st>>>(h->d_xs, n, h->d, npad, h->kind, h->mg, h->jitter, h->bp,
+                                                       h->d_alpha, h->d_partial, h->ntri);
     LAUNCH_CHECK("kmat_kernel<grad>");
   }
   lml_finalize_kernel<<<B, 256, 0, st>>>(h->dy, h->d_alpha, h->d_logdet, h->d_info,

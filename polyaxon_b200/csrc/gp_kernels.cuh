@@ -281,19 +281,26 @@ struct BatchPtrs {
 // ---------------------------------------------------------------------------------------------
 constexpr int DCH = 32;
 
+// X / length_scale for every theta of the batch: Xs[b][n][d] (the division sklearn does, done once)
+__global__ void scale_x_batch_kernel(const double* __restrict__ X, int nd, const double* __restrict__ thetas,
+                                     double* __restrict__ Xs) {
+  const int b = blockIdx.y, e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e < nd) Xs[static_cast<size_t>(b) * nd + e] = X[e] / exp(thetas[b]);
+}
+
 template <int MODE>
-__global__ void __launch_bounds__(256) kmat_kernel(const double* __restrict__ X, int n, int d, int npad,
-                                                   const double* __restrict__ thetas, int kind, MaternGen mg,
-                                                   double jitter, BatchPtrs bp, const double* __restrict__ alpha,
+__global__ void __launch_bounds__(256) kmat_kernel(const double* __restrict__ Xs, int n, int d, int npad,
+                                                   int kind, MaternGen mg, double jitter, BatchPtrs bp,
+                                                   const double* __restrict__ alpha,
                                                    double* __restrict__ partial, int ntri) {
   __shared__ double Xi[32][DCH + 1];
   __shared__ double Xj[32][DCH + 1];
   __shared__ double red[8];
   const int b = blockIdx.z;
+  // linear index over the lower triangle of 32-tiles: p = ti*(ti+1)/2 + tj.  Only the lower triangle
+  // of K is ever read (factorisation, panels and trailing updates all work on i >= j).
   int ti, tj;
-  if (MODE == 0) { ti = blockIdx.y; tj = blockIdx.x; }
-  else {
-    // linear index over the lower triangle of 32-tiles: p = ti*(ti+1)/2 + tj
+  {
     const int p = blockIdx.x;
     ti = static_cast<int>((sqrt(8.0 * p + 1.0) - 1.0) * 0.5);
     while ((ti + 1) * (ti + 2) / 2 <= p) ++ti;
@@ -301,7 +308,7 @@ __global__ void __launch_bounds__(256) kmat_kernel(const double* __restrict__ X,
     tj = p - ti * (ti + 1) / 2;
   }
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const double ell = exp(thetas[b]);
+  const double* Xb = Xs + static_cast<size_t>(b) * n * d;
   const int i0 = ti * 32, j0 = tj * 32;
   double r2[4] = {0.0, 0.0, 0.0, 0.0};
   for (int dc = 0; dc < d; dc += DCH) {
@@ -311,8 +318,8 @@ __global__ void __launch_bounds__(256) kmat_kernel(const double* __restrict__ X,
       const int row = e / DCH, col = e % DCH;
       double vi = 0.0, vj = 0.0;
       if (col < dn) {
-        if (i0 + row < n) vi = X[static_cast<size_t>(i0 + row) * d + dc + col] / ell;
-        if (j0 + row < n) vj = X[static_cast<size_t>(j0 + row) * d + dc + col] / ell;
+        if (i0 + row < n) vi = Xb[static_cast<size_t>(i0 + row) * d + dc + col];
+        if (j0 + row < n) vj = Xb[static_cast<size_t>(j0 + row) * d + dc + col];
       }
       Xi[row][col] = vi; Xj[row][col] = vj;
     }
@@ -324,17 +331,25 @@ __global__ void __launch_bounds__(256) kmat_kernel(const double* __restrict__ X,
     }
   }
   const size_t ld = npad;
+  double kv[4] = {r2[0], r2[1], r2[2], r2[3]};
   if (MODE == 0) {
+    // correctly rounded library sqrt / exp here, not the sweep's 4-ulp versions: the optimiser's line
+    // search works on LML differences at the 1e-12 level near convergence, and extra noise in K costs
+    // it evaluations
+#pragma unroll
+    for (int r = 0; r < 4; ++r) kv[r] = kern_value(kind, r2[r], mg);
     double* A = bp.A + b * bp.mat_stride;
 #pragma unroll
     for (int r = 0; r < 4; ++r) {
       const int i = i0 + ty + 8 * r, j = j0 + tx;
       double v;
-      if (i < n && j < n) v = (i == j) ? 1.0 + jitter : kern_value(kind, r2[r], mg);
+      if (i < n && j < n) v = (i == j) ? 1.0 + jitter : kv[r];
       else v = (i == j) ? 1.0 : 0.0;
       A[i * ld + j] = v;
     }
   } else {
+#pragma unroll
+    for (int r = 0; r < 4; ++r) kv[r] = kern_dtheta(kind, r2[r], mg);
     const double* Kinv = bp.A + b * bp.mat_stride;
     const double* al = alpha + static_cast<size_t>(b) * npad;
     double s = 0.0;
@@ -342,7 +357,7 @@ __global__ void __launch_bounds__(256) kmat_kernel(const double* __restrict__ X,
     for (int r = 0; r < 4; ++r) {
       const int i = i0 + ty + 8 * r, j = j0 + tx;
       if (i < n && j < n) {
-        const double g = (i == j) ? 0.0 : kern_dtheta(kind, r2[r], mg);
+        const double g = (i == j) ? 0.0 : kv[r];
         s += (al[i] * al[j] - Kinv[i * ld + j]) * g;
       }
     }
