@@ -198,7 +198,7 @@ def measure_latency(reps_gpu=7):
         results.append({'config': label, 'get_suggestions_p50_ms': gpu_ms, 'first_call_ms': first_ms,
                         'cpu_reference_ms': float(np.median(cpu)) if cpu else None,
                         'includes': 'fit, sweep, refinement, decode; the first call of the seeded group also draws the '
-                                    'candidates with numpy RandomState (reference RNG contract) and uploads them, later '
+                                    'candidates (numpy MT19937 stream regenerated on the device, bit-identical), later '
                                     'calls reuse the device-resident matrix (same generator state => same candidates)'})
     return results
 
