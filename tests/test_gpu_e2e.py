@@ -203,3 +203,31 @@ def test_device_rng_and_host_rng_give_the_same_suggestion(monkeypatch):
         out.append((opt.get_suggestion(), opt.utility_function.random_generator.get_state()[1].copy()))
     assert out[0][0] == out[1][0]
     assert np.array_equal(out[0][1], out[1][1])
+
+
+def test_suggest_groups_runs_independent_groups_in_order():
+    """C5 shape (scaled down): independent groups through the batch helper equal the one-by-one calls."""
+    from polyaxon_b200.groups import suggest_groups
+    from polyaxon_b200.hpsearch.schemas.bayesian_optimization import BOIterationConfig
+    from polyaxon_b200.hpsearch.search_managers import get_search_algorithm_manager
+    from oracle.reference_path import synthetic_problem
+    cfgs, its = [], []
+    g = load_golden('c5_d16_n128_m25_ei')
+    keys = ['x%03d' % i for i in range(16)]
+    for gid in range(3):
+        X, y, _ = synthetic_problem(64, 16, seed=1234 + gid)
+        cfg = _config(g, {k: {'uniform': [0, 1]} for k in keys})
+        cfg.seed = 100 + gid
+        cfgs.append(cfg)
+        its.append(BOIterationConfig.from_dict({
+            'iteration': 1, 'experiment_ids': list(range(64)),
+            'experiments_configs': [[i, dict(zip(keys, row.tolist()))] for i, row in enumerate(X)],
+            'experiments_metrics': [[i, float(v)] for i, v in enumerate(y)]}))
+    together = suggest_groups(cfgs, its)
+    # BOIterationConfig.combined_* extends its lists in place (as the reference's does), so rebuild them
+    its2 = [BOIterationConfig.from_dict({'iteration': 1, 'experiment_ids': it.experiment_ids,
+                                         'experiments_configs': it.experiments_configs,
+                                         'experiments_metrics': it.experiments_metrics}) for it in its]
+    alone = [get_search_algorithm_manager(c).get_suggestions(i) for c, i in zip(cfgs, its2)]
+    assert together == alone
+    assert len({tuple(sorted(s[0].items())) for s in together}) == 3
