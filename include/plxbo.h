@@ -75,6 +75,14 @@ int plx_gp_fit(plx_bo_handle h, double theta0, const double* theta_restarts, int
  * Replaces sklearn _gpr.py:349-367. */
 int plx_gp_set_theta(plx_bo_handle h, double theta);
 
+/* One more observation at the current theta, in O(n^2) instead of the O(n^3) refit: the factor, its
+ * inverse and alpha are extended by one row (bordered Cholesky), giving the state that
+ * plx_gp_set_data on the n+1 observations followed by plx_gp_set_theta(theta) would build, up to
+ * rounding.  The reference has no such step -- it refits all observations on every iteration
+ * (optimizer.py:21) -- so the host layer uses it only when asked to hold theta between refits
+ * (PLX_BO_REFIT_EVERY > 1).  x_new is d doubles (HOST).  PLX_ERR_NOT_PD leaves the state untouched. */
+int plx_gp_append(plx_bo_handle h, const double* x_new, double y_new);
+
 /* Copy the state back for verification: L (n x n, lower), alpha (n), Linv (n x n); any may be NULL. */
 int plx_gp_get_state(plx_bo_handle h, double* L, double* alpha, double* Linv);
 

@@ -32,6 +32,7 @@ SIGNATURES = {
     'plx_gp_fit': (c_int, [c_void_p, c_double, c_void_p, c_int, c_double, c_double, _dp, _dp, c_void_p]),
     'plx_gp_set_theta': (c_int, [c_void_p, c_double]),
     'plx_gp_get_state': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
+    'plx_gp_append': (c_int, [c_void_p, c_void_p, c_double]),
     'plx_acq_sweep': (c_int, [c_void_p, c_void_p, c_longlong, c_longlong, c_int, c_double, c_double, c_double,
                               _dp, POINTER(c_longlong), c_void_p, c_void_p, c_void_p, c_void_p]),
     'plx_acq_sweep_dev': (c_int, [c_void_p, c_void_p, c_longlong, c_longlong, c_int, c_double, c_double,
@@ -107,6 +108,7 @@ class Handle(object):
         self.device = int(device)
         self.n = self.d = 0
         self.resident_key = None
+        self.held = None          # host-side record of the last fit (DeviceGaussianProcess, PLX_BO_REFIT_EVERY)
 
     def close(self):
         if getattr(self, '_h', None):
@@ -135,6 +137,7 @@ class Handle(object):
         if X.ndim != 2 or y.shape != (X.shape[0],):
             raise ValueError('X must be (n, d) and y (n,)')
         self.n, self.d = X.shape
+        self.held = None
         self._check(self.lib.plx_gp_set_data(self._h, _ptr(X), _ptr(y), self.n, self.d, int(kernel),
                                              float(nu), float(jitter)))
 
@@ -155,7 +158,16 @@ class Handle(object):
         return th.value, lml.value, per_run
 
     def set_theta(self, theta):
+        self.held = None
         self._check(self.lib.plx_gp_set_theta(self._h, float(theta)))
+
+    def append(self, x_new, y_new):
+        """One more observation at the current theta (bordered Cholesky, O(n^2))."""
+        x_new = _f64(x_new).ravel()
+        if x_new.shape[0] != self.d:
+            raise ValueError('x_new must have {} entries'.format(self.d))
+        self._check(self.lib.plx_gp_append(self._h, _ptr(x_new), float(y_new)))
+        self.n += 1
 
     def get_state(self, want_L=True, want_Linv=False):
         L = np.empty((self.n, self.n)) if want_L else None

@@ -2,6 +2,7 @@
 // Declarations and the reference call site each entry point replaces: include/plxbo.h.
 #include "../../include/plxbo.h"
 #include "refine.cuh"
+#include "append.cuh"
 
 #include <cstdio>
 #include <cstring>
@@ -32,6 +33,8 @@ struct plx_bo {
   double jitter = 1e-10;
   double* dX = nullptr; size_t x_cap = 0;
   double* dy = nullptr; size_t y_cap = 0;
+  int kernel_id = 0; double nu = 0.0;          // as given to plx_gp_set_data (plx_gp_append may replay it)
+  double* d_app = nullptr; size_t app_cap = 0; // plx_gp_append scratch: k | l | w | pivot
 
   // batched fit workspace
   int bcap = 0, wnpad = 0;
@@ -206,7 +209,7 @@ extern "C" void plx_bo_destroy(plx_bo_handle h) {
                   h->d_alpha, h->d_partial, h->d_lml, h->d_grad, h->d_xs, h->d_info, h->dZ, h->d_alpha_state, h->dKs, h->dXt,
                   h->d_blk_val, h->d_blk_idx, h->d_best_val, h->d_best_idx, h->dcand[0], h->dcand[1],
                   h->d_out[0], h->d_out[1], h->d_out[2], h->rf_kv, h->rf_kp, h->rf_v, h->rf_w, h->rf_vec,
-                  h->rf_bounds, h->rf_val, h->rf_grad, h->rf_sc, h->rf_active, h->d_resident, h->d_misc};
+                  h->rf_bounds, h->rf_val, h->rf_grad, h->rf_sc, h->rf_active, h->d_resident, h->d_misc, h->d_app};
   for (void* p : ptrs) if (p) cudaFree(p);
   for (int i = 0; i < 2; ++i) { if (h->ev_copy[i]) cudaEventDestroy(h->ev_copy[i]); if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]); }
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
@@ -239,7 +242,7 @@ extern "C" int plx_gp_set_data(plx_bo_handle h, const double* X, const double* y
     return fail(h, rc, "Matern nu must be positive and at most 50");
   if (rc != PLX_OK) return fail(h, rc, "unknown kernel id");
   CK(cudaSetDevice(h->device));
-  h->n = n; h->d = d; h->kind = kind; h->jitter = jitter;
+  h->n = n; h->d = d; h->kind = kind; h->jitter = jitter; h->kernel_id = kernel; h->nu = nu;
   h->mg = (kind == K_GEN) ? make_matern_gen(nu) : MaternGen{};
   h->npad = (n + 127) / 128 * 128; h->nb = h->npad / 128;
   { const int nt32 = (n + 31) / 32; h->ntri = nt32 * (nt32 + 1) / 2; }   // lower 32-tiles that hold observations
@@ -411,6 +414,76 @@ extern "C" int plx_gp_get_state(plx_bo_handle h, double* L, double* alpha, doubl
     for (size_t i = 0; i < n; ++i) for (size_t j = i + 1; j < n; ++j) L[i * n + j] = 0.0;
   if (Linv)
     for (size_t i = 0; i < n; ++i) for (size_t j = i + 1; j < n; ++j) Linv[i * n + j] = 0.0;
+  return PLX_OK;
+}
+
+// One more observation at the current theta.  See append.cuh for the algebra.
+extern "C" int plx_gp_append(plx_bo_handle h, const double* x_new, double y_new) {
+  if (!h || !x_new) return h ? fail(h, PLX_ERR_INVALID, "gp_append: bad arguments") : PLX_ERR_INVALID;
+  if (!h->have_state) return fail(h, PLX_ERR_STATE, "gp_append: no posterior state (call plx_gp_fit or plx_gp_set_theta)");
+  CK(cudaSetDevice(h->device));
+  cudaStream_t st = h->stream;
+  const int n0 = h->n, d = h->d, npad = h->npad;
+  if (n0 == npad) {
+    // the padded storage is full: rebuild at the next padding step from the device copy of the data
+    std::vector<double> X(static_cast<size_t>(n0 + 1) * d), y(n0 + 1);
+    CK(cudaMemcpyAsync(X.data(), h->dX, sizeof(double) * n0 * d, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(y.data(), h->dy, sizeof(double) * n0, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    std::memcpy(X.data() + static_cast<size_t>(n0) * d, x_new, sizeof(double) * d);
+    y[n0] = y_new;
+    const double theta = h->theta;
+    const int r = plx_gp_set_data(h, X.data(), y.data(), n0 + 1, d, h->kernel_id, h->nu, h->jitter);
+    return r != PLX_OK ? r : plx_gp_set_theta(h, theta);
+  }
+  int r;
+  if (h->x_cap < static_cast<size_t>(n0 + 1) * d) {       // grow the observation matrix, keeping its rows
+    double* nx = nullptr;
+    const size_t cap = static_cast<size_t>(npad) * d;
+    CK(cudaMalloc(reinterpret_cast<void**>(&nx), cap * sizeof(double)));
+    CK(cudaMemcpyAsync(nx, h->dX, sizeof(double) * n0 * d, cudaMemcpyDeviceToDevice, st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaFree(h->dX));
+    h->dX = nx; h->x_cap = cap;
+  }
+  if ((r = ensure(h, h->d_app, h->app_cap, static_cast<size_t>(3) * npad + 8)) != PLX_OK) return r;
+  double *kv = h->d_app, *lv = kv + npad, *wv = lv + npad, *piv = wv + npad;
+  const double ell = std::exp(h->theta);
+  CK(cudaMemcpyAsync(h->dX + static_cast<size_t>(n0) * d, x_new, sizeof(double) * d, cudaMemcpyHostToDevice, st));
+  append_kvec_kernel<<<(n0 + 255) / 256, 256, 0, st>>>(h->dX, n0, d, ell, h->kind, h->mg, kv);
+  LAUNCH_CHECK("append_kvec_kernel");
+  trmv_lower_kernel<<<(n0 + 7) / 8, 256, 0, st>>>(h->dZ, npad, n0, kv, lv);
+  LAUNCH_CHECK("trmv_lower_kernel");
+  append_pivot_kernel<<<1, 256, 0, st>>>(lv, n0, 1.0 + h->jitter, piv);
+  LAUNCH_CHECK("append_pivot_kernel");
+  double lam2 = 0.0;
+  CK(cudaMemcpyAsync(&lam2, piv, sizeof(double), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  if (!(lam2 > 0.0))       // nothing of the state has been touched yet
+    return fail(h, PLX_ERR_NOT_PD, "gp_append: the extended kernel matrix is not positive definite (pivot^2 = " +
+                                       std::to_string(lam2) + ")");
+  const double lam = std::sqrt(lam2);
+  // Z row n0 <- -(l^T Z) / lambda, written in place (only rows < n0 are read), then the diagonal
+  trmv_lower_t_kernel<<<(n0 + 31) / 32, 256, 0, st>>>(h->dZ, npad, n0, lv, -1.0 / lam,
+                                                      h->dZ + static_cast<size_t>(n0) * npad);
+  LAUNCH_CHECK("trmv_lower_t_kernel");
+  append_row_kernel<<<(n0 + 256) / 256, 256, 0, st>>>(h->dZ, npad, n0, nullptr, 1.0 / lam);   // diagonal only
+  LAUNCH_CHECK("append_row_kernel");
+  if (h->state_factor_valid) {
+    append_row_kernel<<<(n0 + 256) / 256, 256, 0, st>>>(h->bp.L, npad, n0, lv, lam);
+    LAUNCH_CHECK("append_row_kernel");
+  }
+  CK(cudaMemcpyAsync(h->dy + n0, &y_new, sizeof(double), cudaMemcpyHostToDevice, st));
+  const int n1 = n0 + 1;
+  trmv_lower_kernel<<<(n1 + 7) / 8, 256, 0, st>>>(h->dZ, npad, n1, h->dy, wv);
+  LAUNCH_CHECK("trmv_lower_kernel");
+  trmv_lower_t_kernel<<<(n1 + 31) / 32, 256, 0, st>>>(h->dZ, npad, n1, wv, 1.0, h->d_alpha_state);
+  LAUNCH_CHECK("trmv_lower_t_kernel");
+  scale_transpose_x_kernel<<<dim3((npad + 255) / 256, d), 256, 0, st>>>(h->dX, n1, d, npad, ell, h->dXt);
+  LAUNCH_CHECK("scale_transpose_x_kernel");
+  CK(cudaStreamSynchronize(st));          // y_new / lam2 live on this frame
+  h->n = n1;
+  { const int nt32 = (n1 + 31) / 32; h->ntri = nt32 * (nt32 + 1) / 2; }
   return PLX_OK;
 }
 

@@ -74,11 +74,13 @@ class DeviceGaussianProcess(object):
         if X.ndim != 2 or X.shape[0] != y.shape[0]:
             raise ValueError('Found input variables with inconsistent numbers of samples: '
                              '{} and {}'.format(X.shape, y.shape))
-        self.handle.set_data(X, y, self.kernel_id, self.nu, self.alpha)
         # sklearn draws one theta per restart from the shared generator, before any candidate
         # (sklearn _gpr.py:329-333); same calls here so the stream stays aligned
         lo, hi = np.array([THETA_BOUNDS[0]]), np.array([THETA_BOUNDS[1]])
         restarts = [float(self.random_state.uniform(lo, hi)[0]) for _ in range(self.n_restarts_optimizer)]
+        if self._append_instead_of_refit(X, y):
+            return self
+        self.handle.set_data(X, y, self.kernel_id, self.nu, self.alpha)
         theta, lml, per_run = self._fit_runs(np.log(self.length_scale), restarts)
         self.theta_ = theta
         self.length_scale_ = float(np.exp(theta))
@@ -86,7 +88,39 @@ class DeviceGaussianProcess(object):
         self.optimizer_runs_ = per_run
         self.X_train_, self.y_train_ = X, y
         self.fitted = True
+        self.handle.held = dict(X=X.copy(), y=y.copy(), kernel=(self.kernel_id, self.nu, self.length_scale,
+                                                                self.n_restarts_optimizer),
+                                theta=theta, lml=lml, since_fit=0)
         return self
+
+    def _append_instead_of_refit(self, X, y):
+        """Opt-in (PLX_BO_REFIT_EVERY = k > 1; the default 1 is the reference's behaviour, a full
+        hyper-parameter fit on every call, optimizer.py:21): when this call's observations are the
+        previous call's plus new rows at the end, and fewer than k calls have passed since the last
+        fit, keep theta and extend the posterior state row by row on the device (plx_gp_append)."""
+        every = int(os.environ.get('PLX_BO_REFIT_EVERY', '1') or 1)
+        held = getattr(self.handle, 'held', None)
+        if every <= 1 or held is None:
+            return False
+        n0 = held['X'].shape[0]
+        same_model = held['kernel'] == (self.kernel_id, self.nu, self.length_scale, self.n_restarts_optimizer)
+        if (not same_model or held['since_fit'] + 1 >= every or X.shape[0] <= n0 or X.shape[1] != held['X'].shape[1]
+                or self.handle.n != n0 or not np.array_equal(X[:n0], held['X']) or not np.array_equal(y[:n0], held['y'])):
+            return False
+        try:
+            for i in range(n0, X.shape[0]):
+                self.handle.append(X[i], y[i])
+        except np.linalg.LinAlgError:
+            self.handle.held = None                  # partially extended: let the caller refit from scratch
+            return False
+        held.update(X=X.copy(), y=y.copy(), since_fit=held['since_fit'] + 1)
+        self.theta_ = held['theta']
+        self.length_scale_ = float(np.exp(held['theta']))
+        self.log_marginal_likelihood_value_ = None   # not evaluated on this path
+        self.optimizer_runs_ = None
+        self.X_train_, self.y_train_ = X, y
+        self.fitted = True
+        return True
 
     def _fit_runs(self, theta0, restarts):
         """All optimiser runs (the configured length scale first, then the restarts).  Under

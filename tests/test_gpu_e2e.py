@@ -231,3 +231,61 @@ def test_suggest_groups_runs_independent_groups_in_order():
     alone = [get_search_algorithm_manager(c).get_suggestions(i) for c, i in zip(cfgs, its2)]
     assert together == alone
     assert len({tuple(sorted(s[0].items())) for s in together}) == 3
+
+
+def test_hold_theta_between_refits_is_opt_in(monkeypatch):
+    """PLX_BO_REFIT_EVERY=k > 1: calls whose observations extend the previous call's keep theta and
+    extend the posterior state on the device; the default refits every call like the reference."""
+    from polyaxon_b200 import _lib, device
+    from polyaxon_b200.hpsearch.search_managers.bayesian_optimization.optimizer import BOOptimizer
+    g = load_golden('c5_d16_n128_m25_ei')
+    d = g['X'].shape[1]
+    keys = ['x%03d' % i for i in range(d)]
+    cfg = _config(g, {k: {'uniform': [0, 1]} for k in keys})
+    configs = [dict(zip(keys, row.tolist())) for row in g['X']]
+    metrics = g['y'].tolist()
+    fits = {'n': 0}
+    real_fit = _lib.Handle.fit
+
+    def counting_fit(self, *a, **k):
+        fits['n'] += 1
+        return real_fit(self, *a, **k)
+    monkeypatch.setattr(_lib.Handle, 'fit', counting_fit)
+
+    def run(n):
+        opt = BOOptimizer(hptuning_config=cfg)
+        opt.add_observations(configs=configs[:n], metrics=metrics[:n])
+        s = opt.get_suggestion()
+        return s, opt.utility_function.gaussian_process
+
+    n = len(configs)
+    run(n - 3); run(n - 2)
+    assert fits['n'] == 2                              # default: a fit per call
+    monkeypatch.setenv('PLX_BO_REFIT_EVERY', '3')
+    fits['n'] = 0
+    _, gp0 = run(n - 3)                                # fit
+    s1, gp1 = run(n - 2)                               # +1 row, theta held
+    s2, gp2 = run(n)                                   # +2 rows, theta held
+    assert fits['n'] == 1
+    assert gp1.theta_ == gp0.theta_ == gp2.theta_
+    h = device.get_handle()
+    assert h.n == n
+    _, alpha, Z = h.get_state(want_L=False, want_Linv=True)
+    ref = _lib.Handle(0)
+    try:
+        ref.set_data(g['X'], g['y'], int(g['kernel']), float(g['nu']))
+        ref.set_theta(gp0.theta_)
+        _, alpha_ref, Z_ref = ref.get_state(want_L=False, want_Linv=True)
+    finally:
+        ref.close()
+    tol = max(1e-9, 100 * np.finfo(float).eps * float(g['cond']))
+    assert np.max(np.abs(alpha - alpha_ref)) <= tol * np.max(np.abs(alpha_ref))
+    assert np.max(np.abs(Z - Z_ref)) <= tol * np.max(np.abs(Z_ref))
+    for s in (s1, s2):
+        assert set(s) == set(keys) and all(0.0 <= v <= 1.0 for v in s.values())
+    _, gp3 = run(n)                                    # third call since the fit: refit
+    assert fits['n'] == 2
+    # a different observation history never takes the shortcut
+    fits['n'] = 0
+    run(n - 1)
+    assert fits['n'] == 1
