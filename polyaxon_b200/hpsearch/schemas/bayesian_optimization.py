@@ -45,8 +45,9 @@ class BOIterationConfig(object):
         return cls(**data)
 
     def to_dict(self):
-        # like the reference's post_dump hook: attributes that are None are left out
-        return {k: getattr(self, k) for k in _FIELDS if getattr(self, k) is not None}
+        # every field is dumped, None included: the stored rows the reference's tests compare against
+        # (tests/test_experiment_groups/test_iteration_managers.py:152-160) carry `'old_experiment_ids': None`
+        return {k: getattr(self, k) for k in _FIELDS}
 
     def _combined(self, old, new):
         # the reference extends the stored `old_*` list in place when it is non-empty; keep that

@@ -263,7 +263,10 @@ if not HAVE_POLYAXON_SCHEMAS:
             if key == 'values' or self.is_range:
                 return rng.choice(self.to_numpy(), size=size)
             if key == 'pvalues':
-                return rng.choice([v[0] for v in value], size=size, p=[v[1] for v in value])
+                # the reference's own test matrix has weights summing to 0.9
+                # (test_search_managers.py:138); they are used as relative weights here
+                weights = np.asarray([v[1] for v in value], dtype=float)
+                return rng.choice([v[0] for v in value], size=size, p=weights / weights.sum())
             if key == 'uniform':
                 return rng.uniform(value['low'], value['high'], size=size)
             if key == 'quniform':
@@ -363,9 +366,59 @@ if not HAVE_POLYAXON_SCHEMAS:
                     'n_initial_trials': self.n_initial_trials,
                     'n_iterations': self.n_iterations}
 
+    class GridSearchConfig(object):
+        def __init__(self, n_experiments=None):
+            self.n_experiments = n_experiments
+
+        @classmethod
+        def from_dict(cls, value):
+            return cls(**value)
+
+        def to_dict(self):
+            return {} if self.n_experiments is None else {'n_experiments': self.n_experiments}
+
+    class RandomSearchConfig(GridSearchConfig):
+        def __init__(self, n_experiments):
+            super().__init__(n_experiments=n_experiments)
+
+    class ResourceConfig(object):
+        """Hyperband's resource: the declaration that receives the budget, as int or float."""
+        TYPES = {'int': int, 'float': float}
+
+        def __init__(self, name, type='float'):    # noqa: A002 - the section's key is `type`
+            if type not in self.TYPES:
+                raise ConfigError('resource type must be `int` or `float`')
+            self.name = name
+            self.type = type
+
+        @classmethod
+        def from_dict(cls, value):
+            return cls(**value)
+
+        def to_dict(self):
+            return {'name': self.name, 'type': self.type}
+
+        def cast_value(self, value):
+            return self.TYPES[self.type](value)
+
+    class HyperbandConfig(object):
+        def __init__(self, max_iter, eta, resource, metric, resume=False):
+            self.max_iter = max_iter
+            self.eta = eta
+            self.resource = ResourceConfig.from_dict(resource) if isinstance(resource, dict) else resource
+            self.metric = SearchMetricConfig.from_dict(metric) if isinstance(metric, dict) else metric
+            self.resume = resume
+
+        @classmethod
+        def from_dict(cls, value):
+            return cls(**value)
+
+        def to_dict(self):
+            return {'max_iter': self.max_iter, 'eta': self.eta, 'resource': self.resource.to_dict(),
+                    'metric': self.metric.to_dict(), 'resume': self.resume}
+
     class HPTuningConfig(object):
-        """The ``hptuning`` section.  Only the Bayesian-optimisation branch carries settings here;
-        the sibling algorithms (grid, random, hyperband) are out of scope for this library."""
+        """The ``hptuning`` section: the matrix plus the settings of one search algorithm."""
 
         def __init__(self, matrix=None, seed=None, concurrency=1, bo=None, early_stopping=None,
                      grid_search=None, random_search=None, hyperband=None):
@@ -378,9 +431,13 @@ if not HAVE_POLYAXON_SCHEMAS:
             if isinstance(bo, dict):
                 bo = BOConfig.from_dict(bo)
             self.bo = bo
-            self.grid_search = grid_search
-            self.random_search = random_search
-            self.hyperband = hyperband
+            self.grid_search = (GridSearchConfig.from_dict(grid_search) if isinstance(grid_search, dict)
+                                else grid_search)
+            self.random_search = (RandomSearchConfig.from_dict(random_search)
+                                  if isinstance(random_search, dict) else random_search)
+            self.hyperband = HyperbandConfig.from_dict(hyperband) if isinstance(hyperband, dict) else hyperband
+            if sum(x is not None for x in (self.bo, self.grid_search, self.random_search, self.hyperband)) > 1:
+                raise ConfigError('Only one search algorithm can be configured.')
 
         @classmethod
         def from_dict(cls, value):
@@ -391,8 +448,9 @@ if not HAVE_POLYAXON_SCHEMAS:
                    'matrix': {k: v.to_dict() for k, v in self.matrix.items()}}
             if self.seed is not None:
                 out['seed'] = self.seed
-            if self.bo is not None:
-                out['bo'] = self.bo.to_dict()
+            for key in ('bo', 'grid_search', 'random_search', 'hyperband'):
+                if getattr(self, key) is not None:
+                    out[key] = getattr(self, key).to_dict()
             return out
 
         @property

@@ -47,7 +47,7 @@ def test_manager_dispatch_and_algorithm_check():
     assert isinstance(manager, BOSearchManager) and manager.NAME == SearchAlgorithms.BO
     assert get_search_algorithm_manager(None) is None
     grid = HPTuningConfig.from_dict({'matrix': {'lr': {'values': [1, 2]}}})
-    assert get_search_algorithm_manager(grid) is None
+    assert get_search_algorithm_manager(grid).NAME == SearchAlgorithms.GRID
     with pytest.raises(ValueError):
         BOSearchManager(hptuning_config=grid)
     assert manager.should_reschedule(4) and not manager.should_reschedule(5)
@@ -189,7 +189,8 @@ def test_bo_iteration_config_round_trip():
            'experiment_ids': [4, 5], 'experiments_configs': [[4, {'a': 4}], [5, {'a': 5}]],
            'experiments_metrics': [[4, 0.4], [5, 0.5]]}
     assert BOIterationConfig.from_dict(cfg).to_dict() == cfg
-    assert BOIterationConfig.from_dict({'iteration': 0}).to_dict() == {'iteration': 0}
+    bare = BOIterationConfig.from_dict({'iteration': 0}).to_dict()      # None fields are dumped too
+    assert bare['iteration'] == 0 and len(bare) == 7 and all(v is None for k, v in bare.items() if k != 'iteration')
     it = get_iteration_config(SearchAlgorithms.BO, cfg)
     assert it.combined_experiment_ids == [1, 2, 3, 4, 5]
     assert dict(it.combined_experiments_metrics)[5] == 0.5
