@@ -48,7 +48,9 @@ const char* plx_version(void);
 int plx_bo_set_stream(plx_bo_handle h, void* stream);
 
 /* Options: "sweep_impl" (1 = TMA ring [default], 0 = plain-load cross-check); "sweep_dbg" (profiling
- * only: bit 0 skips the cross-kernel build after the first tile, bit 1 skips the tensor-pipe work). */
+ * only: bit 0 skips the cross-kernel build after the first tile, bit 1 skips the tensor-pipe work);
+ * "lml_batch_limit" (k > 0: at most k thetas per pass of plx_gp_lml / plx_gp_fit; 0 = as many as fit
+ * in the free device memory, which is also what bounds a batch too large for one pass). */
 int plx_bo_set_option(plx_bo_handle h, const char* name, long long value);
 
 /* Observations.  Replaces the arguments of GaussianProcessRegressor.fit(X, y) at optimizer.py:21

@@ -61,7 +61,7 @@ struct plx_bo {
   double* d_out[3] = {nullptr, nullptr, nullptr}; size_t out_cap = 0;
   cudaEvent_t ev_copy[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
   std::vector<cudaEvent_t> ev_pool;
-  int sweep_impl = 1, sweep_dbg = 0;
+  int sweep_impl = 1, sweep_dbg = 0, lml_batch_limit = 0;
   double last_ms = 0.0; long long last_launches = 0;
 
   // resident candidate matrix (iteration-invariant for a seeded group)
@@ -227,6 +227,7 @@ extern "C" int plx_bo_set_stream(plx_bo_handle h, void* stream) {
 extern "C" int plx_bo_set_option(plx_bo_handle h, const char* name, long long value) {
   if (!h || !name) return PLX_ERR_INVALID;
   if (std::strcmp(name, "sweep_impl") == 0 && (value == 0 || value == 1)) { h->sweep_impl = static_cast<int>(value); return PLX_OK; }
+  if (std::strcmp(name, "lml_batch_limit") == 0 && value >= 0) { h->lml_batch_limit = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "sweep_dbg") == 0) { h->sweep_dbg = static_cast<int>(value); return PLX_OK; }
   return fail(h, PLX_ERR_INVALID, std::string("unknown option or value: ") + name);
 }
@@ -339,15 +340,33 @@ static int launch_lml(plx_bo* h, int B, bool want_grad) {
   return PLX_OK;
 }
 
+// Largest number of thetas evaluated in one pass: five n x n matrices per theta must fit in (most of)
+// the memory that is free now plus what the current workspace already holds.
+static int batch_limit(plx_bo* h) {
+  size_t free_b = 0, total_b = 0;
+  if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return 1;
+  const size_t mat = static_cast<size_t>(h->npad) * h->npad * sizeof(double);
+  const size_t per_theta = 4 * mat + static_cast<size_t>(h->nb) * 128 * 128 * sizeof(double) + 4 * mat / 64;
+  size_t avail = free_b;
+  if (h->wnpad == h->npad) avail += static_cast<size_t>(h->bcap) * per_theta;
+  const size_t usable = avail / 10 * 8;
+  return static_cast<int>(std::max<size_t>(1, std::min<size_t>(usable / per_theta, 1 << 20)));
+}
+
 static int eval_lml(plx_bo* h, const double* thetas, int B, double* lml, double* grad) {
   int r;
-  if ((r = ensure_batch(h, B)) != PLX_OK) return r;
-  h->state_factor_valid = false;
-  CK(cudaMemcpyAsync(h->d_thetas, thetas, sizeof(double) * B, cudaMemcpyHostToDevice, h->stream));
-  if ((r = launch_lml(h, B, grad != nullptr)) != PLX_OK) return r;
-  CK(cudaMemcpyAsync(lml, h->d_lml, sizeof(double) * B, cudaMemcpyDeviceToHost, h->stream));
-  if (grad) CK(cudaMemcpyAsync(grad, h->d_grad, sizeof(double) * B, cudaMemcpyDeviceToHost, h->stream));
-  CK(cudaStreamSynchronize(h->stream));
+  int limit = (B <= h->bcap && h->wnpad == h->npad) ? B : batch_limit(h);
+  if (h->lml_batch_limit > 0) limit = std::min(limit, h->lml_batch_limit);
+  for (int first = 0; first < B; first += limit) {
+    const int b = std::min(limit, B - first);
+    if ((r = ensure_batch(h, b)) != PLX_OK) return r;
+    h->state_factor_valid = false;
+    CK(cudaMemcpyAsync(h->d_thetas, thetas + first, sizeof(double) * b, cudaMemcpyHostToDevice, h->stream));
+    if ((r = launch_lml(h, b, grad != nullptr)) != PLX_OK) return r;
+    CK(cudaMemcpyAsync(lml + first, h->d_lml, sizeof(double) * b, cudaMemcpyDeviceToHost, h->stream));
+    if (grad) CK(cudaMemcpyAsync(grad + first, h->d_grad, sizeof(double) * b, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+  }
   return PLX_OK;
 }
 

@@ -125,6 +125,25 @@ def test_lml_and_gradient_batched(handle, name):
                                         abs=max(1e-7, tol * abs(float(g['lml_fixed'][i]))))
 
 
+def test_lml_batches_split_into_passes_give_identical_values(handle):
+    """A batch that does not fit in device memory is evaluated in several passes; forced here with the
+    `lml_batch_limit` option.  Every theta is computed independently, so the results are bit-identical."""
+    g = load_golden('c3_d32_n512_m15_poi')
+    handle.set_data(g['X'], g['y'], int(g['kernel']), float(g['nu']))
+    thetas = np.linspace(-1.0, 2.0, 7)
+    whole = handle.lml(thetas)
+    try:
+        handle.set_option('lml_batch_limit', 3)
+        parts = handle.lml(thetas)
+        fit_parts = handle.fit(0.0, [-1.0, 1.0, 2.0, 0.5])
+    finally:
+        handle.set_option('lml_batch_limit', 0)
+    assert np.array_equal(whole[0], parts[0]) and np.array_equal(whole[1], parts[1])
+    fit_whole = handle.fit(0.0, [-1.0, 1.0, 2.0, 0.5])
+    assert fit_parts[0] == fit_whole[0] and fit_parts[1] == fit_whole[1]
+    assert np.array_equal(fit_parts[2], fit_whole[2])
+
+
 @pytest.mark.parametrize('name', CLOSED_FORM)
 def test_fit_reaches_the_reference_optimum(handle, name):
     g = load_golden(name)
