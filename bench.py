@@ -203,6 +203,79 @@ def measure_latency(reps_gpu=7):
     return results
 
 
+def measure_fit(h):
+    """Config C4: hyper-parameter fit (33 L-BFGS-B runs on theta advanced in lock step) at growing n, d=32,
+    Matern nu=1.5; the sklearn fit of the CPU reference path beside it while it stays within seconds."""
+    import warnings
+    from oracle import gp_numpy as G
+    from oracle import reference_path as R
+    from oracle.reference_path import synthetic_problem
+    from threadpoolctl import threadpool_limits
+    out = []
+    for n in (64, 128, 256, 512, 1024, 2048, 4096):
+        X, y, _ = synthetic_problem(n, 32)
+        rs = np.random.RandomState(17)
+        restarts = rs.uniform(G.THETA_BOUNDS[0], G.THETA_BOUNDS[1], size=32)
+        times = []
+        for _ in range(3 if n <= 2048 else 2):
+            t0 = time.perf_counter()
+            h.set_data(X, y, 1, 1.5)
+            theta, lml, per_run = h.fit(0.0, restarts)
+            times.append((time.perf_counter() - t0) * 1e3)
+        evals = int(per_run[:, 3].sum())
+        flop = evals * (n * n * (3 * 32 + 10) + float(n) ** 3 + 4 * n * n)
+        rec = {'n_obs': n, 'restarts': 33, 'fit_ms': float(np.median(times[1:])), 'lml_evaluations': evals,
+               'tflops_model': flop / (float(np.median(times[1:])) * 1e-3) / 1e12, 'theta': theta, 'lml': lml,
+               'cpu_reference_ms': None}
+        if n <= 256:
+            with threadpool_limits(limits=os.cpu_count()), warnings.catch_warnings():
+                warnings.simplefilter('ignore')
+                gp = R.make_gp(G.KERNEL_MATERN, 1.0, 1.5, 32, R.make_rng(17))
+                t0 = time.perf_counter()
+                gp.fit(X, y)
+                rec['cpu_reference_ms'] = (time.perf_counter() - t0) * 1e3
+                rec['cpu_theta'] = float(gp.kernel_.theta[0])
+        out.append(rec)
+    return out
+
+
+def measure_groups(n_groups=8):
+    """Config C5, one GPU's share: 8 of the 64 independent groups (d=16, n_obs=512) through
+    polyaxon_b200.groups.suggest_groups, one worker thread against eight (a C-ABI handle and stream each)."""
+    from oracle.reference_path import synthetic_problem
+    from polyaxon_b200.groups import suggest_groups
+    from polyaxon_b200.hpsearch.schemas.bayesian_optimization import BOIterationConfig
+    from polyaxon_b200.schemas.hptuning import HPTuningConfig
+    n, d = 512, 16
+    keys = ['x%03d' % i for i in range(d)]
+    cfgs, raw = [], []
+    for g in range(n_groups):
+        X, y, _ = synthetic_problem(n, d, seed=1234 + g)
+        cfgs.append(HPTuningConfig.from_dict({
+            'seed': 1234 + g, 'concurrency': 1,
+            'bo': {'n_iterations': 5, 'n_initial_trials': 5, 'metric': {'name': 'm', 'optimization': 'maximize'},
+                   'utility_function': {'acquisition_function': 'ei', 'eps': 0.0, 'n_warmup': 100000, 'n_iter': 10,
+                                        'gaussian_process': {'kernel': 'matern', 'length_scale': 1.0, 'nu': 2.5,
+                                                             'n_restarts_optimizer': 4}}},
+            'matrix': {k: {'uniform': [0, 1]} for k in keys}}))
+        raw.append({'iteration': 1, 'experiment_ids': list(range(n)),
+                    'experiments_configs': [[i, dict(zip(keys, row.tolist()))] for i, row in enumerate(X)],
+                    'experiments_metrics': [[i, float(v)] for i, v in enumerate(y)]})
+    out = {'config': 'C5 share of one GPU: %d groups, d=16 n=512 matern2.5 ei N=1e5 S=10 R=5' % n_groups}
+    first = None
+    for workers in (1, 8):
+        times = []
+        for _ in range(4):
+            its = [BOIterationConfig.from_dict(r) for r in raw]
+            t0 = time.perf_counter()
+            got = suggest_groups(cfgs, its, workers=workers)
+            times.append(time.perf_counter() - t0)
+        first = got if first is None else first
+        out['groups_per_s_workers%d' % workers] = n_groups / float(np.median(times[1:]))
+        out['same_suggestions'] = bool(got == first)
+    return out
+
+
 def workload_config(args, world):
     return {'workload': 'C3: BO 32-dim continuous, POI eps=0, matern nu=1.5, n_obs=2048, '
                         'num_warmup=%d candidates (global), fixed GP state theta=%.1f' % (args.candidates, THETA),
@@ -369,6 +442,14 @@ def main():
                 line['latency'] = measure_latency()
             except Exception as exc:
                 line['latency'] = 'failed: %r' % (exc,)
+            try:
+                line['fit_c4'] = measure_fit(h)
+            except Exception as exc:
+                line['fit_c4'] = 'failed: %r' % (exc,)
+            try:
+                line['groups_c5'] = measure_groups()
+            except Exception as exc:
+                line['groups_c5'] = 'failed: %r' % (exc,)
         print(json.dumps(line))
     h.close()
     if world > 1:

@@ -109,6 +109,7 @@ class Handle(object):
         self.n = self.d = 0
         self.resident_key = None
         self.held = None          # host-side record of the last fit (DeviceGaussianProcess, PLX_BO_REFIT_EVERY)
+        self.seed_cache = {}      # resident_key -> (x_seeds, generator state after the draws), UtilityFunction._warmup
 
     def close(self):
         if getattr(self, '_h', None):

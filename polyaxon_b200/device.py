@@ -1,29 +1,45 @@
-"""Process-wide device context: one C-ABI handle per (process, GPU).
+"""Process-wide device context: one C-ABI handle per (process, GPU, worker slot).
 
 The caller of the suggestion path is a Celery prefork worker (``cmd/celery_worker``): one thread
 per process, several processes per host.  Each process lazily opens one handle on the GPU named by
 ``PLX_BO_DEVICE`` (default: ``LOCAL_RANK`` under torchrun, else 0) and keeps it for its lifetime.
+
+``polyaxon_b200.groups.suggest_groups`` runs several independent groups at once from worker threads;
+each of those threads names a slot (``use_slot``) and gets a handle of its own -- own stream, own
+workspace, own resident candidate matrix -- so their kernels overlap on the GPU.  A handle is never
+shared between threads (the C ABI is not thread-safe per handle).
 """
 import os
+import threading
 
 from polyaxon_b200 import _lib
 
 _handles = {}
+_lock = threading.Lock()
+_tls = threading.local()
 
 
 def default_device():
     return int(os.environ.get('PLX_BO_DEVICE', os.environ.get('LOCAL_RANK', '0')))
 
 
+def use_slot(slot):
+    """Name the handle slot of the calling thread (0 = the process-wide default)."""
+    _tls.slot = int(slot)
+
+
 def get_handle(device=None):
     device = default_device() if device is None else int(device)
-    h = _handles.get(device)
-    if h is None:
-        h = _handles[device] = _lib.Handle(device)
+    key = (device, getattr(_tls, 'slot', 0))
+    with _lock:
+        h = _handles.get(key)
+        if h is None:
+            h = _handles[key] = _lib.Handle(device)
     return h
 
 
 def close_all():
-    for h in _handles.values():
-        h.close()
-    _handles.clear()
+    with _lock:
+        for h in _handles.values():
+            h.close()
+        _handles.clear()

@@ -5,19 +5,34 @@ groups are dealt to the ranks by contiguous range, every rank works through its 
 with the single-GPU path (no collective on the data path), and the suggestion dicts are gathered at
 the end.  Without torch.distributed all groups run on this process's GPU.
 
+On one GPU the groups of a rank are worked through by a few threads, each with a C-ABI handle of its
+own (own stream and workspace, ``device.use_slot``): a group of C5's size (n_obs = 512) fills neither
+the GPU nor the host thread that drives it, so the fit kernels, sweeps and host steps of different
+groups overlap.  ``workers=1`` (or ``PLX_BO_GROUP_WORKERS=1``) is the plain loop.  The result of a
+group does not depend on the worker that ran it.
+
 Each group is one call of ``BOSearchManager.get_suggestions(iteration_config)`` exactly as
 ``ExperimentGroup.get_suggestions()`` would make it (db/models/experiment_groups.py:270-274).
 """
 import os
+from concurrent.futures import ThreadPoolExecutor
 
-from polyaxon_b200 import dist as pdist
+from polyaxon_b200 import device, dist as pdist
 from polyaxon_b200.hpsearch.search_managers import get_search_algorithm_manager
 
 
-def suggest_groups(hptuning_configs, iteration_configs, gather=True):
+def _one_group(hptuning_config, iteration_config, g):
+    manager = get_search_algorithm_manager(hptuning_config)
+    if manager is None:
+        raise ValueError('group {} has no search algorithm manager'.format(g))
+    return manager.get_suggestions(iteration_config)
+
+
+def suggest_groups(hptuning_configs, iteration_configs, gather=True, workers=None):
     """``hptuning_configs[g]`` / ``iteration_configs[g]`` describe group g.  Returns a list with one
     entry per group (the list ``get_suggestions`` returns, or None); with ``gather=False`` under
-    torch.distributed only this rank's groups are filled in."""
+    torch.distributed only this rank's groups are filled in.  ``workers``: threads (and handles) used
+    for this rank's share, default ``PLX_BO_GROUP_WORKERS`` or 4."""
     if len(hptuning_configs) != len(iteration_configs):
         raise ValueError('one iteration config per hptuning config is required')
     rank, size = pdist.world()
@@ -27,11 +42,21 @@ def suggest_groups(hptuning_configs, iteration_configs, gather=True):
     previous = os.environ.get('PLX_BO_DISTRIBUTED')
     os.environ['PLX_BO_DISTRIBUTED'] = '0'          # inside a group the single-GPU path is used
     try:
-        for g in range(lo, hi):
-            manager = get_search_algorithm_manager(hptuning_configs[g])
-            if manager is None:
-                raise ValueError('group {} is not a Bayesian-optimisation group'.format(g))
-            out[g] = manager.get_suggestions(iteration_configs[g])
+        if workers is None:
+            workers = int(os.environ.get('PLX_BO_GROUP_WORKERS', '4') or 4)
+        workers = max(1, min(int(workers), hi - lo))
+        if workers == 1:
+            for g in range(lo, hi):
+                out[g] = _one_group(hptuning_configs[g], iteration_configs[g], g)
+        else:
+            def work(slot):
+                device.use_slot(slot + 1)                      # slot 0 stays with the calling thread
+                return [(g, _one_group(hptuning_configs[g], iteration_configs[g], g))
+                        for g in range(lo + slot, hi, workers)]
+            with ThreadPoolExecutor(max_workers=workers) as pool:
+                for part in pool.map(work, range(workers)):
+                    for g, suggestion in part:
+                        out[g] = suggestion
     finally:
         if previous is None:
             del os.environ['PLX_BO_DISTRIBUTED']

@@ -32,7 +32,6 @@ from polyaxon_b200.schemas.hptuning import (
 )
 
 THETA_BOUNDS = (float(np.log(1e-5)), float(np.log(1e5)))      # sklearn's default length_scale_bounds
-_SEED_CACHE = {}          # key -> (x_seeds, generator state after the draws); see UtilityFunction._warmup
 
 
 def _acq_id(name):
@@ -209,7 +208,7 @@ class UtilityFunction(object):
             digest.update(repr((state[0], state[2], state[3], state[4], n_warmup, n_iter)).encode())
             digest.update(bounds.tobytes())
             key = digest.hexdigest()
-        cached = _SEED_CACHE.get(key) if key is not None else None
+        cached = h.seed_cache.get(key) if key is not None else None
         if cached is not None and h.resident_key == key:
             x_seeds, state_after = cached
             rng.set_state(state_after)
@@ -227,8 +226,8 @@ class UtilityFunction(object):
             return max_acq, x_max, x_seeds
         if not drawn_on_device:
             h.candidates_set(x_tries, key=key)
-        _SEED_CACHE.clear()                      # one resident matrix per process
-        _SEED_CACHE[key] = (x_seeds.copy(), rng.get_state())
+        h.seed_cache.clear()                     # one resident matrix per handle
+        h.seed_cache[key] = (x_seeds.copy(), rng.get_state())
         max_acq, x_max = self._sweep_resident(h, acq, args, n_warmup)
         return max_acq, x_max, x_seeds
 

@@ -121,7 +121,6 @@ def test_resident_candidate_cache_is_transparent(monkeypatch):
     """Second call of a seeded group reuses the device-resident candidate matrix: same suggestion,
     same generator state afterwards, as with the cache switched off."""
     from polyaxon_b200 import device
-    from polyaxon_b200.hpsearch.search_managers.bayesian_optimization import acquisition_function as af
     from polyaxon_b200.hpsearch.search_managers.bayesian_optimization.optimizer import BOOptimizer
     g = load_golden('c5_d16_n128_m25_ei')
     d = g['X'].shape[1]
@@ -135,11 +134,11 @@ def test_resident_candidate_cache_is_transparent(monkeypatch):
         s = opt.get_suggestion()
         return s, opt.utility_function.random_generator.get_state()[1].copy()
 
-    af._SEED_CACHE.clear()
+    device.get_handle().seed_cache.clear()
     device.get_handle().resident_key = None
     first, state1 = run()
     key = device.get_handle().resident_key
-    assert key is not None and key in af._SEED_CACHE
+    assert key is not None and key in device.get_handle().seed_cache
     uploads = {'n': 0}
     from polyaxon_b200 import _lib
     real_set = _lib.Handle.candidates_set
@@ -188,7 +187,7 @@ def test_device_mt19937_reproduces_numpy_bit_for_bit(d, n_cand, pre_draws):
 
 
 def test_device_rng_and_host_rng_give_the_same_suggestion(monkeypatch):
-    from polyaxon_b200.hpsearch.search_managers.bayesian_optimization import acquisition_function as af
+    from polyaxon_b200 import device
     from polyaxon_b200.hpsearch.search_managers.bayesian_optimization.optimizer import BOOptimizer
     g = load_golden('c1_d2_n15_m25_ucb')
     keys = ['x000', 'x001']
@@ -197,7 +196,7 @@ def test_device_rng_and_host_rng_give_the_same_suggestion(monkeypatch):
     out = []
     for flag in ('1', '0'):
         monkeypatch.setenv('PLX_BO_DEVICE_RNG', flag)
-        af._SEED_CACHE.clear()
+        device.get_handle().seed_cache.clear()
         opt = BOOptimizer(hptuning_config=cfg)
         opt.add_observations(configs=configs, metrics=g['y'].tolist())
         out.append((opt.get_suggestion(), opt.utility_function.random_generator.get_state()[1].copy()))
@@ -223,7 +222,7 @@ def test_suggest_groups_runs_independent_groups_in_order():
             'iteration': 1, 'experiment_ids': list(range(64)),
             'experiments_configs': [[i, dict(zip(keys, row.tolist()))] for i, row in enumerate(X)],
             'experiments_metrics': [[i, float(v)] for i, v in enumerate(y)]}))
-    together = suggest_groups(cfgs, its)
+    together = suggest_groups(cfgs, its)                 # three worker threads, a handle each
     # BOIterationConfig.combined_* extends its lists in place (as the reference's does), so rebuild them
     its2 = [BOIterationConfig.from_dict({'iteration': 1, 'experiment_ids': it.experiment_ids,
                                          'experiments_configs': it.experiments_configs,
@@ -231,6 +230,10 @@ def test_suggest_groups_runs_independent_groups_in_order():
     alone = [get_search_algorithm_manager(c).get_suggestions(i) for c, i in zip(cfgs, its2)]
     assert together == alone
     assert len({tuple(sorted(s[0].items())) for s in together}) == 3
+    its3 = [BOIterationConfig.from_dict({'iteration': 1, 'experiment_ids': it.experiment_ids,
+                                         'experiments_configs': it.experiments_configs,
+                                         'experiments_metrics': it.experiments_metrics}) for it in its2]
+    assert suggest_groups(cfgs, its3, workers=1) == alone
 
 
 def test_hold_theta_between_refits_is_opt_in(monkeypatch):

@@ -8,7 +8,7 @@ sys.path.insert(0, '.')
 import torch
 import torch.distributed as dist
 from oracle.reference_path import synthetic_problem
-from polyaxon_b200.hpsearch.search_managers.bayesian_optimization import acquisition_function as af
+from polyaxon_b200 import device
 from polyaxon_b200.hpsearch.search_managers.bayesian_optimization.optimizer import BOOptimizer
 from polyaxon_b200.schemas.hptuning import HPTuningConfig
 
@@ -29,7 +29,7 @@ configs = [dict(zip(keys, row.tolist())) for row in X]
 
 
 def run():
-    af._SEED_CACHE.clear()
+    device.get_handle().seed_cache.clear()
     opt = BOOptimizer(hptuning_config=cfg)
     opt.add_observations(configs=configs, metrics=y.tolist())
     t0 = time.perf_counter()
