@@ -383,6 +383,110 @@ __global__ void __launch_bounds__(256) kmat_kernel(const double* __restrict__ Xs
 constexpr int POTF_LD = 129;
 constexpr int POTF_SMEM = (128 * POTF_LD + 256) * 8;
 
+// Columns 16*BJ .. 16*BJ+15 of the register-tiled factorisation.  Thread (ti, tc) holds
+// A[ti + 16 a][tc + 16 q]; in this range only a, q >= BJ are live, so that is all that is updated.
+// Column j arrives in colbuf[j & 1] already updated through step j - 1: the threads that own column
+// j + 1 apply step j to it first and publish it BEFORE the barrier, everybody applies step j to the
+// rest of the tile AFTER it -- that bulk update overlaps the pivot chain of step j + 1.
+template <int BJ>
+__device__ __forceinline__ bool potf_factor_cols(double (&acc)[8][8], double* S, double (*colbuf)[128], double* dl,
+                                                 double* wdiag, int* bad, int k, int m, int ti, int tc, int tid) {
+#pragma unroll 1
+  for (int jj = 0; jj < 16; ++jj) {
+    const int j = 16 * BJ + jj;
+    if (j >= m) return false;
+    const double* cb = colbuf[j & 1];
+    double* nx = colbuf[(j + 1) & 1];
+    double ajj = cb[j];
+    if (!(ajj > 0.0)) {                 // non-positive or NaN pivot: not positive definite
+      if (tid == 0 && *bad == 0) *bad = k * 128 + j + 1;
+      ajj = 1.0;
+    }
+    // root and reciprocal root from one hardware seed and a coupled Newton step (<= 2 ulp): the
+    // pivot -> sqrt -> divide chain is on the critical path of every column
+    double y0;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y0) : "d"(ajj));
+    const double e0 = fma(ajj, -(y0 * y0), 1.0);
+    double inv = fma(fma(e0, 0.375, 0.5), y0 * e0, y0);
+    double ljj = ajj * inv;
+    ljj = fma(fma(ljj, -ljj, ajj), 0.5 * inv, ljj);
+    inv = fma(fma(-ljj, inv, 1.0), inv, inv);            // 1 / ljj (LAPACK dpotf2 scales by the reciprocal too)
+    double li[8], lc[8];
+#pragma unroll
+    for (int a = BJ; a < 8; ++a) { li[a] = cb[ti + 16 * a] * inv; lc[a] = cb[tc + 16 * a] * inv; }
+    if (jj < 15) {
+      if (tc == jj + 1) {
+#pragma unroll
+        for (int a = BJ; a < 8; ++a) nx[ti + 16 * a] = fma(-li[a], lc[BJ], acc[a][BJ]);
+      }
+    } else if constexpr (BJ < 7) {
+      if (tc == 0) {
+#pragma unroll
+        for (int a = BJ + 1; a < 8; ++a) nx[ti + 16 * a] = fma(-li[a], lc[BJ + 1], acc[a][BJ + 1]);
+      }
+    }
+    if (tc == jj) {
+#pragma unroll
+      for (int a = BJ; a < 8; ++a) { const int i = ti + 16 * a; if (i > j) S[i * POTF_LD + j] = li[a]; }
+    }
+    if (tid == 0) { dl[j] = ljj; wdiag[j] = inv; }
+    __syncthreads();
+#pragma unroll
+    for (int a = BJ; a < 8; ++a)
+#pragma unroll
+      for (int q = BJ; q < 8; ++q) acc[a][q] = fma(-li[a], lc[q], acc[a][q]);
+  }
+  return true;
+}
+
+// Rows 16*BJ .. 16*BJ+15 of W = L^-1 by right-looking forward substitution on the identity, same
+// tiling: acc[a][q] = W[ti + 16 a][tc + 16 q], live for a >= BJ (rows still open) and q <= BJ
+// (W is lower triangular).  Row j arrives finished in colbuf[j & 1]; the owners of row j + 1 apply
+// step j to it, scale it and publish it before the barrier, the bulk update follows the barrier.
+// W[j][c] (c < j) is parked at S[c][j], the diagonal stays in wdiag.
+template <int BJ>
+__device__ __forceinline__ bool potf_inverse_rows(double (&acc)[8][8], double* S, double (*colbuf)[128],
+                                                  const double* wdiag, int m, int ti, int tc, int tid) {
+#pragma unroll 1
+  for (int jj = 0; jj < 16; ++jj) {
+    const int j = 16 * BJ + jj;
+    if (j >= m) return false;
+    const double* rb = colbuf[j & 1];
+    double* nx = colbuf[(j + 1) & 1];
+    double wr[8], lcol[8];
+#pragma unroll
+    for (int q = 0; q <= BJ; ++q) wr[q] = rb[tc + 16 * q];
+#pragma unroll
+    for (int a = BJ; a < 8; ++a) {
+      const int i = ti + 16 * a;
+      lcol[a] = (i > j && i < m) ? S[i * POTF_LD + j] : 0.0;
+    }
+    if (j + 1 < m) {
+      if (jj < 15) {
+        if (ti == jj + 1) {
+          const double w1 = wdiag[j + 1];
+#pragma unroll
+          for (int q = 0; q <= BJ; ++q) nx[tc + 16 * q] = fma(-lcol[BJ], wr[q], acc[BJ][q]) * w1;
+        }
+      } else if constexpr (BJ < 7) {
+        if (ti == 0) {
+          const double w1 = wdiag[j + 1];
+#pragma unroll
+          for (int q = 0; q <= BJ; ++q) nx[tc + 16 * q] = fma(-lcol[BJ + 1], wr[q], acc[BJ + 1][q]) * w1;
+          nx[tc + 16 * (BJ + 1)] = acc[BJ + 1][BJ + 1] * w1;
+        }
+      }
+    }
+    if (tid < j) S[tid * POTF_LD + j] = rb[tid];
+    __syncthreads();
+#pragma unroll
+    for (int a = BJ; a < 8; ++a)
+#pragma unroll
+      for (int q = 0; q <= BJ; ++q) acc[a][q] = fma(-lcol[a], wr[q], acc[a][q]);
+  }
+  return true;
+}
+
 __global__ void __launch_bounds__(256) potf2_inv_kernel(BatchPtrs bp, int k, int n, int npad,
                                                         double* __restrict__ logdet, int* __restrict__ info) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -413,46 +517,19 @@ __global__ void __launch_bounds__(256) potf2_inv_kernel(BatchPtrs bp, int k, int
   for (int a = 0; a < 8; ++a)
 #pragma unroll
     for (int q = 0; q < 8; ++q) acc[a][q] = S[(ti + 16 * a) * POTF_LD + tc + 16 * q];
-  for (int j = 0; j < m; ++j) {
-    const int bj = j >> 4;
-    double* cb = colbuf[j & 1];
-    if (tc == (j & 15)) {
+  if (tc == 0) {
 #pragma unroll
-      for (int a = 0; a < 8; ++a) {
-        double v = acc[a][0];
-#pragma unroll
-        for (int q = 1; q < 8; ++q) v = (q == bj) ? acc[a][q] : v;
-        cb[ti + 16 * a] = v;
-      }
-    }
-    __syncthreads();
-    double ajj = cb[j];
-    if (!(ajj > 0.0)) {                 // non-positive or NaN pivot: not positive definite
-      if (tid == 0 && bad == 0) bad = k * 128 + j + 1;
-      ajj = 1.0;
-    }
-    // root and reciprocal root from one hardware seed and a coupled Newton step (<= 2 ulp): the
-    // pivot -> sqrt -> divide chain is on the critical path of every column
-    double y0;
-    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y0) : "d"(ajj));
-    const double e0 = fma(ajj, -(y0 * y0), 1.0);
-    double inv = fma(fma(e0, 0.375, 0.5), y0 * e0, y0);
-    double ljj = ajj * inv;
-    ljj = fma(fma(ljj, -ljj, ajj), 0.5 * inv, ljj);
-    inv = fma(fma(-ljj, inv, 1.0), inv, inv);            // 1 / ljj (LAPACK dpotf2 scales by the reciprocal too)
-    double li[8], lc[8];
-#pragma unroll
-    for (int a = 0; a < 8; ++a) { li[a] = cb[ti + 16 * a] * inv; lc[a] = cb[tc + 16 * a] * inv; }
-    if (tc == (j & 15)) {
-#pragma unroll
-      for (int a = 0; a < 8; ++a) { const int i = ti + 16 * a; if (i > j) S[i * POTF_LD + j] = li[a]; }
-    }
-    if (tid == 0) { dl[j] = ljj; wdiag[j] = inv; }
-#pragma unroll
-    for (int a = 0; a < 8; ++a)
-#pragma unroll
-      for (int q = 0; q < 8; ++q) acc[a][q] = fma(-li[a], lc[q], acc[a][q]);
+    for (int a = 0; a < 8; ++a) colbuf[0][ti + 16 * a] = acc[a][0];
   }
+  __syncthreads();
+  potf_factor_cols<0>(acc, S, colbuf, dl, wdiag, &bad, k, m, ti, tc, tid) &&
+      potf_factor_cols<1>(acc, S, colbuf, dl, wdiag, &bad, k, m, ti, tc, tid) &&
+      potf_factor_cols<2>(acc, S, colbuf, dl, wdiag, &bad, k, m, ti, tc, tid) &&
+      potf_factor_cols<3>(acc, S, colbuf, dl, wdiag, &bad, k, m, ti, tc, tid) &&
+      potf_factor_cols<4>(acc, S, colbuf, dl, wdiag, &bad, k, m, ti, tc, tid) &&
+      potf_factor_cols<5>(acc, S, colbuf, dl, wdiag, &bad, k, m, ti, tc, tid) &&
+      potf_factor_cols<6>(acc, S, colbuf, dl, wdiag, &bad, k, m, ti, tc, tid) &&
+      potf_factor_cols<7>(acc, S, colbuf, dl, wdiag, &bad, k, m, ti, tc, tid);
   __syncthreads();
   if (tid >= m && tid < 128) { dl[tid] = 1.0; wdiag[tid] = 1.0; }
   // strict upper triangle will receive W^T; padding rows of L are zero
@@ -470,34 +547,16 @@ __global__ void __launch_bounds__(256) potf2_inv_kernel(BatchPtrs bp, int k, int
   for (int a = 0; a < 8; ++a)
 #pragma unroll
     for (int q = 0; q < 8; ++q) acc[a][q] = (ti + 16 * a == tc + 16 * q) ? 1.0 : 0.0;
-  for (int j = 0; j < m; ++j) {
-    const int aj = j >> 4;
-    double* rb = colbuf[j & 1];
-    __syncthreads();                    // everyone is done with the buffer of step j - 2 ... and S reads
-    if (ti == (j & 15)) {
-      const double wjj = wdiag[j];
-#pragma unroll
-      for (int q = 0; q < 8; ++q) {
-        double v = acc[0][q];
-#pragma unroll
-        for (int a = 1; a < 8; ++a) v = (a == aj) ? acc[a][q] : v;
-        rb[tc + 16 * q] = v * wjj;
-      }
-    }
-    __syncthreads();
-    double wr[8], lcol[8];
-#pragma unroll
-    for (int a = 0; a < 8; ++a) {
-      wr[a] = rb[tc + 16 * a];
-      const int i = ti + 16 * a;
-      lcol[a] = (i > j && i < m) ? S[i * POTF_LD + j] : 0.0;
-    }
-#pragma unroll
-    for (int a = 0; a < 8; ++a)
-#pragma unroll
-      for (int q = 0; q < 8; ++q) acc[a][q] = fma(-lcol[a], wr[q], acc[a][q]);
-    if (tid < j) S[tid * POTF_LD + j] = rb[tid];
-  }
+  if (ti == 0) colbuf[0][tc] = (tc == 0) ? wdiag[0] : 0.0;       // row 0 of W
+  __syncthreads();
+  potf_inverse_rows<0>(acc, S, colbuf, wdiag, m, ti, tc, tid) &&
+      potf_inverse_rows<1>(acc, S, colbuf, wdiag, m, ti, tc, tid) &&
+      potf_inverse_rows<2>(acc, S, colbuf, wdiag, m, ti, tc, tid) &&
+      potf_inverse_rows<3>(acc, S, colbuf, wdiag, m, ti, tc, tid) &&
+      potf_inverse_rows<4>(acc, S, colbuf, wdiag, m, ti, tc, tid) &&
+      potf_inverse_rows<5>(acc, S, colbuf, wdiag, m, ti, tc, tid) &&
+      potf_inverse_rows<6>(acc, S, colbuf, wdiag, m, ti, tc, tid) &&
+      potf_inverse_rows<7>(acc, S, colbuf, wdiag, m, ti, tc, tid);
   __syncthreads();
   double* Lo = bp.L + b * bp.mat_stride + (static_cast<size_t>(k) * 128) * ld + k * 128;
   double* Uo = bp.U + b * bp.mat_stride + (static_cast<size_t>(k) * 128) * ld + k * 128;
