@@ -39,6 +39,7 @@ struct plx_bo {
   // batched fit workspace
   int bcap = 0, wnpad = 0;
   BatchPtrs bp{};
+  FitMaps fit_maps{};          // 3-D tensor maps over A, L, U, T, W of the workspace
   double *d_thetas = nullptr, *d_logdet = nullptr, *d_w = nullptr, *d_alpha = nullptr, *d_partial = nullptr,
          *d_lml = nullptr, *d_grad = nullptr, *d_xs = nullptr;
   size_t xs_cap = 0;
@@ -184,11 +185,11 @@ extern "C" int plx_bo_create(int device, plx_bo_handle* out) {
   h->encode = reinterpret_cast<EncodeTiledFn>(fn);
   // opt in to large dynamic shared memory once
   cudaFuncSetAttribute(potf2_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, POTF_SMEM);
-  cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM);
-  cudaFuncSetAttribute(chol_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM);
-  cudaFuncSetAttribute(trtri_t_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM);
-  cudaFuncSetAttribute(trtri_u_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM);
-  cudaFuncSetAttribute(kinv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM);
+  cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FIT_SMEM);
+  cudaFuncSetAttribute(chol_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FIT_SMEM);
+  cudaFuncSetAttribute(trtri_t_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FIT_SMEM);
+  cudaFuncSetAttribute(trtri_u_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FIT_SMEM);
+  cudaFuncSetAttribute(kinv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FIT_SMEM);
   cudaFuncSetAttribute(sweep_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SWEEP_SMEM);
   cudaFuncSetAttribute(sweep_simple_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SWEEP_SIMPLE_SMEM);
   if (cudaGetLastError() != cudaSuccess) return bail("cudaFuncSetAttribute failed (is the library built for this GPU?)");
@@ -259,6 +260,20 @@ extern "C" int plx_gp_set_data(plx_bo_handle h, const double* X, const double* y
   return PLX_OK;
 }
 
+// 3-D map over a batched buffer: `cols` doubles per row, `rows` rows per batch member, members
+// `stride` doubles apart; box = one 16 x 128 chunk of one member, 128-byte swizzle.
+static int make_map3(plx_bo* h, CUtensorMap* map, double* base, size_t cols, size_t rows, size_t batch, size_t stride) {
+  cuuint64_t dims[3] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows), static_cast<cuuint64_t>(batch)};
+  cuuint64_t strides[2] = {static_cast<cuuint64_t>(cols) * 8, static_cast<cuuint64_t>(stride) * 8};
+  cuuint32_t box[3] = {KCH, TILE, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  const CUresult r = h->encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, base, dims, strides, box, estr,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(h, PLX_ERR_CUDA, "cuTensorMapEncodeTiled (3-D) failed with code " + std::to_string(r));
+  return PLX_OK;
+}
+
 static int ensure_batch(plx_bo* h, int B) {
   if (B <= h->bcap && h->wnpad == h->npad) return PLX_OK;
   const int cap = std::max(B, h->wnpad == h->npad ? h->bcap : 0);
@@ -285,6 +300,15 @@ static int ensure_batch(plx_bo* h, int B) {
   CK(cudaMalloc(&h->d_info, sizeof(int) * cap));
   h->bp.mat_stride = mat; h->bp.blk_stride = blk;
   h->bcap = cap; h->wnpad = h->npad;
+  {
+    int r;
+    const size_t np = h->npad;
+    if ((r = make_map3(h, &h->fit_maps.A, h->bp.A, np, np, cap, mat)) != PLX_OK) return r;
+    if ((r = make_map3(h, &h->fit_maps.L, h->bp.L, np, np, cap, mat)) != PLX_OK) return r;
+    if ((r = make_map3(h, &h->fit_maps.U, h->bp.U, np, np, cap, mat)) != PLX_OK) return r;
+    if ((r = make_map3(h, &h->fit_maps.T, h->bp.T, np, np, cap, mat)) != PLX_OK) return r;
+    if ((r = make_map3(h, &h->fit_maps.W, h->bp.W, 128, static_cast<size_t>(h->nb) * 128, cap, blk)) != PLX_OK) return r;
+  }
   return PLX_OK;
 }
 
@@ -309,17 +333,17 @@ static int launch_lml(plx_bo* h, int B, bool want_grad) {
     LAUNCH_CHECK("potf2_inv_kernel");
     const int T = nb - k - 1;
     if (T > 0) {
-      chol_panel_kernel<<<dim3(T, B), 256, GEMM_SMEM, st>>>(h->bp, k, npad);
+      chol_panel_kernel<<<dim3(T, B), 384, FIT_SMEM, st>>>(h->fit_maps.A, h->fit_maps.W, h->bp, k, npad);
       LAUNCH_CHECK("chol_panel_kernel");
-      chol_syrk_kernel<<<dim3(T * (T + 1) / 2, B), 256, GEMM_SMEM, st>>>(h->bp, k, npad);
+      chol_syrk_kernel<<<dim3(T * (T + 1) / 2, B), 384, FIT_SMEM, st>>>(h->fit_maps.L, h->bp, k, npad);
       LAUNCH_CHECK("chol_syrk_kernel");
     }
   }
   for (int s = 1; s < nb; s *= 2) {               // recursive doubling: 2 launches per level
     const int tiles = ((nb + 2 * s - 1) / (2 * s)) * s * s;
-    trtri_t_kernel<<<dim3(tiles, B), 256, GEMM_SMEM, st>>>(h->bp, s, nb, npad);
+    trtri_t_kernel<<<dim3(tiles, B), 384, FIT_SMEM, st>>>(h->fit_maps.U, h->fit_maps.L, h->bp, s, nb, npad);
     LAUNCH_CHECK("trtri_t_kernel");
-    trtri_u_kernel<<<dim3(tiles, B), 256, GEMM_SMEM, st>>>(h->bp, s, nb, npad);
+    trtri_u_kernel<<<dim3(tiles, B), 384, FIT_SMEM, st>>>(h->fit_maps.T, h->fit_maps.A, h->bp, s, nb, npad);
     LAUNCH_CHECK("trtri_u_kernel");
   }
   uty_kernel<<<dim3(npad / 32, B), 256, 0, st>>>(h->bp, h->dy, npad, h->d_w);
@@ -327,7 +351,7 @@ static int launch_lml(plx_bo* h, int B, bool want_grad) {
   uw_kernel<<<dim3(npad / 8, B), 256, 0, st>>>(h->bp, h->d_w, npad, h->d_alpha);
   LAUNCH_CHECK("uw_kernel");
   if (want_grad) {
-    kinv_kernel<<<dim3(nb * (nb + 1) / 2, B), 256, GEMM_SMEM, st>>>(h->bp, npad);
+    kinv_kernel<<<dim3(nb * (nb + 1) / 2, B), 384, FIT_SMEM, st>>>(h->fit_maps.U, h->bp, npad);
     LAUNCH_CHECK("kinv_kernel");
     kmat_kernel<1><<<dim3(h->ntri, 1, B), 256, 0, st>>>(h->d_xs, n, h->d, npad, h->kind, h->mg, h->jitter, h->bp,
                                                        h->d_alpha, h->d_partial, h->ntri);

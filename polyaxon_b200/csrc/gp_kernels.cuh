@@ -15,7 +15,7 @@
 //   W[b]  nb x 128 x 128  inverses of the diagonal blocks of L (lower)
 //   T[b]  npad x ld  scratch of the triangular inverse
 #pragma once
-#include "mma_f64.cuh"
+#include "tma_ring.cuh"
 #include <math.h>
 
 namespace plx {
@@ -591,12 +591,63 @@ __global__ void __launch_bounds__(256) potf2_inv_kernel(BatchPtrs bp, int k, int
 }
 
 // ---------------------------------------------------------------------------------------------
-// 128x128-tile DMMA kernels of the blocked algorithms.  Each CTA: one output tile, 256 threads.
+// 128x128-tile DMMA kernels of the blocked algorithms.  Each CTA: one output tile, 384 threads:
+// warps 0-7 run the tensor pipe (232 registers), warps 8-11 are the producer warpgroup (40
+// registers), whose elected lane streams 16-wide K-chunks of both operands through a ring of
+// shared-memory stages with 3-D bulk tensor loads (column, row, batch member; 128-byte swizzle).
 // ---------------------------------------------------------------------------------------------
-constexpr int GEMM_SMEM = 4 * TILE_BYTES + 1024;
+constexpr int GEMM_SMEM = 4 * TILE_BYTES + 1024;          // plain-load main loop (mma_f64.cuh)
+constexpr int FIT_STAGES = 4;
+constexpr int FIT_SMEM = FIT_STAGES * 2 * TILE_BYTES + 1024 + 128;
 
 __device__ __forceinline__ unsigned char* align1k(unsigned char* p) {
   return reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(p) + 1023) & ~static_cast<uintptr_t>(1023));
+}
+
+// Tensor maps of the batched fit workspace (built by the host when the workspace is allocated).
+struct FitMaps { CUtensorMap A, L, U, T, W; };
+
+// C[128][128] = sum over nch chunks of A[rowA0.., kA0 + 16c ..] * B[rowB0.., kB0 + 16c ..]^T for batch member b.
+// The consumer threads then run epilogue(acc) (acc in the layout of acc_row / acc_col); the producer
+// threads have nothing left to do.
+template <class Epilogue>
+__device__ __forceinline__ void tile_product_tma(const CUtensorMap* tmA, int rowA0, int kA0, const CUtensorMap* tmB,
+                                                 int rowB0, int kB0, int nch, int b, unsigned char* smem_raw,
+                                                 Epilogue epilogue) {
+  unsigned char* smem = align1k(smem_raw);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t s0 = smem_u32(smem);
+  const uint32_t bar0 = s0 + FIT_STAGES * 2 * TILE_BYTES;      // full[ST], empty[ST]
+  if (tid == 0) {
+    for (int s = 0; s < FIT_STAGES; ++s) { mbar_init(bar0 + 8 * s, 1); mbar_init(bar0 + 8 * (FIT_STAGES + s), 8); }
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  __syncthreads();
+  if (warp >= 8) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;\n");
+    if (warp == 8 && lane == 0) {
+      for (int c = 0; c < nch; ++c) {
+        const uint32_t s = c % FIT_STAGES, ph = (c / FIT_STAGES) & 1;
+        mbar_wait(bar0 + 8 * (FIT_STAGES + s), ph ^ 1);
+        const uint32_t full = bar0 + 8 * s;
+        mbar_expect_tx(full, 2 * TILE_BYTES);
+        tma_load_3d(s0 + s * 2 * TILE_BYTES, tmA, kA0 + c * KCH, rowA0, b, full);
+        tma_load_3d(s0 + s * 2 * TILE_BYTES + TILE_BYTES, tmB, kB0 + c * KCH, rowB0, b, full);
+      }
+    }
+    return;
+  }
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 232;\n");
+  WarpAcc acc;
+  acc.zero();
+  for (int c = 0; c < nch; ++c) {
+    const uint32_t s = c % FIT_STAGES, ph = (c / FIT_STAGES) & 1;
+    mbar_wait(bar0 + 8 * s, ph);
+    mma_chunk_pf(acc, s0 + s * 2 * TILE_BYTES, s0 + s * 2 * TILE_BYTES + TILE_BYTES, warp, lane, 0);
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bar0 + 8 * (FIT_STAGES + s));
+  }
+  epilogue(acc);
 }
 
 template <bool NEG, bool SUB>
@@ -616,16 +667,15 @@ __device__ __forceinline__ void store_tile(const WarpAcc& acc, double* C, size_t
 }
 
 // panel: L[i][k] = A[i][k] * W_k^T for i = k+1+blockIdx.x
-__global__ void __launch_bounds__(256, 1) chol_panel_kernel(BatchPtrs bp, int k, int npad) {
+__global__ void __launch_bounds__(384, 1) chol_panel_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                            const __grid_constant__ CUtensorMap tmW, BatchPtrs bp,
+                                                            int k, int npad) {
   extern __shared__ unsigned char smem_raw[];
-  unsigned char* smem = align1k(smem_raw);
   const int b = blockIdx.y, i = k + 1 + blockIdx.x;
   const size_t ld = npad;
-  const double* A = bp.A + b * bp.mat_stride + (static_cast<size_t>(i) * 128) * ld + k * 128;
-  const double* W = bp.W + b * bp.blk_stride + static_cast<size_t>(k) * 128 * 128;
-  WarpAcc acc; acc.zero();
-  mainloop_nt(acc, A, ld, W, 128, 0, 128, smem);
-  store_tile<false, false>(acc, bp.L + b * bp.mat_stride + (static_cast<size_t>(i) * 128) * ld + k * 128, ld);
+  double* out = bp.L + b * bp.mat_stride + (static_cast<size_t>(i) * 128) * ld + k * 128;
+  tile_product_tma(&tmA, i * 128, k * 128, &tmW, k * 128, 0, 128 / KCH, b, smem_raw,
+                   [&](const WarpAcc& acc) { store_tile<false, false>(acc, out, ld); });
 }
 
 __device__ __forceinline__ void tri_index(int p, int& ti, int& tj) {
@@ -636,18 +686,16 @@ __device__ __forceinline__ void tri_index(int p, int& ti, int& tj) {
 }
 
 // trailing update: A[i][j] -= L[i][k] * L[j][k]^T over the lower tiles of the trailing matrix
-__global__ void __launch_bounds__(256, 1) chol_syrk_kernel(BatchPtrs bp, int k, int npad) {
+__global__ void __launch_bounds__(384, 1) chol_syrk_kernel(const __grid_constant__ CUtensorMap tmL, BatchPtrs bp,
+                                                           int k, int npad) {
   extern __shared__ unsigned char smem_raw[];
-  unsigned char* smem = align1k(smem_raw);
   const int b = blockIdx.y;
   int ti, tj; tri_index(blockIdx.x, ti, tj);
   const int i = k + 1 + ti, j = k + 1 + tj;
   const size_t ld = npad;
-  const double* Li = bp.L + b * bp.mat_stride + (static_cast<size_t>(i) * 128) * ld + k * 128;
-  const double* Lj = bp.L + b * bp.mat_stride + (static_cast<size_t>(j) * 128) * ld + k * 128;
-  WarpAcc acc; acc.zero();
-  mainloop_nt(acc, Li, ld, Lj, ld, 0, 128, smem);
-  store_tile<false, true>(acc, bp.A + b * bp.mat_stride + (static_cast<size_t>(i) * 128) * ld + j * 128, ld);
+  double* out = bp.A + b * bp.mat_stride + (static_cast<size_t>(i) * 128) * ld + j * 128;
+  tile_product_tma(&tmL, i * 128, k * 128, &tmL, j * 128, k * 128, 128 / KCH, b, smem_raw,
+                   [&](const WarpAcc& acc) { store_tile<false, true>(acc, out, ld); });
 }
 
 // Triangular inverse by recursive doubling.  With L = [[L11, 0], [L21, L22]] and both diagonal
@@ -667,57 +715,54 @@ __device__ __forceinline__ bool trtri_tile(int t, int s, int nb, int& left0, int
 }
 
 // part 1: T[left0+a][right0+c] = sum_{m in left block, m >= a} U[left0+a][m] * L[right0+c][m]^T
-__global__ void __launch_bounds__(256, 1) trtri_t_kernel(BatchPtrs bp, int s, int nb, int npad) {
+__global__ void __launch_bounds__(384, 1) trtri_t_kernel(const __grid_constant__ CUtensorMap tmU,
+                                                         const __grid_constant__ CUtensorMap tmL, BatchPtrs bp, int s,
+                                                         int nb, int npad) {
   extern __shared__ unsigned char smem_raw[];
-  unsigned char* smem = align1k(smem_raw);
   const int b = blockIdx.y;
   int left0, right0, a, c;
   if (!trtri_tile(blockIdx.x, s, nb, left0, right0, a, c)) return;
   const size_t ld = npad;
-  const double* Ua = bp.U + b * bp.mat_stride + (static_cast<size_t>(left0 + a) * 128) * ld;
-  const double* Lc = bp.L + b * bp.mat_stride + (static_cast<size_t>(right0 + c) * 128) * ld;
-  WarpAcc acc; acc.zero();
-  mainloop_nt(acc, Ua, ld, Lc, ld, (left0 + a) * 128, (left0 + s) * 128, smem);
-  store_tile<false, false>(acc, bp.T + b * bp.mat_stride + (static_cast<size_t>(left0 + a) * 128) * ld + (right0 + c) * 128, ld);
+  double* out = bp.T + b * bp.mat_stride + (static_cast<size_t>(left0 + a) * 128) * ld + (right0 + c) * 128;
+  tile_product_tma(&tmU, (left0 + a) * 128, (left0 + a) * 128, &tmL, (right0 + c) * 128, (left0 + a) * 128,
+                   (s - a) * 128 / KCH, b, smem_raw, [&](const WarpAcc& acc) { store_tile<false, false>(acc, out, ld); });
 }
 
 // part 2: U[left0+a][right0+c] = -sum_{q in right block, q <= c} T[left0+a][q] * Z[right0+c][q]^T, and Z = U^T
-__global__ void __launch_bounds__(256, 1) trtri_u_kernel(BatchPtrs bp, int s, int nb, int npad) {
+__global__ void __launch_bounds__(384, 1) trtri_u_kernel(const __grid_constant__ CUtensorMap tmT,
+                                                         const __grid_constant__ CUtensorMap tmA, BatchPtrs bp, int s,
+                                                         int nb, int npad) {
   extern __shared__ unsigned char smem_raw[];
-  unsigned char* smem = align1k(smem_raw);
   const int b = blockIdx.y;
   int left0, right0, a, c;
   if (!trtri_tile(blockIdx.x, s, nb, left0, right0, a, c)) return;
   const size_t ld = npad;
-  const double* Ta = bp.T + b * bp.mat_stride + (static_cast<size_t>(left0 + a) * 128) * ld;
-  const double* Zc = bp.A + b * bp.mat_stride + (static_cast<size_t>(right0 + c) * 128) * ld;
-  WarpAcc acc; acc.zero();
-  mainloop_nt(acc, Ta, ld, Zc, ld, right0 * 128, (right0 + c + 1) * 128, smem);
-  store_tile<true, false>(acc, bp.U + b * bp.mat_stride + (static_cast<size_t>(left0 + a) * 128) * ld + (right0 + c) * 128, ld);
+  double* Uo = bp.U + b * bp.mat_stride + (static_cast<size_t>(left0 + a) * 128) * ld + (right0 + c) * 128;
   // transposed copy into Z[right0+c][left0+a]
   double* Zt = bp.A + b * bp.mat_stride + (static_cast<size_t>(right0 + c) * 128) * ld + (left0 + a) * 128;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  tile_product_tma(&tmT, (left0 + a) * 128, right0 * 128, &tmA, (right0 + c) * 128, right0 * 128, (c + 1) * 128 / KCH, b,
+                   smem_raw, [&](const WarpAcc& acc) {
+    store_tile<true, false>(acc, Uo, ld);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 #pragma unroll
-  for (int mf = 0; mf < 4; ++mf)
+    for (int mf = 0; mf < 4; ++mf)
 #pragma unroll
-    for (int nf = 0; nf < 8; ++nf)
+      for (int nf = 0; nf < 8; ++nf)
 #pragma unroll
-      for (int e = 0; e < 2; ++e)
-        Zt[static_cast<size_t>(acc_col(warp, lane, nf, e)) * ld + acc_row(warp, lane, mf)] = -acc.c[mf][nf][e];
+        for (int e = 0; e < 2; ++e)
+          Zt[static_cast<size_t>(acc_col(warp, lane, nf, e)) * ld + acc_row(warp, lane, mf)] = -acc.c[mf][nf][e];
+  });
 }
 
 // K^-1 = U U^T on the lower 128-tiles (diagonal tiles in full), written over A.
-__global__ void __launch_bounds__(256, 1) kinv_kernel(BatchPtrs bp, int npad) {
+__global__ void __launch_bounds__(384, 1) kinv_kernel(const __grid_constant__ CUtensorMap tmU, BatchPtrs bp, int npad) {
   extern __shared__ unsigned char smem_raw[];
-  unsigned char* smem = align1k(smem_raw);
   const int b = blockIdx.y;
   int ta, tb; tri_index(blockIdx.x, ta, tb);
   const size_t ld = npad;
-  const double* Ua = bp.U + b * bp.mat_stride + (static_cast<size_t>(ta) * 128) * ld;
-  const double* Ub = bp.U + b * bp.mat_stride + (static_cast<size_t>(tb) * 128) * ld;
-  WarpAcc acc; acc.zero();
-  mainloop_nt(acc, Ua, ld, Ub, ld, ta * 128, npad, smem);
-  store_tile<false, false>(acc, bp.A + b * bp.mat_stride + (static_cast<size_t>(ta) * 128) * ld + tb * 128, ld);
+  double* out = bp.A + b * bp.mat_stride + (static_cast<size_t>(ta) * 128) * ld + tb * 128;
+  tile_product_tma(&tmU, ta * 128, ta * 128, &tmU, tb * 128, ta * 128, (npad - ta * 128) / KCH, b, smem_raw,
+                   [&](const WarpAcc& acc) { store_tile<false, false>(acc, out, ld); });
 }
 
 // w[m] = sum_{a <= m} U[a][m] y[a]   (w = L^-1 y).  block (32, 8): 32 columns per CTA.
