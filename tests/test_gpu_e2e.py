@@ -1,5 +1,6 @@
 """GPU: the drop-in classes end to end (BOSearchManager -> BOOptimizer -> UtilityFunction) against
 what the real reference suggested for the same config, observations and seed (tests/golden)."""
+import os
 import warnings
 
 import numpy as np
@@ -292,3 +293,28 @@ def test_hold_theta_between_refits_is_opt_in(monkeypatch):
     fits['n'] = 0
     run(n - 1)
     assert fits['n'] == 1
+
+
+def test_unseeded_group_uses_and_advances_the_global_numpy_generator():
+    """seed=None: the reference draws from the numpy module itself (utils.py:37-38).  The device draw
+    must consume exactly the numbers numpy would have produced and leave the global state where the
+    host draw leaves it."""
+    from polyaxon_b200.hpsearch.search_managers.bayesian_optimization.optimizer import BOOptimizer
+    g = load_golden('c1_d2_n15_m25_ucb')
+    keys = ['x000', 'x001']
+    cfg = _config(g, {k: {'uniform': [0, 1]} for k in keys})
+    cfg.seed = None
+    configs = [dict(zip(keys, row.tolist())) for row in g['X']]
+    out = []
+    for flag in ('1', '0'):
+        os.environ['PLX_BO_DEVICE_RNG'] = flag
+        try:
+            np.random.seed(4242)
+            opt = BOOptimizer(hptuning_config=cfg)
+            assert opt.utility_function.random_generator is np.random
+            opt.add_observations(configs=configs, metrics=g['y'].tolist())
+            out.append((opt.get_suggestion(), np.random.get_state()[1].copy(), np.random.get_state()[2]))
+        finally:
+            del os.environ['PLX_BO_DEVICE_RNG']
+    assert out[0][0] == out[1][0]
+    assert np.array_equal(out[0][1], out[1][1]) and out[0][2] == out[1][2]
