@@ -328,14 +328,27 @@ static int launch_lml(plx_bo* h, int B, bool want_grad) {
   kmat_kernel<0><<<dim3(t32 * (t32 + 1) / 2, 1, B), 256, 0, st>>>(h->d_xs, n, h->d, npad, h->kind, h->mg, h->jitter,
                                                                  h->bp, nullptr, nullptr, 0);
   LAUNCH_CHECK("kmat_kernel");
-  for (int k = 0; k < nb; ++k) {
-    potf2_inv_kernel<<<B, 256, POTF_SMEM, st>>>(h->bp, k, n, npad, h->d_logdet, h->d_info);
-    LAUNCH_CHECK("potf2_inv_kernel");
-    const int T = nb - k - 1;
-    if (T > 0) {
-      chol_panel_kernel<<<dim3(T, B), 384, FIT_SMEM, st>>>(h->fit_maps.A, h->fit_maps.W, h->bp, k, npad);
-      LAUNCH_CHECK("chol_panel_kernel");
-      chol_syrk_kernel<<<dim3(T * (T + 1) / 2, B), 384, FIT_SMEM, st>>>(h->fit_maps.L, h->bp, k, npad);
+  const int PANEL = 4;                             // block columns per panel of the factorisation
+  auto syrk_tiles = [&](int jlo, int jhi) { int t = 0; for (int j = jlo; j < jhi; ++j) t += nb - j; return t; };
+  for (int p0 = 0; p0 < nb; p0 += PANEL) {
+    const int p1 = std::min(p0 + PANEL, nb);
+    for (int k = p0; k < p1; ++k) {
+      potf2_inv_kernel<<<B, 256, POTF_SMEM, st>>>(h->bp, k, n, npad, h->d_logdet, h->d_info);
+      LAUNCH_CHECK("potf2_inv_kernel");
+      const int T = nb - k - 1;
+      if (T > 0) {
+        chol_panel_kernel<<<dim3(T, B), 384, FIT_SMEM, st>>>(h->fit_maps.A, h->fit_maps.W, h->bp, k, npad);
+        LAUNCH_CHECK("chol_panel_kernel");
+      }
+      if (k + 1 < p1) {                            // the panel's remaining columns need column k now
+        chol_syrk_kernel<<<dim3(syrk_tiles(k + 1, p1), B), 384, FIT_SMEM, st>>>(h->fit_maps.L, h->bp, k, 1, k + 1, p1,
+                                                                               nb, npad);
+        LAUNCH_CHECK("chol_syrk_kernel");
+      }
+    }
+    if (p1 < nb) {                                 // everything right of the panel: one update with the whole panel
+      chol_syrk_kernel<<<dim3(syrk_tiles(p1, nb), B), 384, FIT_SMEM, st>>>(h->fit_maps.L, h->bp, p0, p1 - p0, p1, nb, nb,
+                                                                          npad);
       LAUNCH_CHECK("chol_syrk_kernel");
     }
   }

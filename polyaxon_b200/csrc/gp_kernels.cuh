@@ -685,16 +685,22 @@ __device__ __forceinline__ void tri_index(int p, int& ti, int& tj) {
   tj = p - ti * (ti + 1) / 2;
 }
 
-// trailing update: A[i][j] -= L[i][k] * L[j][k]^T over the lower tiles of the trailing matrix
+// trailing update: A[i][j] -= sum over block columns kcol .. kcol+kw-1 of L[i][.] * L[j][.]^T for the tiles
+// with jlo <= j < jhi and j <= i < nb.  The factorisation works in panels of a few block columns:
+// inside a panel only the panel's own columns are updated after every block column (kw = 1), the rest
+// of the trailing matrix once per panel with the whole panel as the contraction (kw = panel width) --
+// fewer read-modify-write passes over A and longer runs of the tensor pipe per tile.
 __global__ void __launch_bounds__(384, 1) chol_syrk_kernel(const __grid_constant__ CUtensorMap tmL, BatchPtrs bp,
-                                                           int k, int npad) {
+                                                           int kcol, int kw, int jlo, int jhi, int nb, int npad) {
   extern __shared__ unsigned char smem_raw[];
   const int b = blockIdx.y;
-  int ti, tj; tri_index(blockIdx.x, ti, tj);
-  const int i = k + 1 + ti, j = k + 1 + tj;
+  int j = jlo, t = blockIdx.x;
+  while (j < jhi && t >= nb - j) { t -= nb - j; ++j; }
+  if (j >= jhi) return;
+  const int i = j + t;
   const size_t ld = npad;
   double* out = bp.A + b * bp.mat_stride + (static_cast<size_t>(i) * 128) * ld + j * 128;
-  tile_product_tma(&tmL, i * 128, k * 128, &tmL, j * 128, k * 128, 128 / KCH, b, smem_raw,
+  tile_product_tma(&tmL, i * 128, kcol * 128, &tmL, j * 128, kcol * 128, kw * 128 / KCH, b, smem_raw,
                    [&](const WarpAcc& acc) { store_tile<false, true>(acc, out, ld); });
 }
 
