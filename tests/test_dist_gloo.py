@@ -89,3 +89,40 @@ def test_two_rank_merge_over_gloo(case):
         assert i == want
         assert (np.isnan(v) and np.isnan(ys[want])) or v == ys[want]
         assert (rv, ri) == (2.0, 1)        # equal values: the later seed wins
+
+
+def _groups_worker(rank, world, port, out):
+    """suggest_groups deals groups to ranks by contiguous range and gathers the suggestion lists.  Random-search
+    groups need no GPU, so the dealing / gathering logic of config C5 runs here on CPU."""
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    from polyaxon_b200.groups import suggest_groups
+    from polyaxon_b200.schemas.hptuning import HPTuningConfig
+    cfgs = [HPTuningConfig.from_dict({'seed': 10 + g, 'concurrency': 1, 'random_search': {'n_experiments': 3},
+                                      'matrix': {'lr': {'uniform': [0, 1]}, 'units': {'values': [16, 32, 64]}}})
+            for g in range(5)]
+    everything = suggest_groups(cfgs, [None] * 5, workers=2)
+    mine_only = suggest_groups(cfgs, [None] * 5, gather=False, workers=1)
+    out[rank] = (everything, mine_only)
+    dist.destroy_process_group()
+
+
+def test_groups_are_dealt_to_ranks_and_gathered_over_gloo():
+    from polyaxon_b200.hpsearch.search_managers import get_search_algorithm_manager
+    from polyaxon_b200.schemas.hptuning import HPTuningConfig
+    port = _free_port()
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_groups_worker, args=(2, port, out), nprocs=2, join=True)
+    cfgs = [HPTuningConfig.from_dict({'seed': 10 + g, 'concurrency': 1, 'random_search': {'n_experiments': 3},
+                                      'matrix': {'lr': {'uniform': [0, 1]}, 'units': {'values': [16, 32, 64]}}})
+            for g in range(5)]
+    want = [get_search_algorithm_manager(c).get_suggestions() for c in cfgs]
+    for rank in range(2):
+        everything, mine_only = out[rank]
+        assert everything == want                                   # every rank holds every group's suggestions
+        lo, hi = pd.shard_range(5, rank, 2)
+        assert mine_only[lo:hi] == want[lo:hi]
+        assert all(s is None for s in mine_only[:lo] + mine_only[hi:])
+    assert os.environ.get('PLX_BO_DISTRIBUTED') is None
