@@ -22,6 +22,7 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
 struct plx_bo {
   int device = 0, num_sms = 148;
   cudaStream_t own_stream = nullptr, stream = nullptr, copy_stream = nullptr;
+  cudaStream_t fact_stream = nullptr;      // high priority: diagonal-block factorisations of the fit
   std::string err;
   long long launches = 0;
   EncodeTiledFn encode = nullptr;
@@ -173,6 +174,12 @@ extern "C" int plx_bo_create(int device, plx_bo_handle* out) {
   if (cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking) != cudaSuccess) return bail("stream create failed");
   if (cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking) != cudaSuccess) return bail("stream create failed");
   h->stream = h->own_stream;
+  {
+    int lo = 0, hi = 0;                                    // numerically lowest value = highest priority
+    if (cudaDeviceGetStreamPriorityRange(&lo, &hi) != cudaSuccess ||
+        cudaStreamCreateWithPriority(&h->fact_stream, cudaStreamNonBlocking, hi) != cudaSuccess)
+      return bail("priority stream create failed");
+  }
   for (int i = 0; i < 2; ++i) {
     if (cudaEventCreateWithFlags(&h->ev_copy[i], cudaEventDisableTiming) != cudaSuccess) return bail("event create failed");
     if (cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming) != cudaSuccess) return bail("event create failed");
@@ -216,6 +223,7 @@ extern "C" void plx_bo_destroy(plx_bo_handle h) {
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+  if (h->fact_stream) cudaStreamDestroy(h->fact_stream);
   delete h;
 }
 
@@ -328,28 +336,41 @@ static int launch_lml(plx_bo* h, int B, bool want_grad) {
   kmat_kernel<0><<<dim3(t32 * (t32 + 1) / 2, 1, B), 256, 0, st>>>(h->d_xs, n, h->d, npad, h->kind, h->mg, h->jitter,
                                                                  h->bp, nullptr, nullptr, 0);
   LAUNCH_CHECK("kmat_kernel");
-  const int PANEL = 4;                             // block columns per panel of the factorisation
+  // Blocked right-looking factorisation in panels of PANEL block columns.  The diagonal-block kernel is a
+  // serial chain of 128 column steps on one CTA per theta, so it runs on a second stream: the trailing
+  // update that feeds it is issued in two parts, the next diagonal tile first, and potf2(k + 1) then
+  // overlaps the rest of that update.
+  const int PANEL = 4;
+  cudaStream_t s2 = h->fact_stream;
+  cudaEvent_t ev_diag = h->ev_copy[0], ev_fact = h->ev_done[0];
   auto syrk_tiles = [&](int jlo, int jhi) { int t = 0; for (int j = jlo; j < jhi; ++j) t += nb - j; return t; };
+  potf2_inv_kernel<<<B, 256, POTF_SMEM, st>>>(h->bp, 0, n, npad, h->d_logdet, h->d_info);
+  LAUNCH_CHECK("potf2_inv_kernel");
   for (int p0 = 0; p0 < nb; p0 += PANEL) {
     const int p1 = std::min(p0 + PANEL, nb);
     for (int k = p0; k < p1; ++k) {
-      potf2_inv_kernel<<<B, 256, POTF_SMEM, st>>>(h->bp, k, n, npad, h->d_logdet, h->d_info);
-      LAUNCH_CHECK("potf2_inv_kernel");
+      if (k > 0) CK(cudaStreamWaitEvent(st, ev_fact, 0));          // potf2(k) ran on the second stream
       const int T = nb - k - 1;
-      if (T > 0) {
-        chol_panel_kernel<<<dim3(T, B), 384, FIT_SMEM, st>>>(h->fit_maps.A, h->fit_maps.W, h->bp, k, npad);
-        LAUNCH_CHECK("chol_panel_kernel");
-      }
-      if (k + 1 < p1) {                            // the panel's remaining columns need column k now
-        chol_syrk_kernel<<<dim3(syrk_tiles(k + 1, p1), B), 384, FIT_SMEM, st>>>(h->fit_maps.L, h->bp, k, 1, k + 1, p1,
-                                                                               nb, npad);
+      if (T == 0) break;
+      chol_panel_kernel<<<dim3(T, B), 384, FIT_SMEM, st>>>(h->fit_maps.A, h->fit_maps.W, h->bp, k, npad);
+      LAUNCH_CHECK("chol_panel_kernel");
+      // inside the panel only its remaining columns need column k now; after the panel's last column
+      // everything to its right is updated once with the whole panel as the contraction
+      const bool inside = k + 1 < p1;
+      const int kcol = inside ? k : p0, kw = inside ? 1 : p1 - p0;
+      const int jlo = k + 1, jhi = inside ? p1 : nb;
+      const int tiles = syrk_tiles(jlo, jhi);
+      chol_syrk_kernel<<<dim3(1, B), 384, FIT_SMEM, st>>>(h->fit_maps.L, h->bp, kcol, kw, jlo, jhi, nb, npad, 0);
+      LAUNCH_CHECK("chol_syrk_kernel");
+      CK(cudaEventRecord(ev_diag, st));
+      CK(cudaStreamWaitEvent(s2, ev_diag, 0));
+      potf2_inv_kernel<<<B, 256, POTF_SMEM, s2>>>(h->bp, k + 1, n, npad, h->d_logdet, h->d_info);
+      LAUNCH_CHECK("potf2_inv_kernel");
+      CK(cudaEventRecord(ev_fact, s2));
+      if (tiles > 1) {
+        chol_syrk_kernel<<<dim3(tiles - 1, B), 384, FIT_SMEM, st>>>(h->fit_maps.L, h->bp, kcol, kw, jlo, jhi, nb, npad, 1);
         LAUNCH_CHECK("chol_syrk_kernel");
       }
-    }
-    if (p1 < nb) {                                 // everything right of the panel: one update with the whole panel
-      chol_syrk_kernel<<<dim3(syrk_tiles(p1, nb), B), 384, FIT_SMEM, st>>>(h->fit_maps.L, h->bp, p0, p1 - p0, p1, nb, nb,
-                                                                          npad);
-      LAUNCH_CHECK("chol_syrk_kernel");
     }
   }
   for (int s = 1; s < nb; s *= 2) {               // recursive doubling: 2 launches per level

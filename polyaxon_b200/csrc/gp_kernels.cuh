@@ -690,11 +690,14 @@ __device__ __forceinline__ void tri_index(int p, int& ti, int& tj) {
 // inside a panel only the panel's own columns are updated after every block column (kw = 1), the rest
 // of the trailing matrix once per panel with the whole panel as the contraction (kw = panel width) --
 // fewer read-modify-write passes over A and longer runs of the tensor pipe per tile.
+// Tiles are numbered column by column from (jlo, jlo); the launch covers tiles t0 .. t0 + gridDim.x - 1, which
+// lets the host issue tile 0 -- the next diagonal block -- ahead of the rest.
 __global__ void __launch_bounds__(384, 1) chol_syrk_kernel(const __grid_constant__ CUtensorMap tmL, BatchPtrs bp,
-                                                           int kcol, int kw, int jlo, int jhi, int nb, int npad) {
+                                                           int kcol, int kw, int jlo, int jhi, int nb, int npad,
+                                                           int t0) {
   extern __shared__ unsigned char smem_raw[];
   const int b = blockIdx.y;
-  int j = jlo, t = blockIdx.x;
+  int j = jlo, t = blockIdx.x + t0;
   while (j < jhi && t >= nb - j) { t -= nb - j; ++j; }
   if (j >= jhi) return;
   const int i = j + t;
