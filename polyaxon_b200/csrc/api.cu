@@ -3,8 +3,10 @@
 #include "../../include/plxbo.h"
 #include "refine.cuh"
 #include "append.cuh"
+#include "sweep_i8.cuh"
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -55,6 +57,14 @@ struct plx_bo {
   double* dKs = nullptr; size_t ks_cap = 0;
   double* dXt = nullptr; size_t xt_cap = 0;
   CUtensorMap tmZ, tmK;
+  // int8-sliced variant of the sweep (sweep_impl 2, sweep_i8.cuh)
+  signed char* d_kplanes = nullptr; size_t kplanes_cap = 0;     // [I8_S][i8_rows][npad]
+  signed char* d_zplanes = nullptr; size_t zplanes_cap = 0;     // [I8_S][npad][npad]
+  double* d_zscale = nullptr; size_t zscale_cap = 0;
+  double* d_i8mean = nullptr; size_t i8mean_cap = 0;
+  CUtensorMap tmA8, tmB8;
+  long long i8_rows = 0; int i8_npad = 0;
+  bool i8_state_valid = false;
 
   // sweep buffers
   double* d_blk_val = nullptr; long long* d_blk_idx = nullptr;
@@ -190,6 +200,10 @@ extern "C" int plx_bo_create(int device, plx_bo_handle* out) {
       qres != cudaDriverEntryPointSuccess)
     return bail("cuTensorMapEncodeTiled not available from the driver");
   h->encode = reinterpret_cast<EncodeTiledFn>(fn);
+  if (const char* e = std::getenv("PLX_BO_SWEEP_IMPL")) {       // A/B switch for measurements; see plx_bo_set_option
+    const int v = std::atoi(e);
+    if (v >= 0 && v <= 2) h->sweep_impl = v;
+  }
   // opt in to large dynamic shared memory once
   cudaFuncSetAttribute(potf2_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, POTF_SMEM);
   cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FIT_SMEM);
@@ -199,6 +213,8 @@ extern "C" int plx_bo_create(int device, plx_bo_handle* out) {
   cudaFuncSetAttribute(kinv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FIT_SMEM);
   cudaFuncSetAttribute(sweep_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SWEEP_SMEM);
   cudaFuncSetAttribute(sweep_simple_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SWEEP_SIMPLE_SMEM);
+  cudaFuncSetAttribute(sweep_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, I8_SMEM);
+  cudaFuncSetAttribute(kstar_slices_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, KSL_SMEM);
   if (cudaGetLastError() != cudaSuccess) return bail("cudaFuncSetAttribute failed (is the library built for this GPU?)");
   if (cudaMalloc(&h->d_blk_val, sizeof(double) * 1024) != cudaSuccess ||
       cudaMalloc(&h->d_blk_idx, sizeof(long long) * 1024) != cudaSuccess ||
@@ -217,7 +233,8 @@ extern "C" void plx_bo_destroy(plx_bo_handle h) {
                   h->d_alpha, h->d_partial, h->d_lml, h->d_grad, h->d_xs, h->d_info, h->dZ, h->d_alpha_state, h->dKs, h->dXt,
                   h->d_blk_val, h->d_blk_idx, h->d_best_val, h->d_best_idx, h->dcand[0], h->dcand[1],
                   h->d_out[0], h->d_out[1], h->d_out[2], h->rf_kv, h->rf_kp, h->rf_v, h->rf_w, h->rf_vec,
-                  h->rf_bounds, h->rf_val, h->rf_grad, h->rf_sc, h->rf_active, h->d_resident, h->d_misc, h->d_app};
+                  h->rf_bounds, h->rf_val, h->rf_grad, h->rf_sc, h->rf_active, h->d_resident, h->d_misc, h->d_app,
+                  h->d_kplanes, h->d_zplanes, h->d_zscale, h->d_i8mean};
   for (void* p : ptrs) if (p) cudaFree(p);
   for (int i = 0; i < 2; ++i) { if (h->ev_copy[i]) cudaEventDestroy(h->ev_copy[i]); if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]); }
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
@@ -235,7 +252,7 @@ extern "C" int plx_bo_set_stream(plx_bo_handle h, void* stream) {
 
 extern "C" int plx_bo_set_option(plx_bo_handle h, const char* name, long long value) {
   if (!h || !name) return PLX_ERR_INVALID;
-  if (std::strcmp(name, "sweep_impl") == 0 && (value == 0 || value == 1)) { h->sweep_impl = static_cast<int>(value); return PLX_OK; }
+  if (std::strcmp(name, "sweep_impl") == 0 && value >= 0 && value <= 2) { h->sweep_impl = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "lml_batch_limit") == 0 && value >= 0) { h->lml_batch_limit = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "sweep_dbg") == 0) { h->sweep_dbg = static_cast<int>(value); return PLX_OK; }
   return fail(h, PLX_ERR_INVALID, std::string("unknown option or value: ") + name);
@@ -471,7 +488,7 @@ extern "C" int plx_gp_set_theta(plx_bo_handle h, double theta) {
   CK(cudaStreamSynchronize(h->stream));
   if ((r = make_map(h, &h->tmZ, h->dZ, h->npad, h->npad)) != PLX_OK) return r;
   if ((r = make_map(h, &h->tmK, h->dKs, static_cast<size_t>(h->num_sms) * 128, h->npad)) != PLX_OK) return r;
-  h->theta = theta; h->have_state = true; h->state_factor_valid = true;
+  h->theta = theta; h->have_state = true; h->state_factor_valid = true; h->i8_state_valid = false;
   return PLX_OK;
 }
 
@@ -559,7 +576,7 @@ extern "C" int plx_gp_append(plx_bo_handle h, const double* x_new, double y_new)
   scale_transpose_x_kernel<<<dim3((npad + 255) / 256, d), 256, 0, st>>>(h->dX, n1, d, npad, ell, h->dXt);
   LAUNCH_CHECK("scale_transpose_x_kernel");
   CK(cudaStreamSynchronize(st));          // y_new / lam2 live on this frame
-  h->n = n1;
+  h->n = n1; h->i8_state_valid = false;
   { const int nt32 = (n1 + 31) / 32; h->ntri = nt32 * (nt32 + 1) / 2; }
   return PLX_OK;
 }
@@ -610,15 +627,77 @@ static void fill_params(plx_bo* h, SweepParams& p, const double* Xc_dev, long lo
   p.X = h->dX; p.Xt = h->dXt; p.alpha = h->d_alpha_state; p.Z = h->dZ; p.ell = std::exp(h->theta);
   p.kind = h->kind; p.mg = h->mg; p.acq = acq; p.kappa = kappa; p.eps = eps; p.y_max = y_max;
   p.Ks = h->dKs; p.out_mean = p.out_std = p.out_acq = nullptr;
+  p.planes = nullptr; p.plane_stride = 0;
   p.blk_val = h->d_blk_val; p.blk_idx = h->d_blk_idx; p.dbg = h->sweep_dbg;
+}
+
+// 3-D map over digit planes: `cols` bytes per row, `rows` rows per plane, I8_S planes; box = 64 bytes x box_rows x all planes
+static int make_map_i8(plx_bo* h, CUtensorMap* map, signed char* base, size_t cols, size_t rows, int box_rows) {
+  cuuint64_t dims[3] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows), static_cast<cuuint64_t>(I8_S)};
+  cuuint64_t strides[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(cols) * rows};
+  cuuint32_t box[3] = {I8_KC, static_cast<cuuint32_t>(box_rows), I8_S};
+  cuuint32_t estr[3] = {1, 1, 1};
+  const CUresult r = h->encode(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box, estr,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B,
+                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(h, PLX_ERR_CUDA, "cuTensorMapEncodeTiled (int8 planes) failed with code " + std::to_string(r));
+  return PLX_OK;
+}
+
+// Variant 2 (sweep_i8.cuh): chunks of candidates; per chunk the digit planes of K*, then the sliced contraction.
+static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cudaEvent_t e1) {
+  cudaStream_t st = h->stream;
+  const long long rows = static_cast<long long>(h->num_sms) * 128 * 2;
+  const size_t npad = h->npad;
+  int r;
+  if (h->i8_rows != rows || h->i8_npad != h->npad || !h->d_kplanes) {
+    if ((r = ensure(h, h->d_kplanes, h->kplanes_cap, static_cast<size_t>(I8_S) * rows * npad)) != PLX_OK) return r;
+    if ((r = ensure(h, h->d_zplanes, h->zplanes_cap, static_cast<size_t>(I8_S) * npad * npad)) != PLX_OK) return r;
+    if ((r = ensure(h, h->d_zscale, h->zscale_cap, npad)) != PLX_OK) return r;
+    if ((r = ensure(h, h->d_i8mean, h->i8mean_cap, static_cast<size_t>(rows))) != PLX_OK) return r;
+    if ((r = make_map_i8(h, &h->tmA8, h->d_kplanes, npad, rows, 128)) != PLX_OK) return r;
+    if ((r = make_map_i8(h, &h->tmB8, h->d_zplanes, npad, npad, 64)) != PLX_OK) return r;
+    h->i8_rows = rows; h->i8_npad = h->npad; h->i8_state_valid = false;
+  }
+  if (!h->i8_state_valid) {
+    // columns of the K* planes beyond the observations are never written by the slicing kernel: keep them zero
+    CK(cudaMemsetAsync(h->d_kplanes, 0, static_cast<size_t>(I8_S) * rows * npad, st));
+    zslice_kernel<<<h->npad, 128, 0, st>>>(h->dZ, h->npad, h->n, reinterpret_cast<int8_t*>(h->d_zplanes), h->d_zscale);
+    LAUNCH_CHECK("zslice_kernel");
+    h->i8_state_valid = true;
+  }
+  if (e0) CK(cudaEventRecord(e0, st));
+  for (long long base = 0; base < p.N; base += rows) {
+    const long long cnt = std::min(rows, p.N - base);
+    const int grid = static_cast<int>(std::min<long long>((cnt + 127) / 128, h->num_sms));
+    SweepParams q = p;
+    q.Xc = p.Xc + base * p.d; q.N = cnt; q.dbg = 0;
+    q.planes = h->d_kplanes; q.plane_stride = static_cast<size_t>(rows) * npad;
+    kstar_slices_kernel<<<grid, 256, KSL_SMEM, st>>>(q, h->d_i8mean);
+    LAUNCH_CHECK("kstar_slices_kernel");
+    I8Params ip;
+    ip.N = cnt; ip.idx_base = p.idx_base + base; ip.n = p.n; ip.zscale = h->d_zscale; ip.mean = h->d_i8mean;
+    ip.acq = p.acq; ip.kappa = p.kappa; ip.eps = p.eps; ip.y_max = p.y_max;
+    ip.out_mean = p.out_mean ? p.out_mean + base : nullptr;
+    ip.out_std = p.out_std ? p.out_std + base : nullptr;
+    ip.out_acq = p.out_acq ? p.out_acq + base : nullptr;
+    ip.blk_val = h->d_blk_val; ip.blk_idx = h->d_blk_idx;
+    sweep_i8_kernel<<<grid, 192, I8_SMEM, st>>>(h->tmA8, h->tmB8, ip);
+    LAUNCH_CHECK("sweep_i8_kernel");
+    sweep_merge_kernel<<<1, 32, 0, st>>>(h->d_blk_val, h->d_blk_idx, grid, h->d_best_val, h->d_best_idx);
+    LAUNCH_CHECK("sweep_merge_kernel");
+  }
+  if (e1) CK(cudaEventRecord(e1, st));
+  return PLX_OK;
 }
 
 static int launch_sweep(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cudaEvent_t e1) {
   const long long ntiles = (p.N + 127) / 128;
   const int grid = static_cast<int>(std::min<long long>(ntiles, h->num_sms));
   if (grid <= 0) return PLX_OK;
+  if (h->sweep_impl == 2 && p.kind != K_GEN) return launch_sweep_i8(h, p, e0, e1);
   if (e0) CK(cudaEventRecord(e0, h->stream));
-  if (h->sweep_impl == 1) {
+  if (h->sweep_impl >= 1) {
     sweep_tma_kernel<<<grid, 384, SWEEP_SMEM, h->stream>>>(h->tmZ, h->tmK, p);
     LAUNCH_CHECK("sweep_tma_kernel");
   } else {

@@ -37,6 +37,8 @@ struct SweepParams {
   MaternGen mg;            // constants of the general-nu Matern kernel (kind == K_GEN)
   double kappa, eps, y_max;
   double* Ks;              // scratch [gridDim.x * 128][npad]
+  signed char* planes;     // variant 2: digit planes of K*, [I8_S][plane_rows][npad] int8 (see sweep_i8.cuh)
+  size_t plane_stride;     //            bytes between planes
   double* out_mean; double* out_std; double* out_acq;   // optional per-candidate dumps [N]
   double* blk_val; long long* blk_idx;                  // per-CTA best
   int dbg;                 // profiling only: bit 0 = build K* for the first tile only, bit 1 = skip the DMMA work
@@ -226,7 +228,21 @@ constexpr int PA_CS = 0, PA_XS = 32 * CS_LD, PA_R2 = PA_XS + 32 * XS_LD, PA_MACC
 constexpr int PA_DOUBLES = PA_MACC + 128 * 32;
 static_assert(PA_DOUBLES * 8 <= 5 * 2 * TILE_BYTES, "phase A staging must fit in the pipeline stages");
 
-template <int KIND>
+// Signed 7-bit digits of x = k / 2 (k in [0, 1]): k = 2 * sum_s a_s 2^(-7(s+1)) + O(2^-57); every step is exact.
+__device__ __forceinline__ void store_digits(signed char* dst, size_t plane_stride, double k) {
+  double x = 0.5 * k;
+#pragma unroll
+  for (int s = 0; s < 8; ++s) {
+    x *= 128.0;
+    const double a = rint(x);
+    dst[s * plane_stride] = static_cast<signed char>(static_cast<int>(a));
+    x -= a;
+  }
+}
+
+// SL = false: FP64 kernel values into the K* slab; SL = true: their digit planes (Kslab then points at the
+// tile's first row of plane 0, reinterpreted).
+template <int KIND, bool SL>
 __device__ __forceinline__ void kern_rows(const SweepParams& p, uint32_t sm, double* Kslab, int jb, int warp, int lane) {
   const int j0 = jb * 64 + lane, j1 = j0 + 32;
   const bool real0 = j0 < p.n, real1 = j1 < p.n;
@@ -240,9 +256,15 @@ __device__ __forceinline__ void kern_rows(const SweepParams& p, uint32_t sm, dou
       double k1 = kern_value_t<KIND>(lds64(r2a + 32 * 8), p.mg);
       k0 = real0 ? k0 : 0.0;
       k1 = real1 ? k1 : 0.0;
-      double* row = Kslab + static_cast<size_t>(c) * p.npad;
-      if (st0) row[j0] = k0;
-      if (st1) row[j1] = k1;
+      if constexpr (SL) {
+        signed char* row = reinterpret_cast<signed char*>(Kslab) + static_cast<size_t>(c) * p.npad;
+        if (st0) store_digits(row + j0, p.plane_stride, k0);
+        if (st1) store_digits(row + j1, p.plane_stride, k1);
+      } else {
+        double* row = Kslab + static_cast<size_t>(c) * p.npad;
+        if (st0) row[j0] = k0;
+        if (st1) row[j1] = k1;
+      }
       const uint32_t ma = sm + static_cast<uint32_t>((PA_MACC + c * 32 + lane) * 8);
       sts64(ma, lds64(ma) + (k0 * a0 + k1 * a1));
     }
@@ -262,9 +284,15 @@ __device__ __forceinline__ void kern_rows(const SweepParams& p, uint32_t sm, dou
     for (int u = 0; u < 4; ++u) {
       const int c = warp * 16 + ci + u;
       const double k0 = real0 ? v[2 * u] : 0.0, k1 = real1 ? v[2 * u + 1] : 0.0;
-      double* row = Kslab + static_cast<size_t>(c) * p.npad;
-      if (st0) row[j0] = k0;
-      if (st1) row[j1] = k1;
+      if constexpr (SL) {
+        signed char* row = reinterpret_cast<signed char*>(Kslab) + static_cast<size_t>(c) * p.npad;
+        if (st0) store_digits(row + j0, p.plane_stride, k0);
+        if (st1) store_digits(row + j1, p.plane_stride, k1);
+      } else {
+        double* row = Kslab + static_cast<size_t>(c) * p.npad;
+        if (st0) row[j0] = k0;
+        if (st1) row[j1] = k1;
+      }
       const uint32_t ma = sm + static_cast<uint32_t>((PA_MACC + c * 32 + lane) * 8);
       sts64(ma, lds64(ma) + (k0 * a0 + k1 * a1));
     }
@@ -272,6 +300,7 @@ __device__ __forceinline__ void kern_rows(const SweepParams& p, uint32_t sm, dou
   }
 }
 
+template <bool SL>
 __device__ __forceinline__ void phase_a3(const SweepParams& p, long long tile, double* Kslab, uint32_t sm,
                                          double* mean_s, int tid) {
   const int tx = tid & 15, ty = tid >> 4, warp = tid >> 5, lane = tid & 31;
@@ -343,11 +372,11 @@ __device__ __forceinline__ void phase_a3(const SweepParams& p, long long tile, d
         sts64(sm + static_cast<uint32_t>((PA_R2 + (ty * 8 + i) * R2_LD + tx + 16 * j) * 8), r2[i][j]);
     named_bar_sync(1, 256);
     if (!(p.dbg & 4)) switch (p.kind) {
-      case K_RBF: kern_rows<K_RBF>(p, sm, Kslab, jb, warp, lane); break;
-      case K_M05: kern_rows<K_M05>(p, sm, Kslab, jb, warp, lane); break;
-      case K_M15: kern_rows<K_M15>(p, sm, Kslab, jb, warp, lane); break;
-      case K_GEN: kern_rows<K_GEN>(p, sm, Kslab, jb, warp, lane); break;
-      default: kern_rows<K_M25>(p, sm, Kslab, jb, warp, lane); break;
+      case K_RBF: kern_rows<K_RBF, SL>(p, sm, Kslab, jb, warp, lane); break;
+      case K_M05: kern_rows<K_M05, SL>(p, sm, Kslab, jb, warp, lane); break;
+      case K_M15: kern_rows<K_M15, SL>(p, sm, Kslab, jb, warp, lane); break;
+      case K_GEN: kern_rows<K_GEN, SL>(p, sm, Kslab, jb, warp, lane); break;
+      default: kern_rows<K_M25, SL>(p, sm, Kslab, jb, warp, lane); break;
     }
     // no barrier here: the next block re-writes Xs (free since the barrier above) and parks into R2s only
     // after its own barrier, which every thread reaches after finishing this kern_rows
@@ -429,7 +458,7 @@ __global__ void __launch_bounds__(384, 1) sweep_tma_kernel(const __grid_constant
   const int wn = (warp >> 2) * 64;
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     // every TMA load of the previous tile has been waited for, so the stage memory is free
-    if (!(p.dbg & 1) || tile == blockIdx.x) phase_a3(p, tile, Kslab, s0, tail->mean_s, tid);
+    if (!(p.dbg & 1) || tile == blockIdx.x) phase_a3<false>(p, tile, Kslab, s0, tail->mean_s, tid);
     __threadfence();
     asm volatile("fence.proxy.async;\n" ::: "memory");     // generic-proxy stores -> visible to TMA
     __syncwarp();

@@ -1,0 +1,258 @@
+// Variant 2 of the acquisition sweep (opt-in, "sweep_impl" = 2): the variance contraction V = K* . Z^T on the
+// int8 tensor cores by exact slicing, instead of FP64 DMMA.
+//
+//   K*[c][j] = 2 * sum_s a_s[c][j] 2^(-7(s+1))                  a_s signed 7-bit digits (K* in [0, 1], fixed exponent)
+//   Z[i][j]  = 2^f_i * sum_t b_t[i][j] 2^(-7(t+1))              f_i from the largest entry of row i of L^-1
+//   V[c][i]  = 2^(f_i+1) * sum_{s+t<S} 2^(-7(s+t+2)) (a_s[c] . b_t[i])
+//
+// Every dot product a_s . b_t is an exact int32 (tcgen05.mma kind::i8, accumulators in TMEM); the S scale
+// classes s + t = 0 .. S-1 are kept in S separate accumulators and recombined in FP64, smallest first.  With
+// S = 8 the result is at least as accurate as an FP64 FMA chain (tools/ozaki_probe.cu: 3.5e-16 relative to
+// sum |K* Z| at n = 2048).  Reference arithmetic being reproduced: sklearn _gpr.py:460-481.
+//
+// Two kernels per chunk of candidates:
+//   kstar_slices_kernel  phase A of variant 1 (same distances, same kernel values, same posterior mean) writing
+//                        the S digit planes of K* (int8) instead of the FP64 tile;
+//   sweep_i8_kernel      persistent, 192 threads: warp 4 streams the digit planes of a 128-candidate tile and of a
+//                        64-row half-block of Z through a two-stage ring (one 3-D bulk tensor load per operand and
+//                        64-observation chunk, 64-byte swizzle), warp 5 issues the 72 tensor instructions per stage
+//                        (36 slice pairs x 2 k-steps) into 8 x 64 TMEM columns, warps 0-3 drain the accumulators of a
+//                        finished half-block (tcgen05.ld), recombine in FP64, scale, square and sum per candidate, and
+//                        finish with variance -> acquisition -> arg-max exactly as variant 1.
+#pragma once
+#include "sweep.cuh"
+
+namespace plx {
+
+constexpr int I8_S = 8;                               // digit planes per operand
+constexpr int I8_KC = 64;                             // observations (= bytes) per K chunk
+constexpr int I8_A_SLICE = 128 * I8_KC;               // one plane of the candidate tile chunk
+constexpr int I8_B_SLICE = 64 * I8_KC;                // one plane of the Z half-block chunk
+constexpr int I8_A_BYTES = I8_S * I8_A_SLICE;         // 64 KiB
+constexpr int I8_B_BYTES = I8_S * I8_B_SLICE;         // 32 KiB
+constexpr int I8_STAGE = I8_A_BYTES + I8_B_BYTES;
+constexpr int I8_STAGES = 2;
+constexpr int I8_SMEM = I8_STAGES * I8_STAGE + 1024 /*align*/ + 3072 /*tail*/;
+
+struct I8Params {
+  long long N;                 // candidates of this launch (one chunk)
+  long long idx_base;          // global index of candidate 0 of this launch
+  int n;                       // observations
+  const double* zscale;        // [npad]: 2^(f_i + 1), zero for rows >= n
+  const double* mean;          // [N] posterior means written by kstar_slices_kernel
+  int acq;
+  double kappa, eps, y_max;
+  double* out_mean; double* out_std; double* out_acq;       // optional dumps, indexed like the candidates of this launch
+  double* blk_val; long long* blk_idx;
+};
+
+// K-major operand rows of 64 bytes, 64-byte swizzle, 8-row groups 512 bytes apart
+__device__ __forceinline__ uint64_t umma_desc_sw64(uint32_t saddr) {
+  return static_cast<uint64_t>((saddr & 0x3FFFF) >> 4) | (1ull << 16) | (32ull << 32) | (1ull << 46) | (4ull << 61);
+}
+// kind::i8: D = s32, A = B = signed 8 bit, both K-major, M = 128, N = 64
+constexpr uint32_t I8_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((64u >> 3) << 17) | ((128u >> 4) << 24);
+
+__device__ __forceinline__ void umma_i8(uint32_t tmem_c, uint64_t da, uint64_t db, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}\n"
+      :: "r"(tmem_c), "l"(da), "l"(db), "r"(I8_IDESC), "r"(accumulate), "r"(0u) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" :: "r"(bar) : "memory");
+}
+
+struct I8Tail {
+  unsigned long long bars[2 * I8_STAGES + 2];       // full[ST], empty[ST], accumulators full, accumulators empty
+  uint32_t tmem_base;
+  double sval[128];
+  long long sidx[128];
+};
+static_assert(sizeof(I8Tail) <= 3072, "tail budget");
+
+__global__ void __launch_bounds__(192, 1) sweep_i8_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                          const __grid_constant__ CUtensorMap tmB, const I8Params p) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = align1k(smem_raw);
+  I8Tail* tail = reinterpret_cast<I8Tail*>(smem + I8_STAGES * I8_STAGE);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t s0 = smem_u32(smem);
+  const uint32_t bar0 = smem_u32(tail->bars);
+  const uint32_t bar_accf = bar0 + 8 * (2 * I8_STAGES), bar_acce = bar_accf + 8;
+  if (tid == 0) {
+    for (int s = 0; s < I8_STAGES; ++s) { mbar_init(bar0 + 8 * s, 1); mbar_init(bar0 + 8 * (I8_STAGES + s), 1); }
+    mbar_init(bar_accf, 1);
+    mbar_init(bar_acce, 128);
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" :: "r"(smem_u32(&tail->tmem_base)), "n"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;\n");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;\n");
+  const uint32_t tmem = tail->tmem_base;
+
+  const long long ntiles = (p.N + 127) / 128;
+  const int nh = (p.n + 63) / 64;                    // half-blocks of 64 rows of Z that hold observations
+
+  if (warp == 4) {
+    // ===== producer =====
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
+        for (int h = 0; h < nh; ++h)
+          for (int kc = 0; kc <= h; ++kc, ++it) {
+            const uint32_t s = it % I8_STAGES, ph = (it / I8_STAGES) & 1;
+            mbar_wait(bar0 + 8 * (I8_STAGES + s), ph ^ 1);
+            const uint32_t full = bar0 + 8 * s;
+            mbar_expect_tx(full, I8_STAGE);
+            tma_load_3d(s0 + s * I8_STAGE, &tmA, kc * I8_KC, static_cast<int>(tile * 128), 0, full);
+            tma_load_3d(s0 + s * I8_STAGE + I8_A_BYTES, &tmB, kc * I8_KC, h * 64, 0, full);
+          }
+    }
+  } else if (warp == 5) {
+    // ===== tensor-instruction issuer =====
+    if (lane == 0) {
+      uint32_t it = 0, acc_round = 0;
+      for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
+        for (int h = 0; h < nh; ++h, ++acc_round) {
+          mbar_wait(bar_acce, (acc_round & 1) ^ 1);        // the previous half-block has been drained
+          asm volatile("tcgen05.fence::after_thread_sync;\n");
+          uint32_t started = 0;                            // scale classes whose accumulator holds data
+          for (int kc = 0; kc <= h; ++kc, ++it) {
+            const uint32_t s = it % I8_STAGES, ph = (it / I8_STAGES) & 1;
+            mbar_wait(bar0 + 8 * s, ph);
+            asm volatile("tcgen05.fence::after_thread_sync;\n");
+            const uint32_t a0 = s0 + s * I8_STAGE, b0 = a0 + I8_A_BYTES;
+#pragma unroll 1
+            for (int t = 0; t < I8_S; ++t) {
+              const uint64_t db = umma_desc_sw64(b0 + t * I8_B_SLICE);
+#pragma unroll 1
+              for (int sl = 0; sl + t < I8_S; ++sl) {
+                const uint64_t da = umma_desc_sw64(a0 + sl * I8_A_SLICE);
+                const int cls = sl + t;
+                umma_i8(tmem + cls * 64, da, db, (started >> cls) & 1u);
+                umma_i8(tmem + cls * 64, da + 2, db + 2, 1u);
+                started |= 1u << cls;
+              }
+            }
+            umma_commit(bar0 + 8 * (I8_STAGES + s));       // stage free once these instructions have read it
+          }
+          umma_commit(bar_accf);                           // accumulators of this half-block complete
+        }
+    }
+  } else if (warp < 4) {
+    // ===== accumulator drain + epilogue: thread = candidate row of the tile = TMEM lane =====
+    Best best = {-INFINITY, 0x7fffffffffffffffLL};
+    uint32_t acc_round = 0;
+    const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      double sumsq = 0.0;
+      for (int h = 0; h < nh; ++h, ++acc_round) {
+        mbar_wait(bar_accf, acc_round & 1);
+        asm volatile("tcgen05.fence::after_thread_sync;\n");
+#pragma unroll 1
+        for (int c0 = 0; c0 < 64; c0 += 16) {
+          double v[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] = 0.0;
+#pragma unroll
+          for (int cls = I8_S - 1; cls >= 0; --cls) {      // smallest contributions first
+            uint32_t u[16];
+            asm volatile(
+                "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];\n"
+                : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]),
+                  "=r"(u[8]), "=r"(u[9]), "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15])
+                : "r"(tmem + lane_base + cls * 64 + c0));
+            asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+            const double w = __longlong_as_double(static_cast<long long>(1023 - 7 * (cls + 2)) << 52);   // 2^(-7(cls+2))
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = fma(static_cast<double>(static_cast<int>(u[i])), w, v[i]);
+          }
+          const double* zs = p.zscale + h * 64 + c0;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) { const double x = v[i] * zs[i]; sumsq = fma(x, x, sumsq); }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;\n");
+        mbar_arrive(bar_acce);
+      }
+      const long long ci = tile * 128 + tid;
+      if (ci < p.N) {
+        double var = 1.0 - sumsq;
+        if (var < 0.0) var = 0.0;                 // sklearn clamps negative variances to zero
+        const double sd = sqrt(var), mean = p.mean[ci];
+        const double a = acq_value(p.acq, mean, sd, p.y_max, p.kappa, p.eps);
+        if (p.out_mean) p.out_mean[ci] = mean;
+        if (p.out_std) p.out_std[ci] = sd;
+        if (p.out_acq) p.out_acq[ci] = a;
+        const long long gi = p.idx_base + ci;
+        if (better(a, gi, best.v, best.i)) { best.v = a; best.i = gi; }
+      }
+    }
+    tail->sval[tid] = best.v; tail->sidx[tid] = best.i;
+    named_bar_sync(1, 128);
+    if (tid == 0) {
+      Best b = {tail->sval[0], tail->sidx[0]};
+      for (int t = 1; t < 128; ++t)
+        if (better(tail->sval[t], tail->sidx[t], b.v, b.i)) { b.v = tail->sval[t]; b.i = tail->sidx[t]; }
+      p.blk_val[blockIdx.x] = b.v;
+      p.blk_idx[blockIdx.x] = b.i;
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;\n");
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" :: "r"(tmem), "n"(512));
+}
+
+// Phase A for a chunk of candidates: digit planes of K* (rows = candidates of the chunk) and posterior means.
+constexpr int KSL_SMEM = PA_DOUBLES * 8 + 1024 + 1024;
+
+__global__ void __launch_bounds__(256, 1) kstar_slices_kernel(const SweepParams p, double* __restrict__ mean_out) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = align1k(smem_raw);
+  double* mean_s = reinterpret_cast<double*>(smem + PA_DOUBLES * 8);
+  const uint32_t s0 = smem_u32(smem);
+  const int tid = threadIdx.x;
+  const long long ntiles = (p.N + 127) / 128;
+  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    signed char* rows = p.planes + static_cast<size_t>(tile) * 128 * p.npad;
+    phase_a3<true>(p, tile, reinterpret_cast<double*>(rows), s0, mean_s, tid);
+    if (tid < 128 && tile * 128 + tid < p.N) mean_out[tile * 128 + tid] = mean_s[tid];
+    __syncthreads();                      // the staging area is reused by the next tile
+  }
+}
+
+// Digit planes and row scales of Z = L^-1 (lower triangular, npad x npad).  One CTA per row.
+// planes[s][i][j]; zscale[i] = 2^(f_i + 1) for i < n, else 0 (the extra factor 2 is K*'s fixed exponent).
+__global__ void __launch_bounds__(128) zslice_kernel(const double* __restrict__ Z, int npad, int n,
+                                                     int8_t* __restrict__ planes, double* __restrict__ zscale) {
+  __shared__ double red[128];
+  const int i = blockIdx.x, tid = threadIdx.x;
+  const double* row = Z + static_cast<size_t>(i) * npad;
+  double m = 0.0;
+  if (i < n)
+    for (int j = tid; j <= i; j += 128) m = fmax(m, fabs(row[j]));
+  red[tid] = m;
+  __syncthreads();
+  for (int o = 64; o > 0; o >>= 1) { if (tid < o) red[tid] = fmax(red[tid], red[tid + o]); __syncthreads(); }
+  m = red[0];
+  int e = 0;
+  if (m > 0.0) { frexp(m, &e); e += 1; }          // m * 2^-e in [1/4, 1/2)
+  if (tid == 0) zscale[i] = (i < n && m > 0.0) ? ldexp(1.0, e + 1) : 0.0;
+  const size_t pstride = static_cast<size_t>(npad) * npad;
+  for (int j = tid; j < npad; j += 128) {
+    double x = (i < n && j <= i) ? ldexp(row[j], -e) : 0.0;
+#pragma unroll
+    for (int s = 0; s < I8_S; ++s) {
+      x *= 128.0;
+      const double a = rint(x);
+      planes[s * pstride + static_cast<size_t>(i) * npad + j] = static_cast<int8_t>(static_cast<int>(a));
+      x -= a;
+    }
+  }
+}
+
+}  // namespace plx
