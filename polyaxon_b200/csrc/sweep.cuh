@@ -228,16 +228,18 @@ constexpr int PA_CS = 0, PA_XS = 32 * CS_LD, PA_R2 = PA_XS + 32 * XS_LD, PA_MACC
 constexpr int PA_DOUBLES = PA_MACC + 128 * 32;
 static_assert(PA_DOUBLES * 8 <= 5 * 2 * TILE_BYTES, "phase A staging must fit in the pipeline stages");
 
-// Signed 7-bit digits of x = k / 2 (k in [0, 1]): k = 2 * sum_s a_s 2^(-7(s+1)) + O(2^-57); every step is exact.
+// Signed 7-bit digits of k / 2 (k in [0, 1]): k = 2 * sum_s a_s 2^(-7(s+1)) with the digits of the balanced base-128
+// expansion of round(k * 2^55), extracted with integer arithmetic from the low end (exact; |residual| <= 2^-56).
 __device__ __forceinline__ void store_digits(signed char* dst, size_t plane_stride, double k) {
-  double x = 0.5 * k;
+  long long q = __double2ll_rn(k * 36028797018963968.0);          // k * 2^55 = (k / 2) * 2^56
 #pragma unroll
-  for (int s = 0; s < 8; ++s) {
-    x *= 128.0;
-    const double a = rint(x);
-    dst[s * plane_stride] = static_cast<signed char>(static_cast<int>(a));
-    x -= a;
+  for (int s = 7; s >= 1; --s) {
+    int dgt = static_cast<int>(q & 127);
+    dgt -= (dgt >= 64) ? 128 : 0;
+    dst[s * plane_stride] = static_cast<signed char>(dgt);
+    q = (q - dgt) >> 7;
   }
+  dst[0] = static_cast<signed char>(q);                            // leading digit, 0 .. 65 (k = 1 gives 64)
 }
 
 // SL = false: FP64 kernel values into the K* slab; SL = true: their digit planes (Kslab then points at the

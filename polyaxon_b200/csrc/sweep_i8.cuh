@@ -121,22 +121,23 @@ __global__ void __launch_bounds__(192, 1) sweep_i8_kernel(const __grid_constant_
         for (int h = 0; h < nh; ++h, ++acc_round) {
           mbar_wait(bar_acce, (acc_round & 1) ^ 1);        // the previous half-block has been drained
           asm volatile("tcgen05.fence::after_thread_sync;\n");
-          uint32_t started = 0;                            // scale classes whose accumulator holds data
           for (int kc = 0; kc <= h; ++kc, ++it) {
             const uint32_t s = it % I8_STAGES, ph = (it / I8_STAGES) & 1;
             mbar_wait(bar0 + 8 * s, ph);
             asm volatile("tcgen05.fence::after_thread_sync;\n");
-            const uint32_t a0 = s0 + s * I8_STAGE, b0 = a0 + I8_A_BYTES;
-#pragma unroll 1
+            const uint32_t a0 = s0 + s * I8_STAGE;
+            // descriptors differ only in the 16-byte-unit address field: + slice * size / 16, + 2 for the second k-step
+            const uint64_t da0 = umma_desc_sw64(a0), db0 = umma_desc_sw64(a0 + I8_A_BYTES);
+            const uint32_t fresh = (kc != 0);                // the first chunk of a half-block overwrites the accumulators
+#pragma unroll
             for (int t = 0; t < I8_S; ++t) {
-              const uint64_t db = umma_desc_sw64(b0 + t * I8_B_SLICE);
-#pragma unroll 1
+#pragma unroll
               for (int sl = 0; sl + t < I8_S; ++sl) {
-                const uint64_t da = umma_desc_sw64(a0 + sl * I8_A_SLICE);
-                const int cls = sl + t;
-                umma_i8(tmem + cls * 64, da, db, (started >> cls) & 1u);
-                umma_i8(tmem + cls * 64, da + 2, db + 2, 1u);
-                started |= 1u << cls;
+                const uint64_t da = da0 + static_cast<uint64_t>(sl * (I8_A_SLICE / 16));
+                const uint64_t db = db0 + static_cast<uint64_t>(t * (I8_B_SLICE / 16));
+                // class sl + t is first touched by the pair (sl, 0)
+                umma_i8(tmem + (sl + t) * 64, da, db, t == 0 ? fresh : 1u);
+                umma_i8(tmem + (sl + t) * 64, da + 2, db + 2, 1u);
               }
             }
             umma_commit(bar0 + 8 * (I8_STAGES + s));       // stage free once these instructions have read it
