@@ -10,9 +10,11 @@ one all-gather (strong scaling: the global candidate count is fixed).
   value   whole-job candidates/s with candidates resident in HBM (device-timed, max over ranks)
   e2e     the same through the C-ABI call with HOST (pinned) candidate buffers: host->device copies and
           the device->host read of the result are inside the timed region
-  roofline  FP64 tensor (DMMA) bound; achieved = algorithmic flops per candidate x candidates / duration of
-          the sweep kernel (CUDA events on its own stream); peak = cuBLAS DGEMM 8192^3 measured in this
-          run (MEASURED_PEAKS.json has no FP64 entry)
+  roofline  tensor bound; achieved = algorithmic FP64 flops per candidate x candidates / duration of the sweep
+          kernels (CUDA events on their own stream); peak = cuBLAS DGEMM 8192^3 measured in this run
+          (MEASURED_PEAKS.json has no FP64 entry).  On the default path the variance contraction runs as exact
+          int8 slices on the tcgen05 tensor cores, so the fraction of the FP64 rate can exceed 1; the `int8`
+          sub-object gives the executed int8 tensor ops against the instruction's measured issue rate
   cpu_baseline  the reference's sklearn/scipy path (oracle/reference_path.py) on the host cores, on a
           bounded sample of the same workload
 
@@ -34,8 +36,10 @@ sys.path.insert(0, ROOT)
 D, N_OBS, NU = 32, 2048, 1.5
 THETA = 1.2                      # log length-scale of the benchmark state (near the fitted optimum)
 METRIC = 'acquisition evals/sec (FP64) at d=32,n_obs=2048'
-# dram__bytes_read.sum + dram__bytes_write.sum of sweep_tma_kernel per candidate (profiles/r01_ncu_sweep_tma_v3_summary.csv)
+# dram__bytes_read.sum + dram__bytes_write.sum per candidate: sweep_tma_kernel (profiles/r01_ncu_sweep_tma_v3_summary.csv)
+# and kstar_slices_kernel + sweep_i8_kernel (profiles/r01_ncu_sweep_i8_summary.csv, one 37 888-candidate chunk)
 DRAM_BYTES_PER_CANDIDATE = (18.701e9 + 2.490e9) / 151552
+DRAM_BYTES_PER_CANDIDATE_I8 = (9.846e9 + 0.006e9 + 0.011e9 + 0.567e9) / 37888
 UNIT = 'evals/s'
 
 
@@ -308,7 +312,9 @@ def main():
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--candidates', type=int, default=1 << 24)
     ap.add_argument('--cpu-sample', type=int, default=1 << 15)
-    ap.add_argument('--sweep-impl', type=int, default=1)
+    ap.add_argument('--sweep-impl', type=int, default=3,
+                    help='3 = library default (int8-sliced contraction from 1024 observations), 2 = int8-sliced, '
+                         '1 = FP64 DMMA, 0 = plain-load cross-check')
     ap.add_argument('--skip-latency', action='store_true')
     args = ap.parse_args()
 
@@ -402,6 +408,29 @@ def main():
         fpe = flops_per_eval(N_OBS, D)
         achieved = fpe * n_local / (kernel_ms * 1e-3) / 1e12
         peak = measure_dgemm_tflops(torch, dev)
+        sliced = args.sweep_impl == 2 or (args.sweep_impl == 3 and N_OBS >= 1024)
+        if sliced:
+            nh = (N_OBS + 63) // 64                          # 64-row half-blocks of L^-1, triangular in 64-wide chunks
+            i8_ops = 36 * 2.0 * 64 * 64 * nh * (nh + 1) / 2   # 36 slice pairs, executed tensor ops per candidate
+            i8_peak = h.measure_i8_peak()
+            i8_achieved = i8_ops * n_local / (kernel_ms * 1e-3) / 1e12
+            roof_kernel = 'kstar_slices_kernel + sweep_i8_kernel (alternating, chunks of %d candidates)' % (148 * 256)
+            roof_extra = {'int8': {'executed_tops': i8_achieved, 'peak_tops': i8_peak, 'frac': i8_achieved / i8_peak,
+                                   'ops_per_eval': i8_ops,
+                                   'peak_source': 'tcgen05.mma kind::i8 m128n128k32 issue rate measured in this run '
+                                                  '(plx_measure_i8_peak); the sweep uses n64 accumulators, whose '
+                                                  'measured ceiling is 0.69 of it (tools/i8_umma_n64.cu)'},
+                          'note': 'frac is algorithmic FP64 flops over the measured DGEMM rate: the contraction runs as '
+                                  'exact 7-bit slices on the int8 tensor cores, not on the FP64 pipe'}
+            traffic = DRAM_BYTES_PER_CANDIDATE_I8 * n_local
+            traffic_note = ('DRAM bytes of the two kernels from profiles/ (ncu, one chunk), scaled per candidate: digit '
+                            'planes of K* written once and re-read per 64-row half-block of L^-1')
+        else:
+            roof_kernel = 'sweep_tma_kernel' if args.sweep_impl in (1, 3) else 'sweep_simple_kernel'
+            roof_extra = {}
+            traffic = DRAM_BYTES_PER_CANDIDATE * n_local
+            traffic_note = ('DRAM bytes of this kernel from profiles/ (ncu --set full at 151552 candidates), scaled per '
+                            'candidate: the K* slab round trip, by design')
         line = {
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
             'warmup': args.warmup, 'ms_per_step': ms_dev, 'higher_is_better': True, 'scaling': 'strong',
@@ -412,14 +441,13 @@ def main():
             'gpu_launches': launches,
             'clocks': clocks,
             'roofline': {'bound': 'tensor', 'achieved': achieved, 'peak': peak, 'unit': 'TFLOP/s',
-                         'frac': achieved / peak, 'traffic': DRAM_BYTES_PER_CANDIDATE * n_local,
-                         'kernel': 'sweep_tma_kernel' if args.sweep_impl == 1 else 'sweep_simple_kernel',
-                         'traffic_note': 'DRAM bytes of this kernel from profiles/ (ncu --set full at 151552 '
-                                         'candidates), scaled per candidate: the K* slab round trip, by design',
+                         'frac': achieved / peak, 'traffic': traffic,
+                         'kernel': roof_kernel,
+                         'traffic_note': traffic_note,
                          'kernel_ms_per_launch': kernel_ms,
                          'flops_per_eval': fpe,
                          'peak_source': 'cuBLAS DGEMM 8192^3 FP64 measured in this run (best of 6); '
-                                        'MEASURED_PEAKS.json has no FP64 figure'},
+                                        'MEASURED_PEAKS.json has no FP64 figure', **roof_extra},
             'best': {'value': best_dev[0], 'index': best_dev[1]},
         }
         # CPU baseline beside it: bounded sample, all host cores

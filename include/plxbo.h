@@ -47,7 +47,9 @@ const char* plx_version(void);
 /* Use the caller's CUDA stream (a cudaStream_t passed as void*); NULL restores the handle's own. */
 int plx_bo_set_stream(plx_bo_handle h, void* stream);
 
-/* Options: "sweep_impl" (1 = TMA ring [default], 0 = plain-load cross-check); "sweep_dbg" (profiling
+/* Options: "sweep_impl" (3 [default] = int8-sliced contraction on the tcgen05 tensor cores from 1024 observations
+ * up and the FP64 DMMA kernel below; 2 = always int8-sliced; 1 = always FP64 DMMA with the TMA ring;
+ * 0 = plain-load cross-check); "sweep_dbg" (profiling
  * only: bit 0 skips the cross-kernel build after the first tile, bit 1 skips the tensor-pipe work);
  * "lml_batch_limit" (k > 0: at most k thetas per pass of plx_gp_lml / plx_gp_fit; 0 = as many as fit
  * in the free device memory, which is also what bounds a batch too large for one pass). */
@@ -134,6 +136,11 @@ int plx_acq_sweep_resident_range(plx_bo_handle h, long long first, long long cou
 /* Device time in milliseconds of the main sweep kernel(s) of the last plx_acq_sweep* call, measured
  * with CUDA events on the launching stream, and how many kernels that call launched. */
 int plx_last_sweep_stats(plx_bo_handle h, double* kernel_ms, long long* launches);
+
+/* Measured issue rate, in TOP/s, of the int8 tensor instruction the sliced sweep is built on
+ * (tcgen05.mma kind::i8, m128 n128 k32, operands resident in shared memory, one CTA per SM): the roofline
+ * denominator bench.py reports for that path.  No counterpart in the reference. */
+int plx_measure_i8_peak(plx_bo_handle h, double* tops);
 
 /* Total number of kernels this handle has launched since creation. */
 long long plx_launch_count(plx_bo_handle h);

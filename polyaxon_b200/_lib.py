@@ -47,6 +47,7 @@ SIGNATURES = {
     'plx_acq_sweep_resident_range': (c_int, [c_void_p, c_longlong, c_longlong, c_int, c_double, c_double, c_double,
                                              _dp, POINTER(c_longlong), c_void_p]),
     'plx_last_sweep_stats': (c_int, [c_void_p, _dp, POINTER(c_longlong)]),
+    'plx_measure_i8_peak': (c_int, [c_void_p, _dp]),
     'plx_launch_count': (c_longlong, [c_void_p]),
     'plx_acq_refine': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_double, c_double, c_double, c_int,
                                c_void_p, c_void_p, c_void_p, c_void_p]),
@@ -285,6 +286,11 @@ class Handle(object):
         ms, nl = c_double(), c_longlong()
         self._check(self.lib.plx_last_sweep_stats(self._h, ctypes.byref(ms), ctypes.byref(nl)))
         return ms.value, nl.value
+
+    def measure_i8_peak(self):
+        tops = c_double()
+        self._check(self.lib.plx_measure_i8_peak(self._h, ctypes.byref(tops)))
+        return tops.value
 
     def launch_count(self):
         return int(self.lib.plx_launch_count(self._h))

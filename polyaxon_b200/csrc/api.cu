@@ -73,7 +73,7 @@ struct plx_bo {
   double* d_out[3] = {nullptr, nullptr, nullptr}; size_t out_cap = 0;
   cudaEvent_t ev_copy[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
   std::vector<cudaEvent_t> ev_pool;
-  int sweep_impl = 1, sweep_dbg = 0, lml_batch_limit = 0;
+  int sweep_impl = 3, sweep_dbg = 0, lml_batch_limit = 0;      // 3 = choose per GP state, see launch_sweep
   double last_ms = 0.0; long long last_launches = 0;
 
   // resident candidate matrix (iteration-invariant for a seeded group)
@@ -202,7 +202,7 @@ extern "C" int plx_bo_create(int device, plx_bo_handle* out) {
   h->encode = reinterpret_cast<EncodeTiledFn>(fn);
   if (const char* e = std::getenv("PLX_BO_SWEEP_IMPL")) {       // A/B switch for measurements; see plx_bo_set_option
     const int v = std::atoi(e);
-    if (v >= 0 && v <= 2) h->sweep_impl = v;
+    if (v >= 0 && v <= 3) h->sweep_impl = v;
   }
   // opt in to large dynamic shared memory once
   cudaFuncSetAttribute(potf2_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, POTF_SMEM);
@@ -252,7 +252,7 @@ extern "C" int plx_bo_set_stream(plx_bo_handle h, void* stream) {
 
 extern "C" int plx_bo_set_option(plx_bo_handle h, const char* name, long long value) {
   if (!h || !name) return PLX_ERR_INVALID;
-  if (std::strcmp(name, "sweep_impl") == 0 && value >= 0 && value <= 2) { h->sweep_impl = static_cast<int>(value); return PLX_OK; }
+  if (std::strcmp(name, "sweep_impl") == 0 && value >= 0 && value <= 3) { h->sweep_impl = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "lml_batch_limit") == 0 && value >= 0) { h->lml_batch_limit = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "sweep_dbg") == 0) { h->sweep_dbg = static_cast<int>(value); return PLX_OK; }
   return fail(h, PLX_ERR_INVALID, std::string("unknown option or value: ") + name);
@@ -695,7 +695,10 @@ static int launch_sweep(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cudaEve
   const long long ntiles = (p.N + 127) / 128;
   const int grid = static_cast<int>(std::min<long long>(ntiles, h->num_sms));
   if (grid <= 0) return PLX_OK;
-  if (h->sweep_impl == 2 && p.kind != K_GEN) return launch_sweep_i8(h, p, e0, e1);
+  // 3 (default): the int8-sliced contraction from 1024 observations up (measured crossover ~768), FP64 DMMA below
+  // and for the general-nu Matern kernel, whose Bessel evaluation dominates anyway
+  const bool sliced = h->sweep_impl == 2 || (h->sweep_impl == 3 && p.n >= 1024);
+  if (sliced && p.kind != K_GEN) return launch_sweep_i8(h, p, e0, e1);
   if (e0) CK(cudaEventRecord(e0, h->stream));
   if (h->sweep_impl >= 1) {
     sweep_tma_kernel<<<grid, 384, SWEEP_SMEM, h->stream>>>(h->tmZ, h->tmK, p);
@@ -901,6 +904,25 @@ extern "C" int plx_kernel_values(plx_bo_handle h, int kernel, double nu, const d
   LAUNCH_CHECK("kern_value_probe_kernel");
   CK(cudaMemcpyAsync(out, d_out, sizeof(double) * n, cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
+  return PLX_OK;
+}
+
+extern "C" int plx_measure_i8_peak(plx_bo_handle h, double* tops) {
+  if (!h || !tops) return h ? fail(h, PLX_ERR_INVALID, "measure_i8_peak: bad arguments") : PLX_ERR_INVALID;
+  CK(cudaSetDevice(h->device));
+  int r;
+  if ((r = need_events(h, 2)) != PLX_OK) return r;
+  const int repeats = 20000;
+  i8_peak_kernel<<<h->num_sms, 128, 0, h->stream>>>(1000);
+  LAUNCH_CHECK("i8_peak_kernel");
+  CK(cudaEventRecord(h->ev_pool[0], h->stream));
+  i8_peak_kernel<<<h->num_sms, 128, 0, h->stream>>>(repeats);
+  LAUNCH_CHECK("i8_peak_kernel");
+  CK(cudaEventRecord(h->ev_pool[1], h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  float ms = 0.f;
+  CK(cudaEventElapsedTime(&ms, h->ev_pool[0], h->ev_pool[1]));
+  *tops = 2.0 * 128 * 128 * 128 * static_cast<double>(repeats) * h->num_sms / (ms * 1e-3) / 1e12;
   return PLX_OK;
 }
 

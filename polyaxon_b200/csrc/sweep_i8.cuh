@@ -256,4 +256,49 @@ __global__ void __launch_bounds__(128) zslice_kernel(const double* __restrict__ 
   }
 }
 
+// Issue-rate probe for the roofline denominator of the int8 path: every SM repeats the four k32 steps of one
+// m128 n128 tile product on operands resident in shared memory (contents irrelevant), accumulating in TMEM.
+__global__ void __launch_bounds__(128, 1) i8_peak_kernel(int repeats) {
+  __shared__ __align__(1024) uint8_t sA[128 * 128];
+  __shared__ __align__(1024) uint8_t sB[128 * 128];
+  __shared__ __align__(8) unsigned long long bar;
+  __shared__ uint32_t tmem_base_s;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  for (int i = tid; i < 128 * 128 / 4; i += 128) {
+    reinterpret_cast<uint32_t*>(sA)[i] = 0x01010101u * (i & 3);
+    reinterpret_cast<uint32_t*>(sB)[i] = 0x01010101u;
+  }
+  asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" :: "r"(smem_u32(&tmem_base_s)), "n"(128));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n");
+  }
+  if (tid == 0) {
+    mbar_init(smem_u32(&bar), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;\n");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;\n");
+  const uint32_t tmem = tmem_base_s;
+  if (tid == 0) {
+    // 128-byte rows, 128-byte swizzle, 8-row groups 1024 bytes apart; N = 128
+    const uint64_t hi = (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+    const uint64_t da = hi | ((smem_u32(sA) & 0x3FFFF) >> 4), db = hi | ((smem_u32(sB) & 0x3FFFF) >> 4);
+    constexpr uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
+    for (int rep = 0; rep < repeats; ++rep)
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}\n"
+            :: "r"(tmem), "l"(da + 2 * k), "l"(db + 2 * k), "r"(idesc), "r"(static_cast<uint32_t>((rep | k) != 0)), "r"(0u) : "memory");
+    umma_commit(smem_u32(&bar));
+  }
+  mbar_wait(smem_u32(&bar), 0);
+  asm volatile("tcgen05.fence::before_thread_sync;\n");
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" :: "r"(tmem), "n"(128));
+}
+
 }  // namespace plx
