@@ -411,7 +411,7 @@ def main():
         sliced = args.sweep_impl == 2 or (args.sweep_impl == 3 and N_OBS >= 1024)
         if sliced:
             nh = (N_OBS + 63) // 64                          # 64-row half-blocks of L^-1, triangular in 64-wide chunks
-            i8_ops = 36 * 2.0 * 64 * 64 * nh * (nh + 1) / 2   # 36 slice pairs, executed tensor ops per candidate
+            i8_ops = 28 * 2.0 * 64 * 64 * nh * (nh + 1) / 2   # 28 digit-plane pairs, executed tensor ops per candidate
             i8_peak = h.measure_i8_peak()
             i8_achieved = i8_ops * n_local / (kernel_ms * 1e-3) / 1e12
             roof_kernel = 'kstar_slices_kernel + sweep_i8_kernel (alternating, chunks of %d candidates)' % (148 * 256)

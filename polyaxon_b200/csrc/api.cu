@@ -671,7 +671,7 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     const long long cnt = std::min(rows, p.N - base);
     const int grid = static_cast<int>(std::min<long long>((cnt + 127) / 128, h->num_sms));
     SweepParams q = p;
-    q.Xc = p.Xc + base * p.d; q.N = cnt; q.dbg = 0;
+    q.Xc = p.Xc + base * p.d; q.N = cnt; q.dbg = p.dbg & ~15;
     q.planes = h->d_kplanes; q.plane_stride = static_cast<size_t>(rows) * npad;
     kstar_slices_kernel<<<grid, 256, KSL_SMEM, st>>>(q, h->d_i8mean);
     LAUNCH_CHECK("kstar_slices_kernel");

@@ -228,18 +228,25 @@ constexpr int PA_CS = 0, PA_XS = 32 * CS_LD, PA_R2 = PA_XS + 32 * XS_LD, PA_MACC
 constexpr int PA_DOUBLES = PA_MACC + 128 * 32;
 static_assert(PA_DOUBLES * 8 <= 5 * 2 * TILE_BYTES, "phase A staging must fit in the pipeline stages");
 
-// Signed 7-bit digits of k / 2 (k in [0, 1]): k = 2 * sum_s a_s 2^(-7(s+1)) with the digits of the balanced base-128
-// expansion of round(k * 2^55), extracted with integer arithmetic from the low end (exact; |residual| <= 2^-56).
-__device__ __forceinline__ void store_digits(signed char* dst, size_t plane_stride, double k) {
-  long long q = __double2ll_rn(k * 36028797018963968.0);          // k * 2^55 = (k / 2) * 2^56
+// Digit planes of the int8-sliced sweep (sweep_i8.cuh): I8_S balanced base-256 digits in [-128, 127] per value.
+constexpr int I8_S = 7;
+
+// Balanced base-256 digits of a 56-bit fixed-point integer q (|q| < 2^54), least significant first; the leading
+// digit takes what is left (|.| <= 65).  Integer arithmetic only: exact.
+__device__ __forceinline__ void store_digits_q(signed char* dst, size_t plane_stride, long long q) {
 #pragma unroll
-  for (int s = 7; s >= 1; --s) {
-    int dgt = static_cast<int>(q & 127);
-    dgt -= (dgt >= 64) ? 128 : 0;
+  for (int s = I8_S - 1; s >= 1; --s) {
+    const int dgt = static_cast<int>((q + 128) & 255) - 128;
     dst[s * plane_stride] = static_cast<signed char>(dgt);
-    q = (q - dgt) >> 7;
+    q = (q - dgt) >> 8;
   }
-  dst[0] = static_cast<signed char>(q);                            // leading digit, 0 .. 65 (k = 1 gives 64)
+  dst[0] = static_cast<signed char>(q);
+}
+
+// Kernel value k in [0, 1]: k = 4 * sum_s a_s 256^-(s+1) with the digits of round(k * 2^54) (|residual| <= 2^-55).
+__device__ __forceinline__ void store_digits(signed char* dst, size_t plane_stride, double k, int dbg = 0) {
+  if (dbg & 16) return;
+  store_digits_q(dst, plane_stride, __double2ll_rn(k * 18014398509481984.0));
 }
 
 // SL = false: FP64 kernel values into the K* slab; SL = true: their digit planes (Kslab then points at the
@@ -260,8 +267,8 @@ __device__ __forceinline__ void kern_rows(const SweepParams& p, uint32_t sm, dou
       k1 = real1 ? k1 : 0.0;
       if constexpr (SL) {
         signed char* row = reinterpret_cast<signed char*>(Kslab) + static_cast<size_t>(c) * p.npad;
-        if (st0) store_digits(row + j0, p.plane_stride, k0);
-        if (st1) store_digits(row + j1, p.plane_stride, k1);
+        if (st0) store_digits(row + j0, p.plane_stride, k0, p.dbg);
+        if (st1) store_digits(row + j1, p.plane_stride, k1, p.dbg);
       } else {
         double* row = Kslab + static_cast<size_t>(c) * p.npad;
         if (st0) row[j0] = k0;
@@ -288,8 +295,8 @@ __device__ __forceinline__ void kern_rows(const SweepParams& p, uint32_t sm, dou
       const double k0 = real0 ? v[2 * u] : 0.0, k1 = real1 ? v[2 * u + 1] : 0.0;
       if constexpr (SL) {
         signed char* row = reinterpret_cast<signed char*>(Kslab) + static_cast<size_t>(c) * p.npad;
-        if (st0) store_digits(row + j0, p.plane_stride, k0);
-        if (st1) store_digits(row + j1, p.plane_stride, k1);
+        if (st0) store_digits(row + j0, p.plane_stride, k0, p.dbg);
+        if (st1) store_digits(row + j1, p.plane_stride, k1, p.dbg);
       } else {
         double* row = Kslab + static_cast<size_t>(c) * p.npad;
         if (st0) row[j0] = k0;

@@ -1,14 +1,15 @@
 // Variant 2 of the acquisition sweep (opt-in, "sweep_impl" = 2): the variance contraction V = K* . Z^T on the
 // int8 tensor cores by exact slicing, instead of FP64 DMMA.
 //
-//   K*[c][j] = 2 * sum_s a_s[c][j] 2^(-7(s+1))                  a_s signed 7-bit digits (K* in [0, 1], fixed exponent)
-//   Z[i][j]  = 2^f_i * sum_t b_t[i][j] 2^(-7(t+1))              f_i from the largest entry of row i of L^-1
-//   V[c][i]  = 2^(f_i+1) * sum_{s+t<S} 2^(-7(s+t+2)) (a_s[c] . b_t[i])
+//   K*[c][j] = 4 * sum_s a_s[c][j] 256^-(s+1)                   a_s balanced 8-bit digits (K* in [0, 1], fixed exponent)
+//   Z[i][j]  = 2^f_i * sum_t b_t[i][j] 256^-(t+1)               f_i from the largest entry of row i of L^-1
+//   V[c][i]  = 2^(f_i+2) * sum_{s+t<S} 256^-(s+t+2) (a_s[c] . b_t[i])
 //
 // Every dot product a_s . b_t is an exact int32 (tcgen05.mma kind::i8, accumulators in TMEM); the S scale
 // classes s + t = 0 .. S-1 are kept in S separate accumulators and recombined in FP64, smallest first.  With
-// S = 8 the result is at least as accurate as an FP64 FMA chain (tools/ozaki_probe.cu: 3.5e-16 relative to
-// sum |K* Z| at n = 2048).  Reference arithmetic being reproduced: sklearn _gpr.py:460-481.
+// S = 7 digits of 8 bits (56 bits per operand, 28 digit-plane pairs) the result is as accurate as an FP64 FMA
+// chain (tools/ozaki_probe.cu measured 3.5e-16 relative to sum |K* Z| at n = 2048 for 8 x 7 bits, the same
+// 56 bits and the same truncation order 2^-47).  Reference arithmetic being reproduced: sklearn _gpr.py:460-481.
 //
 // Two kernels per chunk of candidates:
 //   kstar_slices_kernel  phase A of variant 1 (same distances, same kernel values, same posterior mean) writing
@@ -16,7 +17,7 @@
 //   sweep_i8_kernel      persistent, 192 threads: warp 4 streams the digit planes of a 128-candidate tile and of a
 //                        64-row half-block of Z through a two-stage ring (one 3-D bulk tensor load per operand and
 //                        64-observation chunk, 64-byte swizzle), warp 5 issues the 72 tensor instructions per stage
-//                        (36 slice pairs x 2 k-steps) into 8 x 64 TMEM columns, warps 0-3 drain the accumulators of a
+//                        (28 digit-plane pairs x 2 k-steps) into 7 x 64 TMEM columns, warps 0-3 drain the accumulators of a
 //                        finished half-block (tcgen05.ld), recombine in FP64, scale, square and sum per candidate, and
 //                        finish with variance -> acquisition -> arg-max exactly as variant 1.
 #pragma once
@@ -24,7 +25,6 @@
 
 namespace plx {
 
-constexpr int I8_S = 8;                               // digit planes per operand
 constexpr int I8_KC = 64;                             // observations (= bytes) per K chunk
 constexpr int I8_A_SLICE = 128 * I8_KC;               // one plane of the candidate tile chunk
 constexpr int I8_B_SLICE = 64 * I8_KC;                // one plane of the Z half-block chunk
@@ -38,7 +38,7 @@ struct I8Params {
   long long N;                 // candidates of this launch (one chunk)
   long long idx_base;          // global index of candidate 0 of this launch
   int n;                       // observations
-  const double* zscale;        // [npad]: 2^(f_i + 1), zero for rows >= n
+  const double* zscale;        // [npad]: 2^(f_i + 2), zero for rows >= n
   const double* mean;          // [N] posterior means written by kstar_slices_kernel
   int acq;
   double kappa, eps, y_max;
@@ -169,7 +169,7 @@ __global__ void __launch_bounds__(192, 1) sweep_i8_kernel(const __grid_constant_
                   "=r"(u[8]), "=r"(u[9]), "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15])
                 : "r"(tmem + lane_base + cls * 64 + c0));
             asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
-            const double w = __longlong_as_double(static_cast<long long>(1023 - 7 * (cls + 2)) << 52);   // 2^(-7(cls+2))
+            const double w = __longlong_as_double(static_cast<long long>(1023 - 8 * (cls + 2)) << 52);   // 256^-(cls+2)
 #pragma unroll
             for (int i = 0; i < 16; ++i) v[i] = fma(static_cast<double>(static_cast<int>(u[i])), w, v[i]);
           }
@@ -227,7 +227,7 @@ __global__ void __launch_bounds__(256, 1) kstar_slices_kernel(const SweepParams 
 }
 
 // Digit planes and row scales of Z = L^-1 (lower triangular, npad x npad).  One CTA per row.
-// planes[s][i][j]; zscale[i] = 2^(f_i + 1) for i < n, else 0 (the extra factor 2 is K*'s fixed exponent).
+// planes[s][i][j]; zscale[i] = 2^(f_i + 2) for i < n, else 0 (the extra factor 4 is K*'s fixed exponent).
 __global__ void __launch_bounds__(128) zslice_kernel(const double* __restrict__ Z, int npad, int n,
                                                      int8_t* __restrict__ planes, double* __restrict__ zscale) {
   __shared__ double red[128];
@@ -241,18 +241,12 @@ __global__ void __launch_bounds__(128) zslice_kernel(const double* __restrict__ 
   for (int o = 64; o > 0; o >>= 1) { if (tid < o) red[tid] = fmax(red[tid], red[tid + o]); __syncthreads(); }
   m = red[0];
   int e = 0;
-  if (m > 0.0) { frexp(m, &e); e += 1; }          // m * 2^-e in [1/4, 1/2)
-  if (tid == 0) zscale[i] = (i < n && m > 0.0) ? ldexp(1.0, e + 1) : 0.0;
+  if (m > 0.0) { frexp(m, &e); e += 2; }          // m * 2^-e in [1/8, 1/4): the leading digit stays below 65
+  if (tid == 0) zscale[i] = (i < n && m > 0.0) ? ldexp(1.0, e + 2) : 0.0;
   const size_t pstride = static_cast<size_t>(npad) * npad;
   for (int j = tid; j < npad; j += 128) {
-    double x = (i < n && j <= i) ? ldexp(row[j], -e) : 0.0;
-#pragma unroll
-    for (int s = 0; s < I8_S; ++s) {
-      x *= 128.0;
-      const double a = rint(x);
-      planes[s * pstride + static_cast<size_t>(i) * npad + j] = static_cast<int8_t>(static_cast<int>(a));
-      x -= a;
-    }
+    const double x = (i < n && j <= i) ? ldexp(row[j], 56 - e) : 0.0;          // |x| < 2^54
+    store_digits_q(reinterpret_cast<signed char*>(planes) + static_cast<size_t>(i) * npad + j, pstride, __double2ll_rn(x));
   }
 }
 

@@ -1,0 +1,22 @@
+"""Time split of the int8-sliced sweep: whole, without the digit stores, with trivial digits."""
+import sys
+import numpy as np
+sys.path.insert(0, '.')
+from polyaxon_b200 import _lib
+from oracle.reference_path import synthetic_problem
+import torch
+n, d, N = 2048, 32, 148 * 128 * 8
+X, y, _ = synthetic_problem(n, d)
+h = _lib.Handle(0)
+h.set_data(X, y, 1, 1.5)
+h.set_theta(1.2)
+xc = torch.rand(N, d, dtype=torch.float64, device='cuda')
+torch.cuda.synchronize()
+h.set_option('sweep_impl', 2)
+for dbg in (0, 16, 32):
+    h.set_option('sweep_dbg', dbg)
+    ms = []
+    for _ in range(3):
+        h.sweep_dev(xc.data_ptr(), N, _lib.ACQ_POI, float(y.max()))
+        ms.append(h.last_sweep_stats()[0])
+    print('dbg %d: %.2f ms' % (dbg, min(ms)))
