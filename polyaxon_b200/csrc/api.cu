@@ -3,7 +3,7 @@
 #include "../../include/plxbo.h"
 #include "refine.cuh"
 #include "append.cuh"
-#include "sweep_i8.cuh"
+#include "sweep_i8f.cuh"
 
 #include <cstdio>
 #include <cstdlib>
@@ -202,7 +202,7 @@ extern "C" int plx_bo_create(int device, plx_bo_handle* out) {
   h->encode = reinterpret_cast<EncodeTiledFn>(fn);
   if (const char* e = std::getenv("PLX_BO_SWEEP_IMPL")) {       // A/B switch for measurements; see plx_bo_set_option
     const int v = std::atoi(e);
-    if (v >= 0 && v <= 3) h->sweep_impl = v;
+    if (v >= 0 && v <= 4) h->sweep_impl = v;
   }
   // opt in to large dynamic shared memory once
   cudaFuncSetAttribute(potf2_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, POTF_SMEM);
@@ -214,6 +214,7 @@ extern "C" int plx_bo_create(int device, plx_bo_handle* out) {
   cudaFuncSetAttribute(sweep_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SWEEP_SMEM);
   cudaFuncSetAttribute(sweep_simple_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SWEEP_SIMPLE_SMEM);
   cudaFuncSetAttribute(sweep_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, I8_SMEM);
+  cudaFuncSetAttribute(sweep_i8f_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, I8F_SMEM);
   cudaFuncSetAttribute(kstar_slices_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, KSL_SMEM);
   if (cudaGetLastError() != cudaSuccess) return bail("cudaFuncSetAttribute failed (is the library built for this GPU?)");
   if (cudaMalloc(&h->d_blk_val, sizeof(double) * 1024) != cudaSuccess ||
@@ -252,7 +253,7 @@ extern "C" int plx_bo_set_stream(plx_bo_handle h, void* stream) {
 
 extern "C" int plx_bo_set_option(plx_bo_handle h, const char* name, long long value) {
   if (!h || !name) return PLX_ERR_INVALID;
-  if (std::strcmp(name, "sweep_impl") == 0 && value >= 0 && value <= 3) { h->sweep_impl = static_cast<int>(value); return PLX_OK; }
+  if (std::strcmp(name, "sweep_impl") == 0 && value >= 0 && value <= 4) { h->sweep_impl = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "lml_batch_limit") == 0 && value >= 0) { h->lml_batch_limit = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "sweep_dbg") == 0) { h->sweep_dbg = static_cast<int>(value); return PLX_OK; }
   return fail(h, PLX_ERR_INVALID, std::string("unknown option or value: ") + name);
@@ -667,6 +668,23 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     h->i8_state_valid = true;
   }
   if (e0) CK(cudaEventRecord(e0, st));
+  if (h->sweep_impl == 4) {
+    // fused form: one persistent launch, the planes of the next tile are built while the current one is contracted
+    const int grid = static_cast<int>(std::min<long long>((p.N + 127) / 128, h->num_sms));
+    SweepParams q = p;
+    q.dbg = 0; q.planes = h->d_kplanes; q.plane_stride = static_cast<size_t>(rows) * npad;
+    I8Params ip;
+    ip.N = p.N; ip.idx_base = p.idx_base; ip.n = p.n; ip.zscale = h->d_zscale; ip.mean = nullptr;
+    ip.acq = p.acq; ip.kappa = p.kappa; ip.eps = p.eps; ip.y_max = p.y_max;
+    ip.out_mean = p.out_mean; ip.out_std = p.out_std; ip.out_acq = p.out_acq;
+    ip.blk_val = h->d_blk_val; ip.blk_idx = h->d_blk_idx;
+    sweep_i8f_kernel<<<grid, 512, I8F_SMEM, st>>>(h->tmA8, h->tmB8, q, ip, h->d_i8mean);
+    LAUNCH_CHECK("sweep_i8f_kernel");
+    sweep_merge_kernel<<<1, 32, 0, st>>>(h->d_blk_val, h->d_blk_idx, grid, h->d_best_val, h->d_best_idx);
+    LAUNCH_CHECK("sweep_merge_kernel");
+    if (e1) CK(cudaEventRecord(e1, st));
+    return PLX_OK;
+  }
   for (long long base = 0; base < p.N; base += rows) {
     const long long cnt = std::min(rows, p.N - base);
     const int grid = static_cast<int>(std::min<long long>((cnt + 127) / 128, h->num_sms));
@@ -697,7 +715,7 @@ static int launch_sweep(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cudaEve
   if (grid <= 0) return PLX_OK;
   // 3 (default): the int8-sliced contraction from 1024 observations up (measured crossover ~768), FP64 DMMA below
   // and for the general-nu Matern kernel, whose Bessel evaluation dominates anyway
-  const bool sliced = h->sweep_impl == 2 || (h->sweep_impl == 3 && p.n >= 1024);
+  const bool sliced = h->sweep_impl == 2 || h->sweep_impl == 4 || (h->sweep_impl == 3 && p.n >= 1024);
   if (sliced && p.kind != K_GEN) return launch_sweep_i8(h, p, e0, e1);
   if (e0) CK(cudaEventRecord(e0, h->stream));
   if (h->sweep_impl >= 1) {

@@ -1,0 +1,324 @@
+// Fused form of the int8-sliced sweep (sweep_i8.cuh): one persistent CTA per SM in which the digit planes of the
+// NEXT candidate tile are built on the FP64 pipe while the tensor pipe contracts the CURRENT tile.
+//
+// 512 threads, four warpgroups:
+//   WG0, WG1 (warps 0-7)   builders: scaled squared distances for 8 candidates x 4 consecutive observations per
+//                          thread from shared tiles, kernel values straight from those registers (no staging of the
+//                          distance block), balanced 8-bit digits packed four to a 32-bit store into the CTA's own
+//                          plane buffer in global memory (two tiles deep), posterior mean reduced with shuffles;
+//   WG2 (warps 8-11)       accumulator drain + epilogue, one thread per candidate (= TMEM lane);
+//   WG3 (warp 12, 13)      TMA producer and tensor-instruction issuer, one elected lane each.
+// The roles meet only through mbarriers: planes ready (builders -> producer, drain), planes free (drain ->
+// builders), stage full / empty, accumulators full / empty.  Arithmetic is that of kstar_slices_kernel +
+// sweep_i8_kernel; only the summation order of the posterior mean differs (per-thread partial sums over the
+// observations 4 tx .. 4 tx + 3 of every 64-block, then a 16-lane butterfly).
+#pragma once
+#include "sweep_i8.cuh"
+
+namespace plx {
+
+constexpr int F_CS_LD = 130;                               // Cs[32 dims][130]: scaled candidates of the tile
+constexpr int F_XS_LD = 64;                                // Xs[32 dims][64]: scaled observations of a 64-block
+constexpr int F_CS = 0, F_XS = 32 * F_CS_LD;
+constexpr int F_STAGING = (F_XS + 32 * F_XS_LD) * 8;       // 49 664 bytes
+constexpr int I8F_SMEM = I8_STAGES * I8_STAGE + F_STAGING + 1024 /*align*/ + 3072 /*tail*/;
+
+struct I8FTail {
+  unsigned long long bars[2 * I8_STAGES + 2 + 4];   // full[ST], empty[ST], acc full, acc empty, planes ready[2], planes free[2]
+  uint32_t tmem_base;
+  double sval[128];
+  long long sidx[128];
+};
+static_assert(sizeof(I8FTail) <= 3072, "tail budget");
+
+// Four kernel values of one candidate -> 7 planes x 4 packed digits (one 32-bit store per plane).
+__device__ __forceinline__ void store_digits4(signed char* dst, size_t plane_stride, const double (&k)[4]) {
+  long long q[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) q[j] = __double2ll_rn(k[j] * 18014398509481984.0);     // k * 2^54
+#pragma unroll
+  for (int s = I8_S - 1; s >= 0; --s) {
+    uint32_t word = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int dgt;
+      if (s > 0) { dgt = static_cast<int>((q[j] + 128) & 255) - 128; q[j] = (q[j] - dgt) >> 8; }
+      else dgt = static_cast<int>(q[j]);                                              // leading digit, 0 .. 65
+      word |= static_cast<uint32_t>(dgt & 255) << (8 * j);
+    }
+    *reinterpret_cast<uint32_t*>(dst + s * plane_stride) = word;
+  }
+}
+
+// Kernel values, digits and mean contribution of one thread's 8 x 4 block of squared distances.
+template <int KIND>
+__device__ __forceinline__ void builder_block(const SweepParams& p, double (&r2)[8][4], signed char* rows, int jo,
+                                              int ty, double (&macc)[8]) {
+  double al[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) al[j] = (jo + j < p.n) ? p.alpha[jo + j] : 0.0;
+#pragma unroll
+  for (int i = 0; i < 8; i += 2) {
+    double v[8];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { v[j] = r2[i][j]; v[4 + j] = r2[i + 1][j]; }
+    kern_values_n<KIND, 8>(v);
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      double k[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) k[j] = (jo + j < p.n) ? v[4 * u + j] : 0.0;
+      store_digits4(rows + static_cast<size_t>(ty * 8 + i + u) * p.npad + jo, p.plane_stride, k);
+      macc[i + u] += (k[0] * al[0] + k[1] * al[1]) + (k[2] * al[2] + k[3] * al[3]);
+    }
+  }
+}
+
+// Builder role for one tile: planes into `rows` (plane 0, first candidate row of the tile buffer), means into mean_out.
+__device__ __forceinline__ void build_tile(const SweepParams& p, long long tile, signed char* rows, double* mean_out,
+                                           uint32_t sm, int tid) {
+  const int tx = tid & 15, ty = tid >> 4;
+  const long long c_base = tile * 128;
+  const int nchunk_d = (p.d + 31) / 32;
+  const int nblk = (p.n + 63) / 64;
+  double macc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) macc[i] = 0.0;
+  double pre[8];                      // element e = tid + 256 r of a 32 x 64 block: q = e >> 6, j = e & 63
+  auto fetch = [&](int jb, int dc) {
+    const int d0 = dc * 32, dn = min(32, p.d - d0);
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      const int e = tid + 256 * r, q = e >> 6, j = e & 63;
+      pre[r] = (q < dn) ? p.Xt[static_cast<size_t>(d0 + q) * p.npad + jb * 64 + j] : 0.0;
+    }
+  };
+  fetch(0, 0);
+  for (int jb = 0; jb < nblk; ++jb) {
+    double r2[8][4];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) r2[i][j] = 0.0;
+    for (int dc = 0; dc < nchunk_d; ++dc) {
+      const int d0 = dc * 32, dn = min(32, p.d - d0);
+      named_bar_sync(1, 256);                                 // readers of the previous shared tiles are done
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {
+        const int e = tid + 256 * r;
+        sts64(sm + static_cast<uint32_t>((F_XS + (e >> 6) * F_XS_LD + (e & 63)) * 8), pre[r]);
+      }
+      if (jb == 0 || nchunk_d > 1) {
+        for (int e = tid; e < 128 * 32; e += 256) {
+          const int c = e >> 5, q = e & 31;
+          double v = 0.0;
+          if (q < dn && c_base + c < p.N) v = p.Xc[(c_base + c) * p.d + d0 + q] / p.ell;
+          sts64(sm + static_cast<uint32_t>((F_CS + q * F_CS_LD + c) * 8), v);
+        }
+      }
+      named_bar_sync(1, 256);
+      {                                                       // prefetch the next (jb, dc)
+        int njb = jb, ndc = dc + 1;
+        if (ndc == nchunk_d) { ndc = 0; ++njb; }
+        if (njb < nblk) fetch(njb, ndc);
+      }
+      const uint32_t cs = sm + static_cast<uint32_t>((F_CS + ty * 8) * 8);
+      const uint32_t xs = sm + static_cast<uint32_t>((F_XS + 4 * tx) * 8);
+#pragma unroll 2
+      for (int q = 0; q < dn; ++q) {
+        double cv[8], xv[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { const double2 t2 = lds128(cs + (q * F_CS_LD + 2 * i) * 8); cv[2 * i] = t2.x; cv[2 * i + 1] = t2.y; }
+        { const double2 a = lds128(xs + q * F_XS_LD * 8), b = lds128(xs + q * F_XS_LD * 8 + 16); xv[0] = a.x; xv[1] = a.y; xv[2] = b.x; xv[3] = b.y; }
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) { const double df = cv[i] - xv[j]; r2[i][j] += df * df; }
+      }
+    }
+    const int jo = jb * 64 + 4 * tx;
+    switch (p.kind) {
+      case K_RBF: builder_block<K_RBF>(p, r2, rows, jo, ty, macc); break;
+      case K_M05: builder_block<K_M05>(p, r2, rows, jo, ty, macc); break;
+      case K_M15: builder_block<K_M15>(p, r2, rows, jo, ty, macc); break;
+      default: builder_block<K_M25>(p, r2, rows, jo, ty, macc); break;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    double m = macc[i];
+    m += __shfl_xor_sync(0xffffffffu, m, 1);
+    m += __shfl_xor_sync(0xffffffffu, m, 2);
+    m += __shfl_xor_sync(0xffffffffu, m, 4);
+    m += __shfl_xor_sync(0xffffffffu, m, 8);
+    if (tx == 0) mean_out[ty * 8 + i] = m;
+  }
+}
+
+// p: the builders' view (candidates, observations, planes = this launch's plane buffer of gridDim.x * 2 tiles,
+// plane_stride); ip: the contraction's view (ip.mean = mean buffer of gridDim.x * 256 doubles).
+__global__ void __launch_bounds__(512, 1) sweep_i8f_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                           const __grid_constant__ CUtensorMap tmB,
+                                                           const SweepParams p, const I8Params ip, double* meanbuf) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = align1k(smem_raw);
+  I8FTail* tail = reinterpret_cast<I8FTail*>(smem + I8_STAGES * I8_STAGE + F_STAGING);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t s0 = smem_u32(smem);
+  const uint32_t bar0 = smem_u32(tail->bars);
+  const uint32_t bar_accf = bar0 + 8 * (2 * I8_STAGES), bar_acce = bar_accf + 8;
+  const uint32_t bar_ready = bar_acce + 8, bar_free = bar_ready + 16;      // two each, one per plane buffer
+  if (tid == 0) {
+    for (int s = 0; s < I8_STAGES; ++s) { mbar_init(bar0 + 8 * s, 1); mbar_init(bar0 + 8 * (I8_STAGES + s), 1); }
+    mbar_init(bar_accf, 1);
+    mbar_init(bar_acce, 128);
+    for (int b = 0; b < 2; ++b) { mbar_init(bar_ready + 8 * b, 8); mbar_init(bar_free + 8 * b, 128); }
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  if (warp == 8) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" :: "r"(smem_u32(&tail->tmem_base)), "n"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;\n");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;\n");
+  const uint32_t tmem = tail->tmem_base;
+
+  const long long ntiles = (ip.N + 127) / 128;
+  const int nh = (ip.n + 63) / 64;
+  const int buf_row0 = blockIdx.x * 256;               // this CTA's two tile buffers: rows buf_row0 + 128 b
+
+  if (warp < 8) {
+    // ===== builders =====
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 168;\n");
+    const uint32_t sm = s0 + I8_STAGES * I8_STAGE;
+    uint32_t t = 0;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t) {
+      const uint32_t b = t & 1, use = t >> 1;
+      if (use > 0) mbar_wait(bar_free + 8 * b, (use - 1) & 1);       // the tile that used this buffer is consumed
+      signed char* rows = p.planes + static_cast<size_t>(buf_row0 + 128 * b) * p.npad;
+      build_tile(p, tile, rows, meanbuf + buf_row0 + 128 * b, sm, tid);
+      __threadfence();
+      asm volatile("fence.proxy.async;\n" ::: "memory");            // generic-proxy stores -> visible to TMA
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_ready + 8 * b);
+    }
+  } else if (warp < 12) {
+    // ===== accumulator drain + epilogue: thread = candidate row of the tile = TMEM lane =====
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 120;\n");
+    const int row = tid - 256;
+    Best best = {-INFINITY, 0x7fffffffffffffffLL};
+    uint32_t acc_round = 0, t = 0;
+    const uint32_t lane_base = static_cast<uint32_t>((warp - 8) * 32) << 16;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t) {
+      const uint32_t b = t & 1, use = t >> 1;
+      double sumsq = 0.0;
+      for (int h = 0; h < nh; ++h, ++acc_round) {
+        mbar_wait(bar_accf, acc_round & 1);
+        asm volatile("tcgen05.fence::after_thread_sync;\n");
+#pragma unroll 1
+        for (int c0 = 0; c0 < 64; c0 += 16) {
+          double v[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] = 0.0;
+#pragma unroll
+          for (int cls = I8_S - 1; cls >= 0; --cls) {      // smallest contributions first
+            uint32_t u[16];
+            asm volatile(
+                "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];\n"
+                : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]),
+                  "=r"(u[8]), "=r"(u[9]), "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15])
+                : "r"(tmem + lane_base + cls * 64 + c0));
+            asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+            const double w = __longlong_as_double(static_cast<long long>(1023 - 8 * (cls + 2)) << 52);   // 256^-(cls+2)
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = fma(static_cast<double>(static_cast<int>(u[i])), w, v[i]);
+          }
+          const double* zs = ip.zscale + h * 64 + c0;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) { const double x = v[i] * zs[i]; sumsq = fma(x, x, sumsq); }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;\n");
+        mbar_arrive(bar_acce);
+      }
+      // all tensor instructions of the tile have completed, hence all loads of its planes: the means were
+      // written before the builders' arrival on `ready`, which the producer (and so this point) is ordered after
+      mbar_wait(bar_ready + 8 * b, use & 1);
+      const double mean = meanbuf[buf_row0 + 128 * b + row];
+      mbar_arrive(bar_free + 8 * b);
+      const long long ci = tile * 128 + row;
+      if (ci < ip.N) {
+        double var = 1.0 - sumsq;
+        if (var < 0.0) var = 0.0;                 // sklearn clamps negative variances to zero
+        const double sd = sqrt(var);
+        const double a = acq_value(ip.acq, mean, sd, ip.y_max, ip.kappa, ip.eps);
+        if (ip.out_mean) ip.out_mean[ci] = mean;
+        if (ip.out_std) ip.out_std[ci] = sd;
+        if (ip.out_acq) ip.out_acq[ci] = a;
+        const long long gi = ip.idx_base + ci;
+        if (better(a, gi, best.v, best.i)) { best.v = a; best.i = gi; }
+      }
+    }
+    tail->sval[row] = best.v; tail->sidx[row] = best.i;
+    named_bar_sync(2, 128);
+    if (row == 0) {
+      Best bb = {tail->sval[0], tail->sidx[0]};
+      for (int q = 1; q < 128; ++q)
+        if (better(tail->sval[q], tail->sidx[q], bb.v, bb.i)) { bb.v = tail->sval[q]; bb.i = tail->sidx[q]; }
+      ip.blk_val[blockIdx.x] = bb.v;
+      ip.blk_idx[blockIdx.x] = bb.i;
+    }
+  } else {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 48;\n");
+    if (warp == 12 && lane == 0) {
+      // ===== producer =====
+      uint32_t it = 0, t = 0;
+      for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t) {
+        const uint32_t b = t & 1, use = t >> 1;
+        mbar_wait(bar_ready + 8 * b, use & 1);              // the tile's planes are complete and visible to TMA
+        for (int h = 0; h < nh; ++h)
+          for (int kc = 0; kc <= h; ++kc, ++it) {
+            const uint32_t s = it % I8_STAGES, ph = (it / I8_STAGES) & 1;
+            mbar_wait(bar0 + 8 * (I8_STAGES + s), ph ^ 1);
+            const uint32_t full = bar0 + 8 * s;
+            mbar_expect_tx(full, I8_STAGE);
+            tma_load_3d(s0 + s * I8_STAGE, &tmA, kc * I8_KC, buf_row0 + 128 * static_cast<int>(b), 0, full);
+            tma_load_3d(s0 + s * I8_STAGE + I8_A_BYTES, &tmB, kc * I8_KC, h * 64, 0, full);
+          }
+      }
+    } else if (warp == 13 && lane == 0) {
+      // ===== tensor-instruction issuer =====
+      uint32_t it = 0, acc_round = 0;
+      for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
+        for (int h = 0; h < nh; ++h, ++acc_round) {
+          mbar_wait(bar_acce, (acc_round & 1) ^ 1);        // the previous half-block has been drained
+          asm volatile("tcgen05.fence::after_thread_sync;\n");
+          for (int kc = 0; kc <= h; ++kc, ++it) {
+            const uint32_t s = it % I8_STAGES, ph = (it / I8_STAGES) & 1;
+            mbar_wait(bar0 + 8 * s, ph);
+            asm volatile("tcgen05.fence::after_thread_sync;\n");
+            const uint32_t a0 = s0 + s * I8_STAGE;
+            const uint64_t da0 = umma_desc_sw64(a0), db0 = umma_desc_sw64(a0 + I8_A_BYTES);
+            const uint32_t fresh = (kc != 0);              // the first chunk of a half-block overwrites the accumulators
+#pragma unroll
+            for (int tt = 0; tt < I8_S; ++tt) {
+#pragma unroll
+              for (int sl = 0; sl + tt < I8_S; ++sl) {
+                const uint64_t da = da0 + static_cast<uint64_t>(sl * (I8_A_SLICE / 16));
+                const uint64_t db = db0 + static_cast<uint64_t>(tt * (I8_B_SLICE / 16));
+                umma_i8(tmem + (sl + tt) * 64, da, db, tt == 0 ? fresh : 1u);
+                umma_i8(tmem + (sl + tt) * 64, da + 2, db + 2, 1u);
+              }
+            }
+            umma_commit(bar0 + 8 * (I8_STAGES + s));       // stage free once these instructions have read it
+          }
+          umma_commit(bar_accf);                           // accumulators of this half-block complete
+        }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;\n");
+  __syncthreads();
+  if (warp == 8) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" :: "r"(tmem), "n"(512));
+}
+
+}  // namespace plx
