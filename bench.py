@@ -313,8 +313,8 @@ def main():
     ap.add_argument('--candidates', type=int, default=1 << 24)
     ap.add_argument('--cpu-sample', type=int, default=1 << 15)
     ap.add_argument('--sweep-impl', type=int, default=3,
-                    help='3 = library default (int8-sliced contraction from 1024 observations), 2 = int8-sliced, '
-                         '1 = FP64 DMMA, 0 = plain-load cross-check')
+                    help='3 = library default (fused int8-sliced sweep from 256 observations), 4 = fused int8-sliced, '
+                         '2 = int8-sliced as two kernels, 1 = FP64 DMMA, 0 = plain-load cross-check')
     ap.add_argument('--skip-latency', action='store_true')
     args = ap.parse_args()
 
@@ -408,13 +408,14 @@ def main():
         fpe = flops_per_eval(N_OBS, D)
         achieved = fpe * n_local / (kernel_ms * 1e-3) / 1e12
         peak = measure_dgemm_tflops(torch, dev)
-        sliced = args.sweep_impl == 2 or (args.sweep_impl == 3 and N_OBS >= 1024)
+        sliced = args.sweep_impl in (2, 4) or (args.sweep_impl == 3 and N_OBS >= 256)
         if sliced:
             nh = (N_OBS + 63) // 64                          # 64-row half-blocks of L^-1, triangular in 64-wide chunks
             i8_ops = 28 * 2.0 * 64 * 64 * nh * (nh + 1) / 2   # 28 digit-plane pairs, executed tensor ops per candidate
             i8_peak = h.measure_i8_peak()
             i8_achieved = i8_ops * n_local / (kernel_ms * 1e-3) / 1e12
-            roof_kernel = 'kstar_slices_kernel + sweep_i8_kernel (alternating, chunks of %d candidates)' % (148 * 256)
+            roof_kernel = ('kstar_slices_kernel + sweep_i8_kernel (alternating, chunks of %d candidates)' % (148 * 256)
+                           if args.sweep_impl == 2 else 'sweep_i8f_kernel (digit-plane builders + int8 contraction fused)')
             roof_extra = {'int8': {'executed_tops': i8_achieved, 'peak_tops': i8_peak, 'frac': i8_achieved / i8_peak,
                                    'ops_per_eval': i8_ops,
                                    'peak_source': 'tcgen05.mma kind::i8 m128n128k32 issue rate measured in this run '

@@ -639,7 +639,7 @@ static int make_map_i8(plx_bo* h, CUtensorMap* map, signed char* base, size_t co
   cuuint32_t box[3] = {I8_KC, static_cast<cuuint32_t>(box_rows), I8_S};
   cuuint32_t estr[3] = {1, 1, 1};
   const CUresult r = h->encode(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box, estr,
-                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, I8_KC == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B,
                                CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(h, PLX_ERR_CUDA, "cuTensorMapEncodeTiled (int8 planes) failed with code " + std::to_string(r));
   return PLX_OK;
@@ -668,11 +668,11 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     h->i8_state_valid = true;
   }
   if (e0) CK(cudaEventRecord(e0, st));
-  if (h->sweep_impl == 4) {
+  if (h->sweep_impl != 2) {
     // fused form: one persistent launch, the planes of the next tile are built while the current one is contracted
     const int grid = static_cast<int>(std::min<long long>((p.N + 127) / 128, h->num_sms));
     SweepParams q = p;
-    q.dbg = 0; q.planes = h->d_kplanes; q.plane_stride = static_cast<size_t>(rows) * npad;
+    q.dbg = p.dbg & ~15; q.planes = h->d_kplanes; q.plane_stride = static_cast<size_t>(rows) * npad;
     I8Params ip;
     ip.N = p.N; ip.idx_base = p.idx_base; ip.n = p.n; ip.zscale = h->d_zscale; ip.mean = nullptr;
     ip.acq = p.acq; ip.kappa = p.kappa; ip.eps = p.eps; ip.y_max = p.y_max;
@@ -713,9 +713,9 @@ static int launch_sweep(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cudaEve
   const long long ntiles = (p.N + 127) / 128;
   const int grid = static_cast<int>(std::min<long long>(ntiles, h->num_sms));
   if (grid <= 0) return PLX_OK;
-  // 3 (default): the int8-sliced contraction from 1024 observations up (measured crossover ~768), FP64 DMMA below
-  // and for the general-nu Matern kernel, whose Bessel evaluation dominates anyway
-  const bool sliced = h->sweep_impl == 2 || h->sweep_impl == 4 || (h->sweep_impl == 3 && p.n >= 1024);
+  // 3 (default): the fused int8-sliced sweep from 256 observations up (measured break-even between 128 and 256),
+  // FP64 DMMA below and for the general-nu Matern kernel, whose Bessel evaluation dominates anyway
+  const bool sliced = h->sweep_impl == 2 || h->sweep_impl == 4 || (h->sweep_impl == 3 && p.n >= 256);
   if (sliced && p.kind != K_GEN) return launch_sweep_i8(h, p, e0, e1);
   if (e0) CK(cudaEventRecord(e0, h->stream));
   if (h->sweep_impl >= 1) {

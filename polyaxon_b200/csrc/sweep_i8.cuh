@@ -25,13 +25,15 @@
 
 namespace plx {
 
-constexpr int I8_KC = 64;                             // observations (= bytes) per K chunk
+constexpr int I8_KC = 64;                             // observations (= bytes) per K chunk: 32 or 64 (measured equal)
+constexpr int I8_KSTEPS = I8_KC / 32;                 // k32 tensor instructions per chunk and digit pair
+constexpr int I8_CPH = 64 / I8_KC;                    // chunks per 64 observations
 constexpr int I8_A_SLICE = 128 * I8_KC;               // one plane of the candidate tile chunk
 constexpr int I8_B_SLICE = 64 * I8_KC;                // one plane of the Z half-block chunk
 constexpr int I8_A_BYTES = I8_S * I8_A_SLICE;         // 64 KiB
 constexpr int I8_B_BYTES = I8_S * I8_B_SLICE;         // 32 KiB
 constexpr int I8_STAGE = I8_A_BYTES + I8_B_BYTES;
-constexpr int I8_STAGES = 2;
+constexpr int I8_STAGES = 128 / I8_KC;                // 2 x 84 KB or 4 x 42 KB in flight
 constexpr int I8_SMEM = I8_STAGES * I8_STAGE + 1024 /*align*/ + 3072 /*tail*/;
 
 struct I8Params {
@@ -46,9 +48,11 @@ struct I8Params {
   double* blk_val; long long* blk_idx;
 };
 
-// K-major operand rows of 64 bytes, 64-byte swizzle, 8-row groups 512 bytes apart
-__device__ __forceinline__ uint64_t umma_desc_sw64(uint32_t saddr) {
-  return static_cast<uint64_t>((saddr & 0x3FFFF) >> 4) | (1ull << 16) | (32ull << 32) | (1ull << 46) | (4ull << 61);
+// K-major operand rows of I8_KC bytes, swizzle of the same width, 8-row groups 8 * I8_KC bytes apart
+// (layout type 4 = 64-byte, 6 = 32-byte swizzle)
+__device__ __forceinline__ uint64_t umma_desc_k(uint32_t saddr) {
+  return static_cast<uint64_t>((saddr & 0x3FFFF) >> 4) | (1ull << 16) | (static_cast<uint64_t>(8 * I8_KC / 16) << 32) |
+         (1ull << 46) | (static_cast<uint64_t>(I8_KC == 64 ? 4 : 6) << 61);
 }
 // kind::i8: D = s32, A = B = signed 8 bit, both K-major, M = 128, N = 64
 constexpr uint32_t I8_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((64u >> 3) << 17) | ((128u >> 4) << 24);
@@ -104,7 +108,7 @@ __global__ void __launch_bounds__(192, 1) sweep_i8_kernel(const __grid_constant_
       uint32_t it = 0;
       for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
         for (int h = 0; h < nh; ++h)
-          for (int kc = 0; kc <= h; ++kc, ++it) {
+          for (int kc = 0; kc < (h + 1) * I8_CPH; ++kc, ++it) {
             const uint32_t s = it % I8_STAGES, ph = (it / I8_STAGES) & 1;
             mbar_wait(bar0 + 8 * (I8_STAGES + s), ph ^ 1);
             const uint32_t full = bar0 + 8 * s;
@@ -121,13 +125,13 @@ __global__ void __launch_bounds__(192, 1) sweep_i8_kernel(const __grid_constant_
         for (int h = 0; h < nh; ++h, ++acc_round) {
           mbar_wait(bar_acce, (acc_round & 1) ^ 1);        // the previous half-block has been drained
           asm volatile("tcgen05.fence::after_thread_sync;\n");
-          for (int kc = 0; kc <= h; ++kc, ++it) {
+          for (int kc = 0; kc < (h + 1) * I8_CPH; ++kc, ++it) {
             const uint32_t s = it % I8_STAGES, ph = (it / I8_STAGES) & 1;
             mbar_wait(bar0 + 8 * s, ph);
             asm volatile("tcgen05.fence::after_thread_sync;\n");
             const uint32_t a0 = s0 + s * I8_STAGE;
             // descriptors differ only in the 16-byte-unit address field: + slice * size / 16, + 2 for the second k-step
-            const uint64_t da0 = umma_desc_sw64(a0), db0 = umma_desc_sw64(a0 + I8_A_BYTES);
+            const uint64_t da0 = umma_desc_k(a0), db0 = umma_desc_k(a0 + I8_A_BYTES);
             const uint32_t fresh = (kc != 0);                // the first chunk of a half-block overwrites the accumulators
 #pragma unroll
             for (int t = 0; t < I8_S; ++t) {
@@ -137,7 +141,7 @@ __global__ void __launch_bounds__(192, 1) sweep_i8_kernel(const __grid_constant_
                 const uint64_t db = db0 + static_cast<uint64_t>(t * (I8_B_SLICE / 16));
                 // class sl + t is first touched by the pair (sl, 0)
                 umma_i8(tmem + (sl + t) * 64, da, db, t == 0 ? fresh : 1u);
-                umma_i8(tmem + (sl + t) * 64, da + 2, db + 2, 1u);
+                if (I8_KSTEPS == 2) umma_i8(tmem + (sl + t) * 64, da + 2, db + 2, 1u);
               }
             }
             umma_commit(bar0 + 8 * (I8_STAGES + s));       // stage free once these instructions have read it

@@ -197,7 +197,7 @@ __global__ void __launch_bounds__(512, 1) sweep_i8f_kernel(const __grid_constant
       const uint32_t b = t & 1, use = t >> 1;
       if (use > 0) mbar_wait(bar_free + 8 * b, (use - 1) & 1);       // the tile that used this buffer is consumed
       signed char* rows = p.planes + static_cast<size_t>(buf_row0 + 128 * b) * p.npad;
-      build_tile(p, tile, rows, meanbuf + buf_row0 + 128 * b, sm, tid);
+      if (!(p.dbg & 128) || t < 2) build_tile(p, tile, rows, meanbuf + buf_row0 + 128 * b, sm, tid);
       __threadfence();
       asm volatile("fence.proxy.async;\n" ::: "memory");            // generic-proxy stores -> visible to TMA
       __syncwarp();
@@ -277,7 +277,7 @@ __global__ void __launch_bounds__(512, 1) sweep_i8f_kernel(const __grid_constant
         const uint32_t b = t & 1, use = t >> 1;
         mbar_wait(bar_ready + 8 * b, use & 1);              // the tile's planes are complete and visible to TMA
         for (int h = 0; h < nh; ++h)
-          for (int kc = 0; kc <= h; ++kc, ++it) {
+          for (int kc = 0; kc < (h + 1) * I8_CPH; ++kc, ++it) {
             const uint32_t s = it % I8_STAGES, ph = (it / I8_STAGES) & 1;
             mbar_wait(bar0 + 8 * (I8_STAGES + s), ph ^ 1);
             const uint32_t full = bar0 + 8 * s;
@@ -293,12 +293,12 @@ __global__ void __launch_bounds__(512, 1) sweep_i8f_kernel(const __grid_constant
         for (int h = 0; h < nh; ++h, ++acc_round) {
           mbar_wait(bar_acce, (acc_round & 1) ^ 1);        // the previous half-block has been drained
           asm volatile("tcgen05.fence::after_thread_sync;\n");
-          for (int kc = 0; kc <= h; ++kc, ++it) {
+          for (int kc = 0; kc < (h + 1) * I8_CPH; ++kc, ++it) {
             const uint32_t s = it % I8_STAGES, ph = (it / I8_STAGES) & 1;
             mbar_wait(bar0 + 8 * s, ph);
             asm volatile("tcgen05.fence::after_thread_sync;\n");
             const uint32_t a0 = s0 + s * I8_STAGE;
-            const uint64_t da0 = umma_desc_sw64(a0), db0 = umma_desc_sw64(a0 + I8_A_BYTES);
+            const uint64_t da0 = umma_desc_k(a0), db0 = umma_desc_k(a0 + I8_A_BYTES);
             const uint32_t fresh = (kc != 0);              // the first chunk of a half-block overwrites the accumulators
 #pragma unroll
             for (int tt = 0; tt < I8_S; ++tt) {
@@ -306,8 +306,9 @@ __global__ void __launch_bounds__(512, 1) sweep_i8f_kernel(const __grid_constant
               for (int sl = 0; sl + tt < I8_S; ++sl) {
                 const uint64_t da = da0 + static_cast<uint64_t>(sl * (I8_A_SLICE / 16));
                 const uint64_t db = db0 + static_cast<uint64_t>(tt * (I8_B_SLICE / 16));
+                if ((p.dbg & 64) && (sl + tt > 0 || kc > 0)) continue;
                 umma_i8(tmem + (sl + tt) * 64, da, db, tt == 0 ? fresh : 1u);
-                umma_i8(tmem + (sl + tt) * 64, da + 2, db + 2, 1u);
+                if (I8_KSTEPS == 2) umma_i8(tmem + (sl + tt) * 64, da + 2, db + 2, 1u);
               }
             }
             umma_commit(bar0 + 8 * (I8_STAGES + s));       // stage free once these instructions have read it

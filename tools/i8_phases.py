@@ -1,4 +1,4 @@
-"""Time split of the int8-sliced sweep: whole, without the digit stores, with trivial digits."""
+"""Time split of the fused int8-sliced sweep: whole, tensor instructions skipped (builder-bound), builders skipped."""
 import sys
 import numpy as np
 sys.path.insert(0, '.')
@@ -12,8 +12,8 @@ h.set_data(X, y, 1, 1.5)
 h.set_theta(1.2)
 xc = torch.rand(N, d, dtype=torch.float64, device='cuda')
 torch.cuda.synchronize()
-h.set_option('sweep_impl', 2)
-for dbg in (0, 16, 32):
+h.set_option('sweep_impl', 4)
+for dbg in (0, 64, 128, 64 | 128):
     h.set_option('sweep_dbg', dbg)
     ms = []
     for _ in range(3):
