@@ -8,7 +8,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 OUT = os.path.join(HERE, 'libplxbo.so')
 SOURCES = ['api.cu']
-HEADERS = ['mma_f64.cuh', 'tma_ring.cuh', 'gp_kernels.cuh', 'sweep.cuh', 'sweep_i8.cuh', 'sweep_i8f.cuh', 'append.cuh', 'refine.cuh', 'lbfgsb1d.h', os.path.join('..', '..', 'include', 'plxbo.h')]
+HEADERS = ['mma_f64.cuh', 'tma_ring.cuh', 'gp_kernels.cuh', 'sweep.cuh', 'sweep_i8.cuh', 'sweep_i8f.cuh', 'sweep_i8c.cuh', 'append.cuh', 'refine.cuh', 'lbfgsb1d.h', os.path.join('..', '..', 'include', 'plxbo.h')]
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
               '-shared', '-Xcompiler', '-fPIC']
 

@@ -3,7 +3,7 @@
 #include "../../include/plxbo.h"
 #include "refine.cuh"
 #include "append.cuh"
-#include "sweep_i8f.cuh"
+#include "sweep_i8c.cuh"
 
 #include <cstdio>
 #include <cstdlib>
@@ -62,6 +62,8 @@ struct plx_bo {
   signed char* d_zplanes = nullptr; size_t zplanes_cap = 0;     // [I8_S][npad][npad]
   double* d_zscale = nullptr; size_t zscale_cap = 0;
   double* d_i8mean = nullptr; size_t i8mean_cap = 0;
+  double* d_i8part = nullptr; size_t i8part_cap = 0;             // cooperative form: partial sums per group
+  unsigned* d_i8sync = nullptr; size_t i8sync_cap = 0;           //                   counters per group
   CUtensorMap tmA8, tmB8;
   long long i8_rows = 0; int i8_npad = 0;
   bool i8_state_valid = false;
@@ -202,7 +204,7 @@ extern "C" int plx_bo_create(int device, plx_bo_handle* out) {
   h->encode = reinterpret_cast<EncodeTiledFn>(fn);
   if (const char* e = std::getenv("PLX_BO_SWEEP_IMPL")) {       // A/B switch for measurements; see plx_bo_set_option
     const int v = std::atoi(e);
-    if (v >= 0 && v <= 4) h->sweep_impl = v;
+    if (v >= 0 && v <= 5) h->sweep_impl = v;
   }
   // opt in to large dynamic shared memory once
   cudaFuncSetAttribute(potf2_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, POTF_SMEM);
@@ -215,6 +217,7 @@ extern "C" int plx_bo_create(int device, plx_bo_handle* out) {
   cudaFuncSetAttribute(sweep_simple_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SWEEP_SIMPLE_SMEM);
   cudaFuncSetAttribute(sweep_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, I8_SMEM);
   cudaFuncSetAttribute(sweep_i8f_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, I8F_SMEM);
+  cudaFuncSetAttribute(sweep_i8c_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, I8F_SMEM);
   cudaFuncSetAttribute(kstar_slices_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, KSL_SMEM);
   if (cudaGetLastError() != cudaSuccess) return bail("cudaFuncSetAttribute failed (is the library built for this GPU?)");
   if (cudaMalloc(&h->d_blk_val, sizeof(double) * 1024) != cudaSuccess ||
@@ -235,7 +238,7 @@ extern "C" void plx_bo_destroy(plx_bo_handle h) {
                   h->d_blk_val, h->d_blk_idx, h->d_best_val, h->d_best_idx, h->dcand[0], h->dcand[1],
                   h->d_out[0], h->d_out[1], h->d_out[2], h->rf_kv, h->rf_kp, h->rf_v, h->rf_w, h->rf_vec,
                   h->rf_bounds, h->rf_val, h->rf_grad, h->rf_sc, h->rf_active, h->d_resident, h->d_misc, h->d_app,
-                  h->d_kplanes, h->d_zplanes, h->d_zscale, h->d_i8mean};
+                  h->d_kplanes, h->d_zplanes, h->d_zscale, h->d_i8mean, h->d_i8part, h->d_i8sync};
   for (void* p : ptrs) if (p) cudaFree(p);
   for (int i = 0; i < 2; ++i) { if (h->ev_copy[i]) cudaEventDestroy(h->ev_copy[i]); if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]); }
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
@@ -253,7 +256,7 @@ extern "C" int plx_bo_set_stream(plx_bo_handle h, void* stream) {
 
 extern "C" int plx_bo_set_option(plx_bo_handle h, const char* name, long long value) {
   if (!h || !name) return PLX_ERR_INVALID;
-  if (std::strcmp(name, "sweep_impl") == 0 && value >= 0 && value <= 4) { h->sweep_impl = static_cast<int>(value); return PLX_OK; }
+  if (std::strcmp(name, "sweep_impl") == 0 && value >= 0 && value <= 5) { h->sweep_impl = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "lml_batch_limit") == 0 && value >= 0) { h->lml_batch_limit = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "sweep_dbg") == 0) { h->sweep_dbg = static_cast<int>(value); return PLX_OK; }
   return fail(h, PLX_ERR_INVALID, std::string("unknown option or value: ") + name);
@@ -668,6 +671,27 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     h->i8_state_valid = true;
   }
   if (e0) CK(cudaEventRecord(e0, st));
+  if (h->sweep_impl == 5) {
+    // cooperative form: groups of four CTAs share a candidate tile so that the planes in flight stay in L2
+    const int max_groups = h->num_sms / I8C_R;
+    const int groups = static_cast<int>(std::min<long long>((p.N + 127) / 128, max_groups));
+    if ((r = ensure(h, h->d_i8part, h->i8part_cap, static_cast<size_t>(max_groups) * 2 * I8C_R * 256)) != PLX_OK) return r;
+    if ((r = ensure(h, h->d_i8sync, h->i8sync_cap, static_cast<size_t>(max_groups) * 8)) != PLX_OK) return r;
+    CK(cudaMemsetAsync(h->d_i8sync, 0, sizeof(unsigned) * max_groups * 8, st));
+    SweepParams q = p;
+    q.dbg = 0; q.planes = h->d_kplanes; q.plane_stride = static_cast<size_t>(rows) * npad;
+    I8Params ip;
+    ip.N = p.N; ip.idx_base = p.idx_base; ip.n = p.n; ip.zscale = h->d_zscale; ip.mean = nullptr;
+    ip.acq = p.acq; ip.kappa = p.kappa; ip.eps = p.eps; ip.y_max = p.y_max;
+    ip.out_mean = p.out_mean; ip.out_std = p.out_std; ip.out_acq = p.out_acq;
+    ip.blk_val = h->d_blk_val; ip.blk_idx = h->d_blk_idx;
+    sweep_i8c_kernel<<<groups * I8C_R, 512, I8F_SMEM, st>>>(h->tmA8, h->tmB8, q, ip, h->d_i8part, h->d_i8sync);
+    LAUNCH_CHECK("sweep_i8c_kernel");
+    sweep_merge_kernel<<<1, 32, 0, st>>>(h->d_blk_val, h->d_blk_idx, groups * I8C_R, h->d_best_val, h->d_best_idx);
+    LAUNCH_CHECK("sweep_merge_kernel");
+    if (e1) CK(cudaEventRecord(e1, st));
+    return PLX_OK;
+  }
   if (h->sweep_impl != 2) {
     // fused form: one persistent launch, the planes of the next tile are built while the current one is contracted
     const int grid = static_cast<int>(std::min<long long>((p.N + 127) / 128, h->num_sms));
@@ -715,7 +739,7 @@ static int launch_sweep(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cudaEve
   if (grid <= 0) return PLX_OK;
   // 3 (default): the fused int8-sliced sweep from 256 observations up (measured break-even between 128 and 256),
   // FP64 DMMA below and for the general-nu Matern kernel, whose Bessel evaluation dominates anyway
-  const bool sliced = h->sweep_impl == 2 || h->sweep_impl == 4 || (h->sweep_impl == 3 && p.n >= 256);
+  const bool sliced = h->sweep_impl == 2 || h->sweep_impl >= 4 || (h->sweep_impl == 3 && p.n >= 256);
   if (sliced && p.kind != K_GEN) return launch_sweep_i8(h, p, e0, e1);
   if (e0) CK(cudaEventRecord(e0, h->stream));
   if (h->sweep_impl >= 1) {

@@ -75,8 +75,10 @@ __device__ __forceinline__ void builder_block(const SweepParams& p, double (&r2)
 }
 
 // Builder role for one tile: planes into `rows` (plane 0, first candidate row of the tile buffer), means into mean_out.
+// Only the 64-observation blocks jb0, jb0 + jbstep, ... are built (1, 0 = all of them; the cooperative kernel deals
+// the blocks to the CTAs of a group, and mean_out then receives this CTA's partial means).
 __device__ __forceinline__ void build_tile(const SweepParams& p, long long tile, signed char* rows, double* mean_out,
-                                           uint32_t sm, int tid) {
+                                           uint32_t sm, int tid, int jb0 = 0, int jbstep = 1) {
   const int tx = tid & 15, ty = tid >> 4;
   const long long c_base = tile * 128;
   const int nchunk_d = (p.d + 31) / 32;
@@ -93,8 +95,8 @@ __device__ __forceinline__ void build_tile(const SweepParams& p, long long tile,
       pre[r] = (q < dn) ? p.Xt[static_cast<size_t>(d0 + q) * p.npad + jb * 64 + j] : 0.0;
     }
   };
-  fetch(0, 0);
-  for (int jb = 0; jb < nblk; ++jb) {
+  if (jb0 < nblk) fetch(jb0, 0);
+  for (int jb = jb0; jb < nblk; jb += jbstep) {
     double r2[8][4];
 #pragma unroll
     for (int i = 0; i < 8; ++i)
@@ -108,7 +110,7 @@ __device__ __forceinline__ void build_tile(const SweepParams& p, long long tile,
         const int e = tid + 256 * r;
         sts64(sm + static_cast<uint32_t>((F_XS + (e >> 6) * F_XS_LD + (e & 63)) * 8), pre[r]);
       }
-      if (jb == 0 || nchunk_d > 1) {
+      if (jb == jb0 || nchunk_d > 1) {
         for (int e = tid; e < 128 * 32; e += 256) {
           const int c = e >> 5, q = e & 31;
           double v = 0.0;
@@ -119,7 +121,7 @@ __device__ __forceinline__ void build_tile(const SweepParams& p, long long tile,
       named_bar_sync(1, 256);
       {                                                       // prefetch the next (jb, dc)
         int njb = jb, ndc = dc + 1;
-        if (ndc == nchunk_d) { ndc = 0; ++njb; }
+        if (ndc == nchunk_d) { ndc = 0; njb += jbstep; }
         if (njb < nblk) fetch(njb, ndc);
       }
       const uint32_t cs = sm + static_cast<uint32_t>((F_CS + ty * 8) * 8);
