@@ -685,7 +685,14 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     ip.acq = p.acq; ip.kappa = p.kappa; ip.eps = p.eps; ip.y_max = p.y_max;
     ip.out_mean = p.out_mean; ip.out_std = p.out_std; ip.out_acq = p.out_acq;
     ip.blk_val = h->d_blk_val; ip.blk_idx = h->d_blk_idx;
-    sweep_i8c_kernel<<<groups * I8C_R, 512, I8F_SMEM, st>>>(h->tmA8, h->tmB8, q, ip, h->d_i8part, h->d_i8sync);
+    // cooperative launch: the runtime starts the grid only when all its CTAs can be resident at once, which the
+    // spin-waits between the CTAs of a group rely on (two such sweeps from different handles then run one after
+    // the other instead of starving each other)
+    {
+      void* args[] = {&h->tmA8, &h->tmB8, &q, &ip, &h->d_i8part, &h->d_i8sync};
+      CK(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(sweep_i8c_kernel), dim3(groups * I8C_R), dim3(512), args,
+                                     I8F_SMEM, st));
+    }
     LAUNCH_CHECK("sweep_i8c_kernel");
     sweep_merge_kernel<<<1, 32, 0, st>>>(h->d_blk_val, h->d_blk_idx, groups * I8C_R, h->d_best_val, h->d_best_idx);
     LAUNCH_CHECK("sweep_merge_kernel");

@@ -95,6 +95,9 @@ __global__ void __launch_bounds__(512, 1) sweep_i8c_kernel(const __grid_constant
     const uint32_t lane_base = static_cast<uint32_t>((warp - 8) * 32) << 16;
     for (long long tile = g; tile < ntiles; tile += groups, ++t) {
       const uint32_t b = t & 1, use = t >> 1;
+      // a CTA whose share of the half-blocks is empty (fewer than four of them) has no accumulators to wait for:
+      // tie it to the tile through its own builders, or it would run ahead and announce buffers free too early
+      mbar_wait(bar_ready + 8 * b, use & 1);
       double sumsq = 0.0;
       for (int h = 0; h < nh; ++h) {
         if (part_of(h) != r) continue;
