@@ -40,6 +40,7 @@ METRIC = 'acquisition evals/sec (FP64) at d=32,n_obs=2048'
 # and kstar_slices_kernel + sweep_i8_kernel (profiles/r01_ncu_sweep_i8_summary.csv, one 37 888-candidate chunk)
 DRAM_BYTES_PER_CANDIDATE = (18.701e9 + 2.490e9) / 151552
 DRAM_BYTES_PER_CANDIDATE_I8 = (9.846e9 + 0.006e9 + 0.011e9 + 0.567e9) / 37888
+DRAM_BYTES_PER_CANDIDATE_I8C = (2.622e9 + 2.196e9) / 151552       # sweep_i8c_kernel, same csv
 UNIT = 'evals/s'
 
 
@@ -313,7 +314,8 @@ def main():
     ap.add_argument('--candidates', type=int, default=1 << 24)
     ap.add_argument('--cpu-sample', type=int, default=1 << 15)
     ap.add_argument('--sweep-impl', type=int, default=3,
-                    help='3 = library default (fused int8-sliced sweep from 256 observations), 4 = fused int8-sliced, '
+                    help='3 = library default (cooperative int8-sliced sweep from 256 observations), 5 = the same forced, '
+                         '4 = fused int8-sliced (one CTA per tile), '
                          '2 = int8-sliced as two kernels, 1 = FP64 DMMA, 0 = plain-load cross-check')
     ap.add_argument('--skip-latency', action='store_true')
     args = ap.parse_args()
@@ -408,14 +410,16 @@ def main():
         fpe = flops_per_eval(N_OBS, D)
         achieved = fpe * n_local / (kernel_ms * 1e-3) / 1e12
         peak = measure_dgemm_tflops(torch, dev)
-        sliced = args.sweep_impl in (2, 4) or (args.sweep_impl == 3 and N_OBS >= 256)
+        sliced = args.sweep_impl in (2, 4, 5) or (args.sweep_impl == 3 and N_OBS >= 256)
         if sliced:
             nh = (N_OBS + 63) // 64                          # 64-row half-blocks of L^-1, triangular in 64-wide chunks
             i8_ops = 28 * 2.0 * 64 * 64 * nh * (nh + 1) / 2   # 28 digit-plane pairs, executed tensor ops per candidate
             i8_peak = h.measure_i8_peak()
             i8_achieved = i8_ops * n_local / (kernel_ms * 1e-3) / 1e12
             roof_kernel = ('kstar_slices_kernel + sweep_i8_kernel (alternating, chunks of %d candidates)' % (148 * 256)
-                           if args.sweep_impl == 2 else 'sweep_i8f_kernel (digit-plane builders + int8 contraction fused)')
+                           if args.sweep_impl == 2 else 'sweep_i8f_kernel (digit-plane builders + int8 contraction fused)'
+                           if args.sweep_impl == 4 or (args.sweep_impl == 3 and N_OBS < 1536) else
+                           'sweep_i8c_kernel (builders + int8 contraction fused, four CTAs per candidate tile)')
             roof_extra = {'int8': {'executed_tops': i8_achieved, 'peak_tops': i8_peak, 'frac': i8_achieved / i8_peak,
                                    'ops_per_eval': i8_ops,
                                    'peak_source': 'tcgen05.mma kind::i8 m128n128k32 issue rate measured in this run '
@@ -423,7 +427,8 @@ def main():
                                                   'measured ceiling is 0.69 of it (tools/i8_umma_n64.cu)'},
                           'note': 'frac is algorithmic FP64 flops over the measured DGEMM rate: the contraction runs as '
                                   'exact 7-bit slices on the int8 tensor cores, not on the FP64 pipe'}
-            traffic = DRAM_BYTES_PER_CANDIDATE_I8 * n_local
+            coop = args.sweep_impl == 5 or (args.sweep_impl == 3 and N_OBS >= 1536)
+            traffic = (DRAM_BYTES_PER_CANDIDATE_I8C if coop else DRAM_BYTES_PER_CANDIDATE_I8) * n_local
             traffic_note = ('DRAM bytes of the two kernels from profiles/ (ncu, one chunk), scaled per candidate: digit '
                             'planes of K* written once and re-read per 64-row half-block of L^-1')
         else:

@@ -47,9 +47,10 @@ const char* plx_version(void);
 /* Use the caller's CUDA stream (a cudaStream_t passed as void*); NULL restores the handle's own. */
 int plx_bo_set_stream(plx_bo_handle h, void* stream);
 
-/* Options: "sweep_impl" (3 [default] = fused int8-sliced sweep on the tcgen05 tensor cores from 256 observations
- * up and the FP64 DMMA kernel below; 4 = always the fused int8-sliced sweep; 2 = always int8-sliced as two
- * kernels per chunk; 1 = always FP64 DMMA with the TMA ring; 0 = plain-load cross-check); "sweep_dbg" (profiling
+/* Options: "sweep_impl" (3 [default] = int8-sliced sweep on the tcgen05 tensor cores from 256 observations up
+ * (fused form below 1536 observations, cooperative form from there) and the FP64 DMMA kernel below 256; 5 = always the cooperative int8-sliced sweep (four CTAs per
+ * candidate tile); 4 = the fused int8-sliced sweep (one CTA per tile); 2 = int8-sliced as two kernels per chunk;
+ * 1 = always FP64 DMMA with the TMA ring; 0 = plain-load cross-check); "sweep_dbg" (profiling
  * only: bit 0 skips the cross-kernel build after the first tile, bit 1 skips the tensor-pipe work);
  * "lml_batch_limit" (k > 0: at most k thetas per pass of plx_gp_lml / plx_gp_fit; 0 = as many as fit
  * in the free device memory, which is also what bounds a batch too large for one pass). */

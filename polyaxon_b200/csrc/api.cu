@@ -671,7 +671,7 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     h->i8_state_valid = true;
   }
   if (e0) CK(cudaEventRecord(e0, st));
-  if (h->sweep_impl == 5) {
+  if (h->sweep_impl == 5 || (h->sweep_impl == 3 && p.n >= 1536)) {
     // cooperative form: groups of four CTAs share a candidate tile so that the planes in flight stay in L2
     const int max_groups = h->num_sms / I8C_R;
     const int groups = static_cast<int>(std::min<long long>((p.N + 127) / 128, max_groups));
@@ -744,7 +744,8 @@ static int launch_sweep(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cudaEve
   const long long ntiles = (p.N + 127) / 128;
   const int grid = static_cast<int>(std::min<long long>(ntiles, h->num_sms));
   if (grid <= 0) return PLX_OK;
-  // 3 (default): the fused int8-sliced sweep from 256 observations up (measured break-even between 128 and 256),
+  // 3 (default): the int8-sliced sweep from 256 observations up (measured break-even between 128 and 256; fused
+  // form up to 1535 observations, cooperative form -- four CTAs per tile, planes L2-resident -- from 1536),
   // FP64 DMMA below and for the general-nu Matern kernel, whose Bessel evaluation dominates anyway
   const bool sliced = h->sweep_impl == 2 || h->sweep_impl >= 4 || (h->sweep_impl == 3 && p.n >= 256);
   if (sliced && p.kind != K_GEN) return launch_sweep_i8(h, p, e0, e1);
