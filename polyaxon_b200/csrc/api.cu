@@ -679,7 +679,7 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     if ((r = ensure(h, h->d_i8sync, h->i8sync_cap, static_cast<size_t>(max_groups) * 8)) != PLX_OK) return r;
     CK(cudaMemsetAsync(h->d_i8sync, 0, sizeof(unsigned) * max_groups * 8, st));
     SweepParams q = p;
-    q.dbg = 0; q.planes = h->d_kplanes; q.plane_stride = static_cast<size_t>(rows) * npad;
+    q.dbg = p.dbg & ~15; q.planes = h->d_kplanes; q.plane_stride = static_cast<size_t>(rows) * npad;
     I8Params ip;
     ip.N = p.N; ip.idx_base = p.idx_base; ip.n = p.n; ip.zscale = h->d_zscale; ip.mean = nullptr;
     ip.acq = p.acq; ip.kappa = p.kappa; ip.eps = p.eps; ip.y_max = p.y_max;

@@ -67,6 +67,61 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" :: "r"(bar) : "memory");
 }
 
+// tcgen05.ld of 16 consecutive 32-bit columns of this thread's TMEM lane (no wait)
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&u)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];\n"
+      : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]),
+        "=r"(u[8]), "=r"(u[9]), "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15])
+      : "r"(taddr));
+}
+
+// Drain of one finished half-block for one candidate (= TMEM lane): the I8_S class accumulators of 64 columns are
+// recombined in FP64, smallest class first, scaled by zs[.] and their squares added to sumsq.  The loads of several
+// classes are in flight together (one wait per batch: the round trip of tcgen05.ld, not its bandwidth, is what
+// the tensor pipe waits for while TMEM cannot be double-buffered), and the accumulators are handed back
+// (bar_acce) as soon as the last load has landed, before the arithmetic on it.
+__device__ __forceinline__ void drain_halfblock(uint32_t taddr, const double* __restrict__ zs, double& sumsq,
+                                                uint32_t bar_acce) {
+  constexpr int HI = (I8_S + 1) / 2;                     // classes I8_S-1 .. I8_S-HI first, then the rest
+#pragma unroll 1
+  for (int c0 = 0; c0 < 64; c0 += 16) {
+    double v[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = 0.0;
+    {
+      uint32_t u[HI][16];
+#pragma unroll
+      for (int k = 0; k < HI; ++k) tmem_ld16(taddr + (I8_S - 1 - k) * 64 + c0, u[k]);
+      asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+#pragma unroll
+      for (int k = 0; k < HI; ++k) {
+        const double w = __longlong_as_double(static_cast<long long>(1023 - 8 * (I8_S - 1 - k + 2)) << 52);   // 256^-(cls+2)
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = fma(static_cast<double>(static_cast<int>(u[k][i])), w, v[i]);
+      }
+    }
+    {
+      uint32_t u[I8_S - HI][16];
+#pragma unroll
+      for (int k = 0; k < I8_S - HI; ++k) tmem_ld16(taddr + (I8_S - HI - 1 - k) * 64 + c0, u[k]);
+      asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+      if (c0 == 48) {                                     // every column of every class has been read
+        asm volatile("tcgen05.fence::before_thread_sync;\n");
+        mbar_arrive(bar_acce);
+      }
+#pragma unroll
+      for (int k = 0; k < I8_S - HI; ++k) {
+        const double w = __longlong_as_double(static_cast<long long>(1023 - 8 * (I8_S - HI - 1 - k + 2)) << 52);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = fma(static_cast<double>(static_cast<int>(u[k][i])), w, v[i]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 16; ++i) { const double x = v[i] * zs[c0 + i]; sumsq = fma(x, x, sumsq); }
+  }
+}
+
 struct I8Tail {
   unsigned long long bars[2 * I8_STAGES + 2];       // full[ST], empty[ST], accumulators full, accumulators empty
   uint32_t tmem_base;
@@ -159,30 +214,7 @@ __global__ void __launch_bounds__(192, 1) sweep_i8_kernel(const __grid_constant_
       for (int h = 0; h < nh; ++h, ++acc_round) {
         mbar_wait(bar_accf, acc_round & 1);
         asm volatile("tcgen05.fence::after_thread_sync;\n");
-#pragma unroll 1
-        for (int c0 = 0; c0 < 64; c0 += 16) {
-          double v[16];
-#pragma unroll
-          for (int i = 0; i < 16; ++i) v[i] = 0.0;
-#pragma unroll
-          for (int cls = I8_S - 1; cls >= 0; --cls) {      // smallest contributions first
-            uint32_t u[16];
-            asm volatile(
-                "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];\n"
-                : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]),
-                  "=r"(u[8]), "=r"(u[9]), "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15])
-                : "r"(tmem + lane_base + cls * 64 + c0));
-            asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
-            const double w = __longlong_as_double(static_cast<long long>(1023 - 8 * (cls + 2)) << 52);   // 256^-(cls+2)
-#pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] = fma(static_cast<double>(static_cast<int>(u[i])), w, v[i]);
-          }
-          const double* zs = p.zscale + h * 64 + c0;
-#pragma unroll
-          for (int i = 0; i < 16; ++i) { const double x = v[i] * zs[i]; sumsq = fma(x, x, sumsq); }
-        }
-        asm volatile("tcgen05.fence::before_thread_sync;\n");
-        mbar_arrive(bar_acce);
+        drain_halfblock(tmem + lane_base, p.zscale + h * 64, sumsq, bar_acce);
       }
       const long long ci = tile * 128 + tid;
       if (ci < p.N) {

@@ -218,30 +218,7 @@ __global__ void __launch_bounds__(512, 1) sweep_i8f_kernel(const __grid_constant
       for (int h = 0; h < nh; ++h, ++acc_round) {
         mbar_wait(bar_accf, acc_round & 1);
         asm volatile("tcgen05.fence::after_thread_sync;\n");
-#pragma unroll 1
-        for (int c0 = 0; c0 < 64; c0 += 16) {
-          double v[16];
-#pragma unroll
-          for (int i = 0; i < 16; ++i) v[i] = 0.0;
-#pragma unroll
-          for (int cls = I8_S - 1; cls >= 0; --cls) {      // smallest contributions first
-            uint32_t u[16];
-            asm volatile(
-                "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];\n"
-                : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]),
-                  "=r"(u[8]), "=r"(u[9]), "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15])
-                : "r"(tmem + lane_base + cls * 64 + c0));
-            asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
-            const double w = __longlong_as_double(static_cast<long long>(1023 - 8 * (cls + 2)) << 52);   // 256^-(cls+2)
-#pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] = fma(static_cast<double>(static_cast<int>(u[i])), w, v[i]);
-          }
-          const double* zs = ip.zscale + h * 64 + c0;
-#pragma unroll
-          for (int i = 0; i < 16; ++i) { const double x = v[i] * zs[i]; sumsq = fma(x, x, sumsq); }
-        }
-        asm volatile("tcgen05.fence::before_thread_sync;\n");
-        mbar_arrive(bar_acce);
+        drain_halfblock(tmem + lane_base, ip.zscale + h * 64, sumsq, bar_acce);
       }
       // all tensor instructions of the tile have completed, hence all loads of its planes: the means were
       // written before the builders' arrival on `ready`, which the producer (and so this point) is ordered after

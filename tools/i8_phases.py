@@ -12,7 +12,7 @@ h.set_data(X, y, 1, 1.5)
 h.set_theta(1.2)
 xc = torch.rand(N, d, dtype=torch.float64, device='cuda')
 torch.cuda.synchronize()
-h.set_option('sweep_impl', 4)
+h.set_option('sweep_impl', int(sys.argv[1]) if len(sys.argv) > 1 else 5)
 for dbg in (0, 64, 128, 64 | 128):
     h.set_option('sweep_dbg', dbg)
     ms = []
