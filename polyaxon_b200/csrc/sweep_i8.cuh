@@ -63,6 +63,13 @@ __device__ __forceinline__ void umma_i8(uint32_t tmem_c, uint64_t da, uint64_t d
       "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}\n"
       :: "r"(tmem_c), "l"(da), "l"(db), "r"(I8_IDESC), "r"(accumulate), "r"(0u) : "memory");
 }
+// One lane of a converged warp (elect.sync): tensor instructions take their operands from uniform registers, and
+// issuing them from a branch the compiler knows to be single-lane avoids a per-instruction lane loop.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n.reg .pred P;\nelect.sync _|P, 0xffffffff;\nselp.u32 %0, 1, 0, P;\n}\n" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" :: "r"(bar) : "memory");
 }
@@ -173,8 +180,8 @@ __global__ void __launch_bounds__(192, 1) sweep_i8_kernel(const __grid_constant_
           }
     }
   } else if (warp == 5) {
-    // ===== tensor-instruction issuer =====
-    if (lane == 0) {
+    // ===== tensor-instruction issuer: the whole warp walks the loops, one elected lane issues =====
+    {
       uint32_t it = 0, acc_round = 0;
       for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
         for (int h = 0; h < nh; ++h, ++acc_round) {
@@ -188,6 +195,7 @@ __global__ void __launch_bounds__(192, 1) sweep_i8_kernel(const __grid_constant_
             // descriptors differ only in the 16-byte-unit address field: + slice * size / 16, + 2 for the second k-step
             const uint64_t da0 = umma_desc_k(a0), db0 = umma_desc_k(a0 + I8_A_BYTES);
             const uint32_t fresh = (kc != 0);                // the first chunk of a half-block overwrites the accumulators
+            if (elect_one()) {
 #pragma unroll
             for (int t = 0; t < I8_S; ++t) {
 #pragma unroll
@@ -200,8 +208,11 @@ __global__ void __launch_bounds__(192, 1) sweep_i8_kernel(const __grid_constant_
               }
             }
             umma_commit(bar0 + 8 * (I8_STAGES + s));       // stage free once these instructions have read it
+            }
+            __syncwarp();
           }
-          umma_commit(bar_accf);                           // accumulators of this half-block complete
+          if (elect_one()) umma_commit(bar_accf);          // accumulators of this half-block complete
+          __syncwarp();
         }
     }
   } else if (warp < 4) {

@@ -172,8 +172,8 @@ __global__ void __launch_bounds__(512, 1) sweep_i8c_kernel(const __grid_constant
           }
         }
       }
-    } else if (warp == 13 && lane == 0) {
-      // ===== tensor-instruction issuer =====
+    } else if (warp == 13) {
+      // ===== tensor-instruction issuer: the whole warp walks the loops, one elected lane issues =====
       uint32_t it = 0, acc_round = 0;
       for (long long tile = g; tile < ntiles; tile += groups)
         for (int h = 0; h < nh; ++h) {
@@ -188,6 +188,7 @@ __global__ void __launch_bounds__(512, 1) sweep_i8c_kernel(const __grid_constant
             const uint32_t a0 = s0 + s * I8_STAGE;
             const uint64_t da0 = umma_desc_k(a0), db0 = umma_desc_k(a0 + I8_A_BYTES);
             const uint32_t fresh = (kc != 0);              // the first chunk of a half-block overwrites the accumulators
+            if (elect_one()) {
 #pragma unroll
             for (int tt = 0; tt < I8_S; ++tt) {
 #pragma unroll
@@ -200,8 +201,11 @@ __global__ void __launch_bounds__(512, 1) sweep_i8c_kernel(const __grid_constant
               }
             }
             umma_commit(bar0 + 8 * (I8_STAGES + s));       // stage free once these instructions have read it
+            }
+            __syncwarp();
           }
-          umma_commit(bar_accf);                           // accumulators of this half-block complete
+          if (elect_one()) umma_commit(bar_accf);          // accumulators of this half-block complete
+          __syncwarp();
         }
     }
   }

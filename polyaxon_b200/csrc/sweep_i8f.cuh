@@ -265,8 +265,8 @@ __global__ void __launch_bounds__(512, 1) sweep_i8f_kernel(const __grid_constant
             tma_load_3d(s0 + s * I8_STAGE + I8_A_BYTES, &tmB, kc * I8_KC, h * 64, 0, full);
           }
       }
-    } else if (warp == 13 && lane == 0) {
-      // ===== tensor-instruction issuer =====
+    } else if (warp == 13) {
+      // ===== tensor-instruction issuer: the whole warp walks the loops, one elected lane issues =====
       uint32_t it = 0, acc_round = 0;
       for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
         for (int h = 0; h < nh; ++h, ++acc_round) {
@@ -279,6 +279,7 @@ __global__ void __launch_bounds__(512, 1) sweep_i8f_kernel(const __grid_constant
             const uint32_t a0 = s0 + s * I8_STAGE;
             const uint64_t da0 = umma_desc_k(a0), db0 = umma_desc_k(a0 + I8_A_BYTES);
             const uint32_t fresh = (kc != 0);              // the first chunk of a half-block overwrites the accumulators
+            if (elect_one()) {
 #pragma unroll
             for (int tt = 0; tt < I8_S; ++tt) {
 #pragma unroll
@@ -291,8 +292,11 @@ __global__ void __launch_bounds__(512, 1) sweep_i8f_kernel(const __grid_constant
               }
             }
             umma_commit(bar0 + 8 * (I8_STAGES + s));       // stage free once these instructions have read it
+            }
+            __syncwarp();
           }
-          umma_commit(bar_accf);                           // accumulators of this half-block complete
+          if (elect_one()) umma_commit(bar_accf);          // accumulators of this half-block complete
+          __syncwarp();
         }
     }
   }
