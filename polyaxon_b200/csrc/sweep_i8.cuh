@@ -1,5 +1,8 @@
-// Variant 2 of the acquisition sweep (opt-in, "sweep_impl" = 2): the variance contraction V = K* . Z^T on the
-// int8 tensor cores by exact slicing, instead of FP64 DMMA.
+// The int8-sliced acquisition sweep: the variance contraction V = K* . Z^T on the int8 tensor cores by exact
+// slicing, instead of FP64 DMMA.  This header holds the arithmetic shared by its three forms -- digit planes,
+// tensor-instruction and descriptor helpers, the accumulator drain -- and the two-kernel form ("sweep_impl" = 2);
+// sweep_i8f.cuh fuses the two kernels into one persistent CTA per SM (4), sweep_i8c.cuh lets four CTAs share a
+// candidate tile (5; the default from 1536 observations, the fused form from 256).
 //
 //   K*[c][j] = 4 * sum_s a_s[c][j] 256^-(s+1)                   a_s balanced 8-bit digits (K* in [0, 1], fixed exponent)
 //   Z[i][j]  = 2^f_i * sum_t b_t[i][j] 256^-(t+1)               f_i from the largest entry of row i of L^-1
@@ -11,15 +14,15 @@
 // chain (tools/ozaki_probe.cu measured 3.5e-16 relative to sum |K* Z| at n = 2048 for 8 x 7 bits, the same
 // 56 bits and the same truncation order 2^-47).  Reference arithmetic being reproduced: sklearn _gpr.py:460-481.
 //
-// Two kernels per chunk of candidates:
-//   kstar_slices_kernel  phase A of variant 1 (same distances, same kernel values, same posterior mean) writing
+// Two-kernel form, per chunk of candidates:
+//   kstar_slices_kernel  phase A of the DMMA variant (same distances, same kernel values, same posterior mean) writing
 //                        the S digit planes of K* (int8) instead of the FP64 tile;
 //   sweep_i8_kernel      persistent, 192 threads: warp 4 streams the digit planes of a 128-candidate tile and of a
 //                        64-row half-block of Z through a two-stage ring (one 3-D bulk tensor load per operand and
-//                        64-observation chunk, 64-byte swizzle), warp 5 issues the 72 tensor instructions per stage
+//                        64-observation chunk, 64-byte swizzle), warp 5 issues the 56 tensor instructions per stage
 //                        (28 digit-plane pairs x 2 k-steps) into 7 x 64 TMEM columns, warps 0-3 drain the accumulators of a
 //                        finished half-block (tcgen05.ld), recombine in FP64, scale, square and sum per candidate, and
-//                        finish with variance -> acquisition -> arg-max exactly as variant 1.
+//                        finish with variance -> acquisition -> arg-max exactly as the DMMA variant.
 #pragma once
 #include "sweep.cuh"
 
