@@ -224,9 +224,16 @@ REF10_Y = [2.3018131256103516, 2.302884340286255, 2.3071441650390625, 2.30346369
            2.3120572566986084, 0.7617478370666504]
 
 
-def main():
+def main(only=None):
     standin, opt_mod, _ = load_reference()
     thetas = [-2.0, -1.0, 0.0, 0.7, 1.5, 3.0]
+    if only:
+        real_run_case = run_case
+
+        def filtered(name, *args, **kw):
+            if name in only:
+                real_run_case(name, *args, **kw)
+        globals()['run_case'] = filtered
 
     # C1: d=2, Matern 2.5, UCB kappa=2.576, n=15 (5 initial + 10 iterations)
     c, m = synthetic_configs(15, 2)
@@ -256,6 +263,13 @@ def main():
     run_case('c3_d32_n512_m15_poi', standin, opt_mod,
              hp_config(standin, 32, 'matern', 1.5, 'poi', None, 0.0, 2, 4096, 2, 5),
              c, m, thetas, 1024)
+    # C3 at its real shape: d=32, n=2048, Matern 1.5, POI eps=0, 17 optimiser runs, 2^18 candidates swept by the
+    # reference's own single compute() call (K* is 2^18 x 2048 doubles = 4.3 GB; ~30 GB peak with sklearn's
+    # temporaries, ~10 minutes on 8 cores).  acquisition_function.py:88-92 at the headline size.
+    c, m = synthetic_configs(2048, 32)
+    run_case('c3_d32_n2048_m15_poi_full', standin, opt_mod,
+             hp_config(standin, 32, 'matern', 1.5, 'poi', None, 0.0, 16, 1 << 18, 3, 5),
+             c, m, thetas, 4096)
     # C5 member: d=16, n=512 would repeat C3's shape; use n=128, Matern 0.5 + RBF variants instead
     c, m = synthetic_configs(128, 16, seed=1240)
     run_case('c5_d16_n128_m05_ucb', standin, opt_mod,
@@ -300,4 +314,4 @@ def main():
 
 
 if __name__ == '__main__':
-    main()
+    main(only=set(sys.argv[1:]) or None)
