@@ -50,8 +50,11 @@ int plx_bo_set_stream(plx_bo_handle h, void* stream);
 /* Options: "sweep_impl" (3 [default] = int8-sliced sweep on the tcgen05 tensor cores from 256 observations up
  * (fused form below 1536 observations, cooperative form from there) and the FP64 DMMA kernel below 256; 5 = always the cooperative int8-sliced sweep (four CTAs per
  * candidate tile); 4 = the fused int8-sliced sweep (one CTA per tile); 2 = int8-sliced as two kernels per chunk;
- * 1 = always FP64 DMMA with the TMA ring; 0 = plain-load cross-check); "sweep_dbg" (profiling
- * only: bit 0 skips the cross-kernel build after the first tile, bit 1 skips the tensor-pipe work);
+ * 1 = always FP64 DMMA with the TMA ring; 0 = plain-load cross-check); "i8_operand" (0 [default] = the digit planes of
+ * the candidate tile reach the tensor core through tensor memory, 1 = both operands from shared memory; same
+ * results, kept for A/B timing);
+ * "fit_apply" (1 [default]: plx_gp_fit ends by building the posterior state at the best theta; 0: it returns the
+ * optimiser runs only -- a rank's share of a fit whose runs are dealt to several GPUs);
  * "lml_batch_limit" (k > 0: at most k thetas per pass of plx_gp_lml / plx_gp_fit; 0 = as many as fit
  * in the free device memory, which is also what bounds a batch too large for one pass). */
 int plx_bo_set_option(plx_bo_handle h, const char* name, long long value);
@@ -117,7 +120,16 @@ int plx_candidates_set(plx_bo_handle h, const double* Xc, long long N, int d);
  * receive the state after the draw so the host generator can be moved on.  pos must be even. */
 int plx_candidates_draw_mt19937(plx_bo_handle h, const unsigned* key, int pos, const double* low,
                                 const double* range, long long N, int d, unsigned* key_out, int* pos_out);
-/* Copy rows [first, first + count) of the resident matrix back to the host (verification). */
+/* The same draw restricted to rows [first, first + count) of that N x d matrix: the block a rank of a multi-GPU job
+ * sweeps (each rank calls it with the SAME key / pos / N and its own range).  The generator is not run through the
+ * rows before `first`: the device jumps to their end in O(log) steps (csrc/mt19937.cuh), so the cost is that of
+ * `count` rows, spread over up to two CTAs per SM.  Only the block is held; plx_acq_sweep_resident_range and
+ * plx_candidates_get take GLOBAL row numbers and refuse rows outside it.  key_out / pos_out are the state after the
+ * WHOLE matrix (identical on every rank), in numpy's own representation. */
+int plx_candidates_draw_mt19937_range(plx_bo_handle h, const unsigned* key, int pos, const double* low,
+                                      const double* range, long long N, int d, long long first, long long count,
+                                      unsigned* key_out, int* pos_out);
+/* Copy rows [first, first + count) (global row numbers, inside the resident block) back to the host. */
 int plx_candidates_get(plx_bo_handle h, double* out, long long first, long long count);
 int plx_acq_sweep_resident(plx_bo_handle h, long long idx_base, int acq, double kappa, double eps, double y_max,
                            double* best_value, long long* best_index, double* best_x);

@@ -40,6 +40,8 @@ SIGNATURES = {
     'plx_candidates_set': (c_int, [c_void_p, c_void_p, c_longlong, c_int]),
     'plx_candidates_draw_mt19937': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_longlong, c_int,
                                             c_void_p, POINTER(c_int)]),
+    'plx_candidates_draw_mt19937_range': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_longlong, c_int,
+                                                  c_longlong, c_longlong, c_void_p, POINTER(c_int)]),
     'plx_candidates_get': (c_int, [c_void_p, c_void_p, c_longlong, c_longlong]),
     'plx_acq_sweep_resident': (c_int, [c_void_p, c_longlong, c_int, c_double, c_double, c_double, _dp,
                                        POINTER(c_longlong), c_void_p]),
@@ -109,6 +111,7 @@ class Handle(object):
         self.device = int(device)
         self.n = self.d = 0
         self.resident_key = None
+        self.owner = None         # (id, fit count) of the DeviceGaussianProcess whose state this handle holds
         self.held = None          # host-side record of the last fit (DeviceGaussianProcess, PLX_BO_REFIT_EVERY)
         self.seed_cache = {}      # resident_key -> (x_seeds, generator state after the draws), UtilityFunction._warmup
 
@@ -140,6 +143,7 @@ class Handle(object):
             raise ValueError('X must be (n, d) and y (n,)')
         self.n, self.d = X.shape
         self.held = None
+        self.owner = None
         self._check(self.lib.plx_gp_set_data(self._h, _ptr(X), _ptr(y), self.n, self.d, int(kernel),
                                              float(nu), float(jitter)))
 
@@ -150,7 +154,10 @@ class Handle(object):
         self._check(self.lib.plx_gp_lml(self._h, _ptr(thetas), thetas.size, _ptr(out), _ptr(g)))
         return (out, g) if grad else out
 
-    def fit(self, theta0, theta_restarts=(), bounds=(np.log(1e-5), np.log(1e5))):
+    def fit(self, theta0, theta_restarts=(), bounds=(np.log(1e-5), np.log(1e5)), apply=True):
+        """All optimiser runs in lock step.  apply=False returns the runs only and leaves the posterior state
+        alone (a rank of a sharded fit: the state is built at the winner of all ranks' runs)."""
+        self.set_option('fit_apply', 1 if apply else 0)
         rs = _f64(np.atleast_1d(np.asarray(theta_restarts, dtype=np.float64)))
         per_run = np.empty((rs.size + 1, 4))
         th, lml = c_double(), c_double()
@@ -236,10 +243,12 @@ class Handle(object):
         self._check(self.lib.plx_candidates_set(self._h, _ptr(Xc), Xc.shape[0], Xc.shape[1]))
         self.resident_key = key
 
-    def candidates_draw(self, rng, low, high, N, key=None):
+    def candidates_draw(self, rng, low, high, N, key=None, first=0, count=None):
         """Draw rng.uniform(low, high, size=(N, d)) on the device (bit-identical to numpy's MT19937
-        stream) into the resident matrix and move `rng` past the draw.  Returns False -- nothing
-        drawn, nothing changed -- when the generator is not an MT19937 at an even position."""
+        stream) into the resident matrix and move `rng` past the WHOLE draw.  With first / count only
+        rows [first, first + count) are produced and held (a rank's block of a sharded sweep).  Returns
+        False -- nothing drawn, nothing changed -- when the generator is not an MT19937 at an even
+        position."""
         state = rng.get_state()
         if state[0] != 'MT19937' or int(state[2]) & 1:
             return False
@@ -249,15 +258,20 @@ class Handle(object):
         key_out = np.empty(624, dtype=np.uint32)
         pos_out = c_int()
         self.resident_key = None
-        self._check(self.lib.plx_candidates_draw_mt19937(self._h, _ptr(key_in), int(state[2]), _ptr(low),
-                                                         _ptr(rng_range), int(N), low.size, _ptr(key_out),
-                                                         ctypes.byref(pos_out)))
+        count = int(N) - int(first) if count is None else int(count)
+        self._check(self.lib.plx_candidates_draw_mt19937_range(self._h, _ptr(key_in), int(state[2]), _ptr(low),
+                                                               _ptr(rng_range), int(N), low.size, int(first), count,
+                                                               _ptr(key_out), ctypes.byref(pos_out)))
         rng.set_state((state[0], key_out, pos_out.value) + tuple(state[3:]))
         self.resident_key = key
         return True
 
-    def candidates_get(self, first, count, d):
-        out = np.empty((count, d))
+    def candidates_get(self, first, count, d, out=None):
+        """Rows [first, first + count) (global row numbers) of the resident block; `out` may be a
+        C-contiguous float64 array to fill (e.g. the numpy view of a pinned buffer)."""
+        if out is None:
+            out = np.empty((count, d))
+        assert out.dtype == np.float64 and out.flags.c_contiguous and out.size == count * d
         self._check(self.lib.plx_candidates_get(self._h, _ptr(out), int(first), int(count)))
         return out
 

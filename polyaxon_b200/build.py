@@ -8,7 +8,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 OUT = os.path.join(HERE, 'libplxbo.so')
 SOURCES = ['api.cu']
-HEADERS = ['mma_f64.cuh', 'tma_ring.cuh', 'gp_kernels.cuh', 'sweep.cuh', 'sweep_i8.cuh', 'sweep_i8f.cuh', 'sweep_i8c.cuh', 'append.cuh', 'refine.cuh', 'lbfgsb1d.h', os.path.join('..', '..', 'include', 'plxbo.h')]
+HEADERS = ['mma_f64.cuh', 'tma_ring.cuh', 'gp_kernels.cuh', 'sweep.cuh', 'sweep_i8.cuh', 'sweep_i8f.cuh', 'sweep_i8c.cuh', 'mt19937.cuh', 'mt19937_jump.inc', 'append.cuh', 'refine.cuh', 'lbfgsb1d.h', os.path.join('..', '..', 'include', 'plxbo.h')]
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
               '-shared', '-Xcompiler', '-fPIC']
 
@@ -21,11 +21,13 @@ def up_to_date():
     return all(os.path.getmtime(p) <= t for p in deps if os.path.exists(p))
 
 
-def build(force=False, verbose=False):
-    if not force and up_to_date():
+def build(force=False, verbose=False, profile=False):
+    """profile=True adds -DPLX_PROFILE: the work-skipping `sweep_dbg` switches that tools/*_phases.py use to time
+    parts of the sweep kernels.  They are compiled out of the normal build."""
+    if not force and not profile and up_to_date():
         return OUT
     nvcc = os.environ.get('NVCC', 'nvcc')
-    cmd = [nvcc] + NVCC_FLAGS + (['-Xptxas', '-v'] if verbose else []) + ['-o', OUT] + SOURCES
+    cmd = [nvcc] + NVCC_FLAGS + (['-DPLX_PROFILE'] if profile else []) + (['-Xptxas', '-v'] if verbose else []) + ['-o', OUT] + SOURCES
     res = subprocess.run(cmd, cwd=CSRC, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if res.returncode != 0:
         sys.stderr.write(res.stdout)
@@ -36,4 +38,4 @@ def build(force=False, verbose=False):
 
 
 if __name__ == '__main__':
-    print(build(force='--force' in sys.argv, verbose='-v' in sys.argv))
+    print(build(force='--force' in sys.argv, verbose='-v' in sys.argv, profile='--profile' in sys.argv))

@@ -4,6 +4,7 @@
 #include "refine.cuh"
 #include "append.cuh"
 #include "sweep_i8c.cuh"
+#include "mt19937.cuh"
 
 #include <cstdio>
 #include <cstdlib>
@@ -15,6 +16,10 @@ using namespace plx;
 
 namespace {
 std::string g_create_error;
+// Errors of the handle-less entry point plx_acq_sweep_noalloc: a pointer to a string literal (never freed, one
+// word), so two host threads failing at once cannot corrupt anything; plx_last_error(NULL) returns it while it is
+// newer than the last plx_bo_create.
+const char* volatile g_noalloc_error = nullptr;
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -75,11 +80,12 @@ struct plx_bo {
   double* d_out[3] = {nullptr, nullptr, nullptr}; size_t out_cap = 0;
   cudaEvent_t ev_copy[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
   std::vector<cudaEvent_t> ev_pool;
-  int sweep_impl = 3, sweep_dbg = 0, lml_batch_limit = 0;      // 3 = choose per GP state, see launch_sweep
+  int sweep_impl = 3, sweep_dbg = 0, lml_batch_limit = 0, i8_a_from_smem = 0, fit_apply = 1;      // 3 = choose per GP state, see launch_sweep
   double last_ms = 0.0; long long last_launches = 0;
 
   // resident candidate matrix (iteration-invariant for a seeded group)
-  double* d_resident = nullptr; size_t resident_cap = 0; long long resident_n = 0; int resident_d = 0;
+  double* d_resident = nullptr; size_t resident_cap = 0; long long resident_n = 0, resident_first = 0; int resident_d = 0;
+  //   rows [resident_first, resident_first + resident_n) of the group's candidate matrix (a rank of a multi-GPU job holds its slice)
 
   // small persistent scratch (generator state + bounds of the device draw; verification probe)
   double* d_misc = nullptr; size_t misc_cap = 0;
@@ -161,11 +167,13 @@ static MaternGen make_matern_gen(double nu) {
 
 extern "C" const char* plx_version(void) { return "plxbo 0.1 (sm_100a)"; }
 
-extern "C" const char* plx_last_error(plx_bo_handle h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+static const char* last_handleless_error();
+extern "C" const char* plx_last_error(plx_bo_handle h) { return h ? h->err.c_str() : last_handleless_error(); }
 
 extern "C" int plx_bo_create(int device, plx_bo_handle* out) {
   if (!out) return PLX_ERR_INVALID;
   *out = nullptr;
+  g_noalloc_error = nullptr;               // plx_last_error(NULL) now reports this call
   int count = 0;
   cudaError_t e = cudaGetDeviceCount(&count);
   if (e != cudaSuccess || count == 0) {
@@ -219,6 +227,8 @@ extern "C" int plx_bo_create(int device, plx_bo_handle* out) {
   cudaFuncSetAttribute(sweep_i8f_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, I8F_SMEM);
   cudaFuncSetAttribute(sweep_i8c_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, I8F_SMEM);
   cudaFuncSetAttribute(kstar_slices_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, KSL_SMEM);
+  cudaFuncSetAttribute(mt19937_draw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                       static_cast<int>(sizeof(unsigned) * MT_SEQ + sizeof(double) * 2 * 2048));
   if (cudaGetLastError() != cudaSuccess) return bail("cudaFuncSetAttribute failed (is the library built for this GPU?)");
   if (cudaMalloc(&h->d_blk_val, sizeof(double) * 1024) != cudaSuccess ||
       cudaMalloc(&h->d_blk_idx, sizeof(long long) * 1024) != cudaSuccess ||
@@ -258,7 +268,11 @@ extern "C" int plx_bo_set_option(plx_bo_handle h, const char* name, long long va
   if (!h || !name) return PLX_ERR_INVALID;
   if (std::strcmp(name, "sweep_impl") == 0 && value >= 0 && value <= 5) { h->sweep_impl = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "lml_batch_limit") == 0 && value >= 0) { h->lml_batch_limit = static_cast<int>(value); return PLX_OK; }
+  if (std::strcmp(name, "fit_apply") == 0 && (value == 0 || value == 1)) { h->fit_apply = static_cast<int>(value); return PLX_OK; }
+  if (std::strcmp(name, "i8_operand") == 0 && (value == 0 || value == 1)) { h->i8_a_from_smem = static_cast<int>(value); return PLX_OK; }
+#ifdef PLX_PROFILE
   if (std::strcmp(name, "sweep_dbg") == 0) { h->sweep_dbg = static_cast<int>(value); return PLX_OK; }
+#endif
   return fail(h, PLX_ERR_INVALID, std::string("unknown option or value: ") + name);
 }
 
@@ -522,31 +536,21 @@ extern "C" int plx_gp_append(plx_bo_handle h, const double* x_new, double y_new)
   CK(cudaSetDevice(h->device));
   cudaStream_t st = h->stream;
   const int n0 = h->n, d = h->d, npad = h->npad;
-  if (n0 == npad) {
-    // the padded storage is full: rebuild at the next padding step from the device copy of the data
-    std::vector<double> X(static_cast<size_t>(n0 + 1) * d), y(n0 + 1);
-    CK(cudaMemcpyAsync(X.data(), h->dX, sizeof(double) * n0 * d, cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpyAsync(y.data(), h->dy, sizeof(double) * n0, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    std::memcpy(X.data() + static_cast<size_t>(n0) * d, x_new, sizeof(double) * d);
-    y[n0] = y_new;
-    const double theta = h->theta;
-    const int r = plx_gp_set_data(h, X.data(), y.data(), n0 + 1, d, h->kernel_id, h->nu, h->jitter);
-    return r != PLX_OK ? r : plx_gp_set_theta(h, theta);
-  }
   int r;
   if (h->x_cap < static_cast<size_t>(n0 + 1) * d) {       // grow the observation matrix, keeping its rows
     double* nx = nullptr;
-    const size_t cap = static_cast<size_t>(npad) * d;
+    const size_t cap = static_cast<size_t>(npad + 128) * d;
     CK(cudaMalloc(reinterpret_cast<void**>(&nx), cap * sizeof(double)));
     CK(cudaMemcpyAsync(nx, h->dX, sizeof(double) * n0 * d, cudaMemcpyDeviceToDevice, st));
     CK(cudaStreamSynchronize(st));
     CK(cudaFree(h->dX));
     h->dX = nx; h->x_cap = cap;
   }
-  if ((r = ensure(h, h->d_app, h->app_cap, static_cast<size_t>(3) * npad + 8)) != PLX_OK) return r;
+  if ((r = ensure(h, h->d_app, h->app_cap, static_cast<size_t>(3) * (npad + 128) + 8)) != PLX_OK) return r;
   double *kv = h->d_app, *lv = kv + npad, *wv = lv + npad, *piv = wv + npad;
   const double ell = std::exp(h->theta);
+  // the bordered pivot first: k = k(X, x_new), l = L^-1 k, pivot^2 = 1 + jitter - l.l.  Only scratch (and the
+  // unused row n0 of the observation matrix) is written before it is known to be positive.
   CK(cudaMemcpyAsync(h->dX + static_cast<size_t>(n0) * d, x_new, sizeof(double) * d, cudaMemcpyHostToDevice, st));
   append_kvec_kernel<<<(n0 + 255) / 256, 256, 0, st>>>(h->dX, n0, d, ell, h->kind, h->mg, kv);
   LAUNCH_CHECK("append_kvec_kernel");
@@ -560,6 +564,19 @@ extern "C" int plx_gp_append(plx_bo_handle h, const double* x_new, double y_new)
   if (!(lam2 > 0.0))       // nothing of the state has been touched yet
     return fail(h, PLX_ERR_NOT_PD, "gp_append: the extended kernel matrix is not positive definite (pivot^2 = " +
                                        std::to_string(lam2) + ")");
+  if (n0 == npad) {
+    // the padded storage is full: rebuild at the next padding step from the device copy of the data (the pivot
+    // above says the extended matrix is positive definite, so the rebuild does not fail on that account)
+    std::vector<double> X(static_cast<size_t>(n0 + 1) * d), y(n0 + 1);
+    CK(cudaMemcpyAsync(X.data(), h->dX, sizeof(double) * n0 * d, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(y.data(), h->dy, sizeof(double) * n0, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    std::memcpy(X.data() + static_cast<size_t>(n0) * d, x_new, sizeof(double) * d);
+    y[n0] = y_new;
+    const double theta = h->theta;
+    r = plx_gp_set_data(h, X.data(), y.data(), n0 + 1, d, h->kernel_id, h->nu, h->jitter);
+    return r != PLX_OK ? r : plx_gp_set_theta(h, theta);
+  }
   const double lam = std::sqrt(lam2);
   // Z row n0 <- -(l^T Z) / lambda, written in place (only rows < n0 are read), then the diagonal
   trmv_lower_t_kernel<<<(n0 + 31) / 32, 256, 0, st>>>(h->dZ, npad, n0, lv, -1.0 / lam,
@@ -618,6 +635,7 @@ extern "C" int plx_gp_fit(plx_bo_handle h, double theta0, const double* theta_re
     }
   if (theta_star) *theta_star = runs[best].x;
   if (lml_star) *lml_star = -runs[best].f;
+  if (!h->fit_apply) return PLX_OK;       // runs only (a rank's share of a sharded fit)
   return plx_gp_set_theta(h, runs[best].x);
 }
 
@@ -684,7 +702,7 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     ip.N = p.N; ip.idx_base = p.idx_base; ip.n = p.n; ip.zscale = h->d_zscale; ip.mean = nullptr;
     ip.acq = p.acq; ip.kappa = p.kappa; ip.eps = p.eps; ip.y_max = p.y_max;
     ip.out_mean = p.out_mean; ip.out_std = p.out_std; ip.out_acq = p.out_acq;
-    ip.blk_val = h->d_blk_val; ip.blk_idx = h->d_blk_idx;
+    ip.blk_val = h->d_blk_val; ip.blk_idx = h->d_blk_idx; ip.a_from_smem = h->i8_a_from_smem;
     // cooperative launch: the runtime starts the grid only when all its CTAs can be resident at once, which the
     // spin-waits between the CTAs of a group rely on (two such sweeps from different handles then run one after
     // the other instead of starving each other)
@@ -708,7 +726,7 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     ip.N = p.N; ip.idx_base = p.idx_base; ip.n = p.n; ip.zscale = h->d_zscale; ip.mean = nullptr;
     ip.acq = p.acq; ip.kappa = p.kappa; ip.eps = p.eps; ip.y_max = p.y_max;
     ip.out_mean = p.out_mean; ip.out_std = p.out_std; ip.out_acq = p.out_acq;
-    ip.blk_val = h->d_blk_val; ip.blk_idx = h->d_blk_idx;
+    ip.blk_val = h->d_blk_val; ip.blk_idx = h->d_blk_idx; ip.a_from_smem = h->i8_a_from_smem;
     sweep_i8f_kernel<<<grid, 512, I8F_SMEM, st>>>(h->tmA8, h->tmB8, q, ip, h->d_i8mean);
     LAUNCH_CHECK("sweep_i8f_kernel");
     sweep_merge_kernel<<<1, 32, 0, st>>>(h->d_blk_val, h->d_blk_idx, grid, h->d_best_val, h->d_best_idx);
@@ -730,7 +748,7 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     ip.out_mean = p.out_mean ? p.out_mean + base : nullptr;
     ip.out_std = p.out_std ? p.out_std + base : nullptr;
     ip.out_acq = p.out_acq ? p.out_acq + base : nullptr;
-    ip.blk_val = h->d_blk_val; ip.blk_idx = h->d_blk_idx;
+    ip.blk_val = h->d_blk_val; ip.blk_idx = h->d_blk_idx; ip.a_from_smem = h->i8_a_from_smem;
     sweep_i8_kernel<<<grid, 192, I8_SMEM, st>>>(h->tmA8, h->tmB8, ip);
     LAUNCH_CHECK("sweep_i8_kernel");
     sweep_merge_kernel<<<1, 32, 0, st>>>(h->d_blk_val, h->d_blk_idx, grid, h->d_best_val, h->d_best_idx);
@@ -879,21 +897,25 @@ extern "C" int plx_candidates_set(plx_bo_handle h, const double* Xc, long long N
   if ((r = ensure(h, h->d_resident, h->resident_cap, static_cast<size_t>(std::max<long long>(N, 1)) * d)) != PLX_OK) return r;
   if (N > 0) CK(cudaMemcpyAsync(h->d_resident, Xc, sizeof(double) * N * d, cudaMemcpyHostToDevice, h->stream));
   CK(cudaStreamSynchronize(h->stream));
-  h->resident_n = N; h->resident_d = d;
+  h->resident_n = N; h->resident_first = 0; h->resident_d = d;
   return PLX_OK;
 }
 
-extern "C" int plx_candidates_draw_mt19937(plx_bo_handle h, const unsigned* key, int pos, const double* low,
-                                           const double* range, long long N, int d, unsigned* key_out, int* pos_out) {
-  if (!h || !key || !low || !range || !key_out || !pos_out || N < 0 || d <= 0 || pos < 0 || pos > 624)
+extern "C" int plx_candidates_draw_mt19937_range(plx_bo_handle h, const unsigned* key, int pos, const double* low,
+                                                 const double* range, long long N, int d, long long first,
+                                                 long long count, unsigned* key_out, int* pos_out) {
+  if (!h || !key || !low || !range || !key_out || !pos_out || N < 0 || d <= 0 || pos < 0 || pos > 624 || first < 0 ||
+      count < 0 || first + count > N)
     return h ? fail(h, PLX_ERR_INVALID, "candidates_draw_mt19937: bad arguments") : PLX_ERR_INVALID;
   if (pos & 1) return fail(h, PLX_ERR_UNSUPPORTED, "candidates_draw_mt19937: odd stream position (draw on the host instead)");
   if (d > 2048) return fail(h, PLX_ERR_UNSUPPORTED, "candidates_draw_mt19937: d exceeds 2048");
+  if (static_cast<double>(N) * d * 2.0 + 1248.0 >= std::ldexp(1.0, MT_JUMP_KMAX + 1))
+    return fail(h, PLX_ERR_UNSUPPORTED, "candidates_draw_mt19937: N * d beyond the jump table (2^40 values)");
   CK(cudaSetDevice(h->device));
-  h->resident_n = 0;
+  h->resident_n = 0; h->resident_first = 0;
   int r;
-  if ((r = ensure(h, h->d_resident, h->resident_cap, static_cast<size_t>(std::max<long long>(N, 1)) * d)) != PLX_OK) return r;
-  // scratch layout (doubles): [0, 2d) low | range, then 1248 words of generator state, then the position
+  if ((r = ensure(h, h->d_resident, h->resident_cap, static_cast<size_t>(std::max<long long>(count, 1)) * d)) != PLX_OK) return r;
+  // scratch layout (doubles): [0, 2d) low | range, then 1248 words of generator state (in | out), then the position
   if ((r = ensure(h, h->d_misc, h->misc_cap, static_cast<size_t>(2 * d) + 640)) != PLX_OK) return r;
   double* d_lr = h->d_misc;
   unsigned* d_key = reinterpret_cast<unsigned*>(h->d_misc + 2 * d);
@@ -901,21 +923,37 @@ extern "C" int plx_candidates_draw_mt19937(plx_bo_handle h, const unsigned* key,
   CK(cudaMemcpyAsync(d_key, key, sizeof(unsigned) * 624, cudaMemcpyHostToDevice, h->stream));
   CK(cudaMemcpyAsync(d_lr, low, sizeof(double) * d, cudaMemcpyHostToDevice, h->stream));
   CK(cudaMemcpyAsync(d_lr + d, range, sizeof(double) * d, cudaMemcpyHostToDevice, h->stream));
-  mt19937_uniform_kernel<<<1, 512, sizeof(double) * 2 * d, h->stream>>>(d_key, pos, d_lr, d_lr + d, d, N * d,
-                                                                       h->d_resident, d_key + 624, d_pos);
-  LAUNCH_CHECK("mt19937_uniform_kernel");
+  // One CTA per chunk of rows, two CTAs per SM.  A chunk pays up to ~1 ms for its jump, so short draws (below ~4 M
+  // stream words per extra CTA) stay on fewer CTAs; the first chunk of a draw that starts at row 0 needs no jump.
+  const long long words = 2 * count * d;
+  long long chunks = std::min<long long>(2LL * h->num_sms, std::max<long long>(1, words >> 22));
+  chunks = std::max<long long>(1, std::min(chunks, count));
+  MtDrawParams mp;
+  mp.key = d_key; mp.pos = pos; mp.low = d_lr; mp.range = d_lr + d; mp.d = d;
+  mp.first_row = first; mp.rows = count; mp.rows_per_cta = (count + chunks - 1) / chunks;
+  mp.out = h->d_resident; mp.total_words = pos + 2 * N * d;
+  mp.key_out = d_key + 624; mp.pos_out = d_pos;
+  const size_t smem = sizeof(unsigned) * MT_SEQ + sizeof(double) * 2 * d;
+  mt19937_draw_kernel<<<static_cast<int>(chunks) + 1, MT_THREADS, smem, h->stream>>>(mp);
+  LAUNCH_CHECK("mt19937_draw_kernel");
   CK(cudaMemcpyAsync(key_out, d_key + 624, sizeof(unsigned) * 624, cudaMemcpyDeviceToHost, h->stream));
   CK(cudaMemcpyAsync(pos_out, d_pos, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
-  h->resident_n = N; h->resident_d = d;
+  h->resident_n = count; h->resident_first = first; h->resident_d = d;
   return PLX_OK;
+}
+
+extern "C" int plx_candidates_draw_mt19937(plx_bo_handle h, const unsigned* key, int pos, const double* low,
+                                           const double* range, long long N, int d, unsigned* key_out, int* pos_out) {
+  return plx_candidates_draw_mt19937_range(h, key, pos, low, range, N, d, 0, N, key_out, pos_out);
 }
 
 extern "C" int plx_candidates_get(plx_bo_handle h, double* out, long long first, long long count) {
   if (!h || !out || first < 0 || count < 0) return h ? fail(h, PLX_ERR_INVALID, "candidates_get: bad arguments") : PLX_ERR_INVALID;
-  if (first + count > h->resident_n) return fail(h, PLX_ERR_INVALID, "candidates_get: range beyond the resident matrix");
+  if (first < h->resident_first || first + count > h->resident_first + h->resident_n)
+    return fail(h, PLX_ERR_INVALID, "candidates_get: rows outside the resident block");
   CK(cudaSetDevice(h->device));
-  CK(cudaMemcpyAsync(out, h->d_resident + first * h->resident_d, sizeof(double) * count * h->resident_d,
+  CK(cudaMemcpyAsync(out, h->d_resident + (first - h->resident_first) * h->resident_d, sizeof(double) * count * h->resident_d,
                      cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
   return PLX_OK;
@@ -927,9 +965,9 @@ extern "C" int plx_acq_sweep_resident_range(plx_bo_handle h, long long first, lo
   if (!h) return PLX_ERR_INVALID;
   if (h->resident_d != h->d || (h->resident_n > 0 && !h->d_resident))
     return fail(h, PLX_ERR_STATE, "acq_sweep_resident_range: no resident candidates of this dimension");
-  if (first < 0 || count < 0 || first + count > h->resident_n)
-    return fail(h, PLX_ERR_INVALID, "acq_sweep_resident_range: rows outside the resident matrix");
-  return plx_acq_sweep_dev(h, h->d_resident + first * h->d, count, first, acq, kappa, eps, y_max, best_value,
+  if (first < h->resident_first || count < 0 || first + count > h->resident_first + h->resident_n)
+    return fail(h, PLX_ERR_INVALID, "acq_sweep_resident_range: rows outside the resident block");
+  return plx_acq_sweep_dev(h, h->d_resident + (first - h->resident_first) * h->d, count, first, acq, kappa, eps, y_max, best_value,
                            best_index, best_x);
 }
 
@@ -938,7 +976,7 @@ extern "C" int plx_acq_sweep_resident(plx_bo_handle h, long long idx_base, int a
   if (!h) return PLX_ERR_INVALID;
   if (h->resident_d != h->d || (h->resident_n > 0 && !h->d_resident))
     return fail(h, PLX_ERR_STATE, "acq_sweep_resident: no resident candidates of this dimension (call plx_candidates_set)");
-  return plx_acq_sweep_dev(h, h->d_resident, h->resident_n, idx_base, acq, kappa, eps, y_max, best_value, best_index, best_x);
+  return plx_acq_sweep_dev(h, h->d_resident, h->resident_n, idx_base + h->resident_first, acq, kappa, eps, y_max, best_value, best_index, best_x);
 }
 
 extern "C" int plx_kernel_values(plx_bo_handle h, int kernel, double nu, const double* r2, int n, double* out) {
@@ -1044,7 +1082,7 @@ static int launch_refine_round(plx_bo* h, const RefineParams& p) {
   LAUNCH_CHECK("refine_v_kernel");
   refine_w_kernel<<<(p.n + 31) / 32, 256, 0, st>>>(p);
   LAUNCH_CHECK("refine_w_kernel");
-  refine_step_kernel<<<p.S, 128, 0, st>>>(p);
+  refine_step_kernel<<<p.S, 128, sizeof(double) * 2 * p.d, st>>>(p);
   LAUNCH_CHECK("refine_step_kernel");
   return PLX_OK;
 }
@@ -1062,7 +1100,7 @@ extern "C" int plx_acq_value_grad(plx_bo_handle h, const double* Xp, int S, int 
                                   double y_max, double* values, double* grads) {
   if (!h || !Xp || S <= 0 || acq < 0 || acq > 2 || !values || !grads) return h ? fail(h, PLX_ERR_INVALID, "acq_value_grad: bad arguments") : PLX_ERR_INVALID;
   if (!h->have_state) return fail(h, PLX_ERR_STATE, "acq_value_grad: no posterior state");
-  if (h->d > RF_DMAX) return fail(h, PLX_ERR_UNSUPPORTED, "acq_value_grad: d exceeds 128");
+  if (h->d > RF_DMAX) return fail(h, PLX_ERR_UNSUPPORTED, "acq_value_grad: d exceeds 2048");
   CK(cudaSetDevice(h->device));
   int r;
   if ((r = ensure_refine(h, S)) != PLX_OK) return r;
@@ -1083,7 +1121,7 @@ extern "C" int plx_acq_refine(plx_bo_handle h, const double* seeds, int S, const
   if (!h || S < 0 || (S > 0 && (!seeds || !x_out || !acq_out || !success_out)) || !bounds || acq < 0 || acq > 2)
     return h ? fail(h, PLX_ERR_INVALID, "acq_refine: bad arguments") : PLX_ERR_INVALID;
   if (!h->have_state) return fail(h, PLX_ERR_STATE, "acq_refine: no posterior state");
-  if (h->d > RF_DMAX) return fail(h, PLX_ERR_UNSUPPORTED, "acq_refine: d exceeds 128");
+  if (h->d > RF_DMAX) return fail(h, PLX_ERR_UNSUPPORTED, "acq_refine: d exceeds 2048");
   h->last_refine_rounds = 0;
   if (S == 0) return PLX_OK;
   CK(cudaSetDevice(h->device));
@@ -1147,7 +1185,10 @@ extern "C" int plx_acq_refine(plx_bo_handle h, const double* seeds, int S, const
 // that first call before any stream capture.  Later calls issue three kernel launches and nothing
 // else.  All calls share the one array and it keeps the previous call's contents; every region a
 // call reads is rewritten by that call first, but two calls that overlap on the GPU (different
-// streams, or different host threads) race on it -- serialise them.
+// streams, or different host threads) race on it -- serialise them.  The one-time set-up itself takes no
+// lock either: two host threads making their FIRST call on a device at the same moment both run it and
+// store the same address (harmless, but make the first call from one thread).  The call leaves the
+// caller's current CUDA device as it found it.  A failure is described by plx_last_error(NULL).
 // ---------------------------------------------------------------------------------------------
 namespace {
 constexpr int NOALLOC_MAX_OBS = 256;
@@ -1176,7 +1217,12 @@ __global__ void noalloc_pack_kernel(const double* __restrict__ Linv, int n, int 
   if (blockIdx.x == 0 && threadIdx.x == 0) { *best_val = -INFINITY; *best_idx = 0x7fffffffffffffffLL; }
 }
 
-static int noalloc_fail(int code, const char* msg) { g_create_error = msg; return code; }
+static int noalloc_fail(int code, const char* msg) { g_noalloc_error = msg; return code; }
+
+static const char* last_handleless_error() {
+  const char* e = g_noalloc_error;
+  return e ? e : g_create_error.c_str();
+}
 
 extern "C" int plx_acq_sweep_noalloc(int device, void* stream, const double* Xc_dev, long long N,
                                      long long idx_base, const double* X_dev, const double* alpha_dev,
@@ -1192,6 +1238,12 @@ extern "C" int plx_acq_sweep_noalloc(int device, void* stream, const double* Xc_
     return noalloc_fail(PLX_ERR_INVALID, "sweep_noalloc: bad arguments");
   int kind;
   if (kernel_kind(kernel, nu, &kind) != PLX_OK) return noalloc_fail(PLX_ERR_UNSUPPORTED, "sweep_noalloc: unsupported kernel / nu");
+  // the caller's current device is put back on every path out of here
+  struct DeviceGuard {
+    int prev = -1;
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+  } guard;
+  if (cudaGetDevice(&guard.prev) != cudaSuccess) guard.prev = -1;
   if (cudaSetDevice(device) != cudaSuccess) return noalloc_fail(PLX_ERR_CUDA, "sweep_noalloc: cudaSetDevice failed");
   if (g_noalloc_ptr[device] == nullptr) {
     // once per device, with that device current
@@ -1212,7 +1264,7 @@ extern "C" int plx_acq_sweep_noalloc(int device, void* stream, const double* Xc_
   noalloc_pack_kernel<<<64, 256, 0, st>>>(Linv_dev, n, ldz, npad, Zpad, best_value_dev, best_index_dev);
   if (cudaGetLastError() != cudaSuccess) return noalloc_fail(PLX_ERR_CUDA, "sweep_noalloc: launch of the pack kernel failed");
   if (N == 0) return PLX_OK;                    // outputs hold (-inf, INT64_MAX): no candidate
-  SweepParams p;
+  SweepParams p{};
   p.Xc = Xc_dev; p.N = N; p.idx_base = idx_base;
   p.d = d; p.n = n; p.npad = npad; p.n16 = (n + 15) / 16 * 16;
   p.X = X_dev; p.Xt = nullptr; p.alpha = alpha_dev; p.Z = Zpad; p.ell = std::exp(theta);

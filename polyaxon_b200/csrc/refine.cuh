@@ -26,7 +26,7 @@
 namespace plx {
 
 constexpr int RF_M = 10;          // stored correction pairs
-constexpr int RF_DMAX = 128;      // largest encoded dimension the refinement supports
+constexpr int RF_DMAX = 2048;     // largest encoded dimension the refinement supports (per-seed gradient in shared memory: 16 d bytes)
 constexpr int RF_SB = 8;          // seeds per register block in the matrix-vector kernels
 
 // d k / d (r^2) for the closed-form kernels (r^2 = squared distance in length-scale units)
@@ -325,7 +325,9 @@ __device__ void rf_advance(const RefineParams& p, int s, RefineScalars& sc, int 
 __global__ void __launch_bounds__(128) refine_step_kernel(RefineParams p) {
   __shared__ double red_mu[4], red_s2[4];
   __shared__ double gsum[4][2][32];
-  __shared__ double gm[RF_DMAX], gv[RF_DMAX];
+  extern __shared__ double rf_grad_smem[];        // gm[d] | gv[d]
+  double* gm = rf_grad_smem;
+  double* gv = rf_grad_smem + p.d;
   __shared__ double sh_mu, sh_s2;
   const int s = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const bool eval_only = p.val_out != nullptr;

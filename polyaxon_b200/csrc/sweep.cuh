@@ -23,6 +23,14 @@ namespace plx {
 
 enum AcqKind { ACQ_UCB = 0, ACQ_EI = 1, ACQ_POI = 2 };
 
+// Work-skipping switches for phase timing exist only in builds made with -DPLX_PROFILE (python -m polyaxon_b200.build
+// --profile); in the shipped library the tests below are constant false and the option is refused.
+#ifdef PLX_PROFILE
+#define PLX_DBG(flags, bit) (((flags) & (bit)) != 0)
+#else
+#define PLX_DBG(flags, bit) false
+#endif
+
 struct SweepParams {
   const double* Xc;        // candidates [N][d], device
   long long N;             // candidates in this launch
@@ -41,7 +49,7 @@ struct SweepParams {
   size_t plane_stride;     //            bytes between planes
   double* out_mean; double* out_std; double* out_acq;   // optional per-candidate dumps [N]
   double* blk_val; long long* blk_idx;                  // per-CTA best
-  int dbg;                 // profiling only: bit 0 = build K* for the first tile only, bit 1 = skip the DMMA work
+  int dbg;                 // read only in PLX_PROFILE builds (tools/*_phases.py): bits skip parts of the work to time the rest
 };
 
 struct Best { double v; long long i; };
@@ -245,7 +253,7 @@ __device__ __forceinline__ void store_digits_q(signed char* dst, size_t plane_st
 
 // Kernel value k in [0, 1]: k = 4 * sum_s a_s 256^-(s+1) with the digits of round(k * 2^54) (|residual| <= 2^-55).
 __device__ __forceinline__ void store_digits(signed char* dst, size_t plane_stride, double k, int dbg = 0) {
-  if (dbg & 16) return;
+  if (PLX_DBG(dbg, 16)) return;
   store_digits_q(dst, plane_stride, __double2ll_rn(k * 18014398509481984.0));
 }
 
@@ -361,7 +369,7 @@ __device__ __forceinline__ void phase_a3(const SweepParams& p, long long tile, d
       const uint32_t cs = sm + static_cast<uint32_t>((PA_CS + ty * 8) * 8);
       const uint32_t xs = sm + static_cast<uint32_t>((PA_XS + tx) * 8);
 #pragma unroll 2
-      for (int q = 0; q < ((p.dbg & 8) ? 1 : dn); ++q) {
+      for (int q = 0; q < (PLX_DBG(p.dbg, 8) ? 1 : dn); ++q) {
         double cv[8], xv[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) { const double2 t2 = lds128(cs + (q * CS_LD + 2 * i) * 8); cv[2 * i] = t2.x; cv[2 * i + 1] = t2.y; }
@@ -380,7 +388,7 @@ __device__ __forceinline__ void phase_a3(const SweepParams& p, long long tile, d
       for (int j = 0; j < 4; ++j)
         sts64(sm + static_cast<uint32_t>((PA_R2 + (ty * 8 + i) * R2_LD + tx + 16 * j) * 8), r2[i][j]);
     named_bar_sync(1, 256);
-    if (!(p.dbg & 4)) switch (p.kind) {
+    if (!PLX_DBG(p.dbg, 4)) switch (p.kind) {
       case K_RBF: kern_rows<K_RBF, SL>(p, sm, Kslab, jb, warp, lane); break;
       case K_M05: kern_rows<K_M05, SL>(p, sm, Kslab, jb, warp, lane); break;
       case K_M15: kern_rows<K_M15, SL>(p, sm, Kslab, jb, warp, lane); break;
@@ -467,7 +475,7 @@ __global__ void __launch_bounds__(384, 1) sweep_tma_kernel(const __grid_constant
   const int wn = (warp >> 2) * 64;
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     // every TMA load of the previous tile has been waited for, so the stage memory is free
-    if (!(p.dbg & 1) || tile == blockIdx.x) phase_a3<false>(p, tile, Kslab, s0, tail->mean_s, tid);
+    if (!PLX_DBG(p.dbg, 1) || tile == blockIdx.x) phase_a3<false>(p, tile, Kslab, s0, tail->mean_s, tid);
     __threadfence();
     asm volatile("fence.proxy.async;\n" ::: "memory");     // generic-proxy stores -> visible to TMA
     __syncwarp();
@@ -482,7 +490,7 @@ __global__ void __launch_bounds__(384, 1) sweep_tma_kernel(const __grid_constant
         const uint32_t s = it % SWEEP_STAGES, ph = (it / SWEEP_STAGES) & 1;
         mbar_wait(bar0 + 8 * s, ph);
         const int skip = tri_skip(j0, ib, wn);
-        if (skip < 8 && !(p.dbg & 2)) mma_chunk_pf(acc, s0 + s * 2 * TILE_BYTES, s0 + s * 2 * TILE_BYTES + TILE_BYTES, warp, lane, skip);
+        if (skip < 8 && !PLX_DBG(p.dbg, 2)) mma_chunk_pf(acc, s0 + s * 2 * TILE_BYTES, s0 + s * 2 * TILE_BYTES + TILE_BYTES, warp, lane, skip);
         __syncwarp();
         if (lane == 0) mbar_arrive(bar0 + 8 * (SWEEP_STAGES + s));
       }
@@ -538,83 +546,6 @@ __global__ void scale_transpose_x_kernel(const double* __restrict__ X, int n, in
   const int j = blockIdx.x * blockDim.x + threadIdx.x, q = blockIdx.y;
   if (j >= npad) return;
   Xt[static_cast<size_t>(q) * npad + j] = (j < n) ? X[static_cast<size_t>(j) * d + q] / ell : 0.0;
-}
-
-// ------------------------------------------------------------------------------------------
-// Candidate draws on the device, bit-identical to the reference's generator.
-//
-// Reference: x_tries = random_generator.uniform(bounds[:, 0], bounds[:, 1], size=(n_warmup, d))
-// (acquisition_function.py:88-89) on numpy.random.RandomState, i.e. MT19937 with
-// next_double = ((w0 >> 5) * 2^26 + (w1 >> 6)) / 2^53 and x = low + (high - low) * next_double, values
-// filled candidate-major.  At C3 that is 1.07e9 32-bit outputs: ~4.5 s of host time per call.
-// The recurrence is sequential over 624-word blocks, but inside a block it splits into three
-// data-parallel sweeps (k < 227 depends on old words only; 227 <= k < 454 and 454 <= k < 624 on words
-// of the previous sweep), so one CTA regenerates a block in three barriers and tempers/scales 312
-// doubles per block with all threads.  Multiplication and addition are kept separate (no FMA), as in
-// numpy's C code.  Requires an even stream position (always true when only doubles were drawn).
-// ------------------------------------------------------------------------------------------
-__device__ __forceinline__ unsigned mt_twist(unsigned a, unsigned b) {
-  const unsigned y = (a & 0x80000000u) | (b & 0x7fffffffu);
-  return (y >> 1) ^ ((0u - (y & 1u)) & 0x9908b0dfu);
-}
-__device__ __forceinline__ unsigned mt_temper(unsigned y) {
-  y ^= (y >> 11);
-  y ^= (y << 7) & 0x9d2c5680u;
-  y ^= (y << 15) & 0xefc60000u;
-  y ^= (y >> 18);
-  return y;
-}
-
-__global__ void __launch_bounds__(512) mt19937_uniform_kernel(const unsigned* __restrict__ key_in, int pos,
-                                                              const double* __restrict__ low,
-                                                              const double* __restrict__ range, int d,
-                                                              long long count, double* __restrict__ out,
-                                                              unsigned* __restrict__ key_out, int* __restrict__ pos_out) {
-  // Threads 0-255 regenerate the NEXT 624-word block (three data-parallel sweeps, barriers among
-  // themselves only) while threads 256-511 temper, scale and store the doubles of the CURRENT block;
-  // one CTA-wide barrier per block.
-  __shared__ unsigned buf[2][624];
-  extern __shared__ double lr[];                 // low[d], range[d]
-  const int tid = threadIdx.x;
-  for (int i = tid; i < 624; i += 512) buf[0][i] = key_in[i];
-  for (int i = tid; i < d; i += 512) { lr[i] = low[i]; lr[d + i] = range[i]; }
-  __syncthreads();
-  int cur = 0, p = pos;
-  int qbase = 0;                                 // (doubles produced so far) mod d
-  long long produced = 0;
-  while (produced < count) {
-    const long long left = count - produced;
-    const int pairs = (p >= 624) ? 0 : static_cast<int>(min(static_cast<long long>((624 - p) / 2), left));
-    const bool more = left > pairs;              // another block will be needed after this one
-    if (tid < 256) {
-      if (more) {
-        const unsigned* o = buf[cur];
-        unsigned* nw = buf[cur ^ 1];
-        if (tid < 227) nw[tid] = o[tid + 397] ^ mt_twist(o[tid], o[tid + 1]);
-        named_bar_sync(3, 256);
-        if (tid < 227) { const int k = tid + 227; nw[k] = nw[k - 227] ^ mt_twist(o[k], o[k + 1]); }
-        named_bar_sync(3, 256);
-        if (tid < 169) { const int k = tid + 454; nw[k] = nw[k - 227] ^ mt_twist(o[k], o[k + 1]); }
-        named_bar_sync(3, 256);
-        if (tid == 0) nw[623] = nw[396] ^ mt_twist(o[623], nw[0]);
-      }
-    } else {
-      const unsigned* w = buf[cur];
-      for (int t = tid - 256; t < pairs; t += 256) {
-        const unsigned a = mt_temper(w[p + 2 * t]) >> 5, b = mt_temper(w[p + 2 * t + 1]) >> 6;
-        const double u = (a * 67108864.0 + b) / 9007199254740992.0;
-        const int q = (qbase + t) % d;
-        out[produced + t] = __dadd_rn(lr[q], __dmul_rn(lr[d + q], u));
-      }
-    }
-    produced += pairs;
-    qbase = (qbase + pairs) % d;
-    p += 2 * pairs;
-    __syncthreads();
-    if (more) { cur ^= 1; p = 0; }
-  }
-  for (int i = tid; i < 624; i += 512) key_out[i] = buf[cur][i];
-  if (tid == 0) *pos_out = p;
 }
 
 // Merge the per-CTA bests into the running best of the whole sweep (one thread; grid <= #SMs).

@@ -49,6 +49,7 @@ struct I8Params {
   double kappa, eps, y_max;
   double* out_mean; double* out_std; double* out_acq;       // optional dumps, indexed like the candidates of this launch
   double* blk_val; long long* blk_idx;
+  int a_from_smem;             // 1: both tensor-core operands from shared memory (A/B measurement), 0: A planes via tensor memory
 };
 
 // K-major operand rows of I8_KC bytes, swizzle of the same width, 8-row groups 8 * I8_KC bytes apart
@@ -72,6 +73,67 @@ __device__ __forceinline__ bool elect_one() {
   uint32_t pred;
   asm volatile("{\n.reg .pred P;\nelect.sync _|P, 0xffffffff;\nselp.u32 %0, 1, 0, P;\n}\n" : "=r"(pred));
   return pred != 0;
+}
+// The same instruction with the A operand (128 candidate rows x 32 bytes of one digit plane) in tensor memory:
+// lane = candidate row, 8 columns = the 32 bytes of the k step.
+__device__ __forceinline__ void umma_i8_ts(uint32_t tmem_c, uint32_t tmem_a, uint64_t db, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, {%5, %5, %5, %5}, p;\n\t}\n"
+      :: "r"(tmem_c), "r"(tmem_a), "l"(db), "r"(I8_IDESC), "r"(accumulate), "r"(0u) : "memory");
+}
+// shared memory -> tensor memory: 128 rows x 256 bits described by a K-major operand descriptor
+__device__ __forceinline__ void tmem_cp_128x256b(uint32_t tmem_dst, uint64_t desc) {
+  asm volatile("tcgen05.cp.cta_group::1.128x256b [%0], %1;\n" :: "r"(tmem_dst), "l"(desc) : "memory");
+}
+
+// Tensor instructions of one stage (I8_KSTEPS k32 steps of the 28 digit-plane pairs), issued by ONE lane.
+//
+// from_smem = false (default): every A plane of a k step is copied once into tensor memory (tcgen05.cp) and the
+// 7 - s instructions that use plane s read it from there, so the tensor core fetches only the B planes from shared
+// memory: 28 KB (copies) + 56 KB (B) per k step instead of 168 KB.  With both operands in shared memory the
+// m128 n64 k32 instruction is bound by that fetch (6 KB per 262 k MAC: 2982 TOPS measured against 4074 for n128);
+// with A in tensor memory the same stream runs at 4032 TOPS (tools/i8_umma_ts.cu, profiles/r02_i8_umma_ts_probe.log).
+// The planes go through a ring of I8_RING slots of 8 columns in the 64 columns the accumulators leave free; the copy
+// of plane p + 1 is issued before the instructions of plane p.  Copies and tensor instructions of one thread execute
+// in issue order, so a slot is overwritten only after the instructions that read it (no barrier needed).
+// `ring` is the running plane count of the caller (advance it by I8_KSTEPS * I8_S per stage on every lane).
+// `fresh` = 0 on the first chunk of a half-block: the first instruction into each class overwrites the accumulator.
+constexpr int I8_ACC_COLS = I8_S * 64;
+constexpr int I8_RING = (512 - I8_ACC_COLS) / 8;
+static_assert(I8_RING >= 2, "the A-plane ring needs two slots");
+__device__ __forceinline__ void issue_stage(uint32_t tmem, uint64_t da0, uint64_t db0, uint32_t fresh, uint32_t ring,
+                                            bool from_smem) {
+  if (from_smem) {
+#pragma unroll
+    for (int t = 0; t < I8_S; ++t) {
+#pragma unroll
+      for (int sl = 0; sl + t < I8_S; ++sl) {
+        // descriptors differ only in the 16-byte-unit address field: + slice * size / 16, + 2 for the second k-step
+        const uint64_t da = da0 + static_cast<uint64_t>(sl * (I8_A_SLICE / 16));
+        const uint64_t db = db0 + static_cast<uint64_t>(t * (I8_B_SLICE / 16));
+        umma_i8(tmem + (sl + t) * 64, da, db, t == 0 ? fresh : 1u);          // class sl + t is first touched by (sl, 0)
+        if (I8_KSTEPS == 2) umma_i8(tmem + (sl + t) * 64, da + 2, db + 2, 1u);
+      }
+    }
+    return;
+  }
+  constexpr int P = I8_KSTEPS * I8_S;
+  const uint32_t ring0 = tmem + I8_ACC_COLS;
+  tmem_cp_128x256b(ring0 + 8 * (ring % I8_RING), da0);
+#pragma unroll
+  for (int pl = 0; pl < P; ++pl) {
+    const int k = pl / I8_S, sl = pl % I8_S;
+    if (pl + 1 < P) {
+      const int k1 = (pl + 1) / I8_S, s1 = (pl + 1) % I8_S;
+      tmem_cp_128x256b(ring0 + 8 * ((ring + pl + 1) % I8_RING), da0 + static_cast<uint64_t>(s1 * (I8_A_SLICE / 16) + 2 * k1));
+    }
+    const uint32_t ta = ring0 + 8 * ((ring + pl) % I8_RING);
+#pragma unroll
+    for (int t = 0; sl + t < I8_S; ++t)                                       // class t is first touched by (0, t) of k step 0
+      umma_i8_ts(tmem + (sl + t) * 64, ta, db0 + static_cast<uint64_t>(t * (I8_B_SLICE / 16) + 2 * k),
+                 (sl == 0 && k == 0) ? fresh : 1u);
+  }
 }
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" :: "r"(bar) : "memory");
@@ -185,7 +247,7 @@ __global__ void __launch_bounds__(192, 1) sweep_i8_kernel(const __grid_constant_
   } else if (warp == 5) {
     // ===== tensor-instruction issuer: the whole warp walks the loops, one elected lane issues =====
     {
-      uint32_t it = 0, acc_round = 0;
+      uint32_t it = 0, acc_round = 0, ring = 0;
       for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
         for (int h = 0; h < nh; ++h, ++acc_round) {
           mbar_wait(bar_acce, (acc_round & 1) ^ 1);        // the previous half-block has been drained
@@ -195,23 +257,13 @@ __global__ void __launch_bounds__(192, 1) sweep_i8_kernel(const __grid_constant_
             mbar_wait(bar0 + 8 * s, ph);
             asm volatile("tcgen05.fence::after_thread_sync;\n");
             const uint32_t a0 = s0 + s * I8_STAGE;
-            // descriptors differ only in the 16-byte-unit address field: + slice * size / 16, + 2 for the second k-step
             const uint64_t da0 = umma_desc_k(a0), db0 = umma_desc_k(a0 + I8_A_BYTES);
             const uint32_t fresh = (kc != 0);                // the first chunk of a half-block overwrites the accumulators
             if (elect_one()) {
-#pragma unroll
-            for (int t = 0; t < I8_S; ++t) {
-#pragma unroll
-              for (int sl = 0; sl + t < I8_S; ++sl) {
-                const uint64_t da = da0 + static_cast<uint64_t>(sl * (I8_A_SLICE / 16));
-                const uint64_t db = db0 + static_cast<uint64_t>(t * (I8_B_SLICE / 16));
-                // class sl + t is first touched by the pair (sl, 0)
-                umma_i8(tmem + (sl + t) * 64, da, db, t == 0 ? fresh : 1u);
-                if (I8_KSTEPS == 2) umma_i8(tmem + (sl + t) * 64, da + 2, db + 2, 1u);
-              }
+              issue_stage(tmem, da0, db0, fresh, ring, p.a_from_smem != 0);
+              umma_commit(bar0 + 8 * (I8_STAGES + s));       // stage free once these instructions have read it
             }
-            umma_commit(bar0 + 8 * (I8_STAGES + s));       // stage free once these instructions have read it
-            }
+            ring += I8_KSTEPS * I8_S;
             __syncwarp();
           }
           if (elect_one()) umma_commit(bar_accf);          // accumulators of this half-block complete

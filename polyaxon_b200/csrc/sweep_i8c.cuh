@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(512, 1) sweep_i8c_kernel(const __grid_constant
         named_bar_sync(1, 256);
       }
       signed char* rows = p.planes + static_cast<size_t>(buf_row0 + 128 * b) * p.npad;
-      if (!(p.dbg & 128) || t < 2) build_tile(p, tile, rows, part_g + (b * I8C_R + r) * 256 + 128, sm, tid, r, I8C_R);
+      if (!PLX_DBG(p.dbg, 128) || t < 2) build_tile(p, tile, rows, part_g + (b * I8C_R + r) * 256 + 128, sm, tid, r, I8C_R);
       __threadfence();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_ready + 8 * b);
@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(512, 1) sweep_i8c_kernel(const __grid_constant
       }
     } else if (warp == 13) {
       // ===== tensor-instruction issuer: the whole warp walks the loops, one elected lane issues =====
-      uint32_t it = 0, acc_round = 0;
+      uint32_t it = 0, acc_round = 0, ring = 0;
       for (long long tile = g; tile < ntiles; tile += groups)
         for (int h = 0; h < nh; ++h) {
           if (part_of(h) != r) continue;
@@ -189,19 +189,10 @@ __global__ void __launch_bounds__(512, 1) sweep_i8c_kernel(const __grid_constant
             const uint64_t da0 = umma_desc_k(a0), db0 = umma_desc_k(a0 + I8_A_BYTES);
             const uint32_t fresh = (kc != 0);              // the first chunk of a half-block overwrites the accumulators
             if (elect_one()) {
-#pragma unroll
-            for (int tt = 0; tt < I8_S; ++tt) {
-#pragma unroll
-              for (int sl = 0; sl + tt < I8_S; ++sl) {
-                const uint64_t da = da0 + static_cast<uint64_t>(sl * (I8_A_SLICE / 16));
-                const uint64_t db = db0 + static_cast<uint64_t>(tt * (I8_B_SLICE / 16));
-                if ((p.dbg & 64) && (sl + tt > 0 || kc > 0)) continue;
-                umma_i8(tmem + (sl + tt) * 64, da, db, tt == 0 ? fresh : 1u);
-                if (I8_KSTEPS == 2) umma_i8(tmem + (sl + tt) * 64, da + 2, db + 2, 1u);
-              }
+              issue_stage(tmem, da0, db0, fresh, ring, ip.a_from_smem != 0);
+              umma_commit(bar0 + 8 * (I8_STAGES + s));       // stage free once these instructions have read it
             }
-            umma_commit(bar0 + 8 * (I8_STAGES + s));       // stage free once these instructions have read it
-            }
+            ring += I8_KSTEPS * I8_S;
             __syncwarp();
           }
           if (elect_one()) umma_commit(bar_accf);          // accumulators of this half-block complete

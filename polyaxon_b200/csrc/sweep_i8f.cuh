@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(512, 1) sweep_i8f_kernel(const __grid_constant
       const uint32_t b = t & 1, use = t >> 1;
       if (use > 0) mbar_wait(bar_free + 8 * b, (use - 1) & 1);       // the tile that used this buffer is consumed
       signed char* rows = p.planes + static_cast<size_t>(buf_row0 + 128 * b) * p.npad;
-      if (!(p.dbg & 128) || t < 2) build_tile(p, tile, rows, meanbuf + buf_row0 + 128 * b, sm, tid);
+      if (!PLX_DBG(p.dbg, 128) || t < 2) build_tile(p, tile, rows, meanbuf + buf_row0 + 128 * b, sm, tid);
       __threadfence();
       asm volatile("fence.proxy.async;\n" ::: "memory");            // generic-proxy stores -> visible to TMA
       __syncwarp();
@@ -267,7 +267,7 @@ __global__ void __launch_bounds__(512, 1) sweep_i8f_kernel(const __grid_constant
       }
     } else if (warp == 13) {
       // ===== tensor-instruction issuer: the whole warp walks the loops, one elected lane issues =====
-      uint32_t it = 0, acc_round = 0;
+      uint32_t it = 0, acc_round = 0, ring = 0;
       for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
         for (int h = 0; h < nh; ++h, ++acc_round) {
           mbar_wait(bar_acce, (acc_round & 1) ^ 1);        // the previous half-block has been drained
@@ -280,19 +280,10 @@ __global__ void __launch_bounds__(512, 1) sweep_i8f_kernel(const __grid_constant
             const uint64_t da0 = umma_desc_k(a0), db0 = umma_desc_k(a0 + I8_A_BYTES);
             const uint32_t fresh = (kc != 0);              // the first chunk of a half-block overwrites the accumulators
             if (elect_one()) {
-#pragma unroll
-            for (int tt = 0; tt < I8_S; ++tt) {
-#pragma unroll
-              for (int sl = 0; sl + tt < I8_S; ++sl) {
-                const uint64_t da = da0 + static_cast<uint64_t>(sl * (I8_A_SLICE / 16));
-                const uint64_t db = db0 + static_cast<uint64_t>(tt * (I8_B_SLICE / 16));
-                if ((p.dbg & 64) && (sl + tt > 0 || kc > 0)) continue;
-                umma_i8(tmem + (sl + tt) * 64, da, db, tt == 0 ? fresh : 1u);
-                if (I8_KSTEPS == 2) umma_i8(tmem + (sl + tt) * 64, da + 2, db + 2, 1u);
-              }
+              issue_stage(tmem, da0, db0, fresh, ring, ip.a_from_smem != 0);
+              umma_commit(bar0 + 8 * (I8_STAGES + s));       // stage free once these instructions have read it
             }
-            umma_commit(bar0 + 8 * (I8_STAGES + s));       // stage free once these instructions have read it
-            }
+            ring += I8_KSTEPS * I8_S;
             __syncwarp();
           }
           if (elect_one()) umma_commit(bar_accf);          // accumulators of this half-block complete

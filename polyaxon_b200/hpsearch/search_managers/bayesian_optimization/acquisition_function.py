@@ -34,6 +34,15 @@ from polyaxon_b200.schemas.hptuning import (
 THETA_BOUNDS = (float(np.log(1e-5)), float(np.log(1e5)))      # sklearn's default length_scale_bounds
 
 
+def _warn_clamped(std):
+    """sklearn warns when predicted variances come out negative and sets them to zero
+    (_gpr.py:485-491, reached from acquisition_function.py:49); the kernels clamp, the warning is raised here
+    for the per-candidate outputs the caller asked for (an exact zero is what the clamp leaves)."""
+    if std is not None and np.any(std == 0.0):
+        import warnings
+        warnings.warn('Predicted variances smaller than 0. Setting those variances to 0.')
+
+
 def _acq_id(name):
     if AcquisitionFunctions.is_ucb(name):
         return _lib.ACQ_UCB
@@ -60,6 +69,7 @@ class DeviceGaussianProcess(object):
         self.random_state = random_state
         self._handle = handle
         self.fitted = False
+        self._fit_count = 0
 
     @property
     def handle(self):
@@ -87,10 +97,30 @@ class DeviceGaussianProcess(object):
         self.optimizer_runs_ = per_run
         self.X_train_, self.y_train_ = X, y
         self.fitted = True
+        self._stamp()
         self.handle.held = dict(X=X.copy(), y=y.copy(), kernel=(self.kernel_id, self.nu, self.length_scale,
                                                                 self.n_restarts_optimizer),
                                 theta=theta, lml=lml, since_fit=0)
         return self
+
+    # The handle (observations, factor, posterior state on the GPU) is shared by every model of a thread
+    # (device.get_handle); in the reference each UtilityFunction owns its GaussianProcessRegressor.  The stamp
+    # says whose state the handle holds; a model that finds somebody else's puts its own back before it is used.
+    def _stamp(self):
+        self._fit_count += 1
+        self.handle.owner = (id(self), self._fit_count)
+
+    def ensure_state(self):
+        """Make the handle hold THIS model's observations and posterior state (a no-op for the usual
+        one-optimizer-per-call flow).  Raises when the model was never fitted."""
+        if not self.fitted:
+            raise RuntimeError('this Gaussian process has not been fitted: call fit(X, y) first')
+        h = self.handle
+        if getattr(h, 'owner', None) != (id(self), self._fit_count):
+            h.set_data(self.X_train_, self.y_train_, self.kernel_id, self.nu, self.alpha)
+            h.set_theta(self.theta_)
+            h.owner = (id(self), self._fit_count)
+        return h
 
     def _append_instead_of_refit(self, X, y):
         """Opt-in (PLX_BO_REFIT_EVERY = k > 1; the default 1 is the reference's behaviour, a full
@@ -99,7 +129,8 @@ class DeviceGaussianProcess(object):
         fit, keep theta and extend the posterior state row by row on the device (plx_gp_append)."""
         every = int(os.environ.get('PLX_BO_REFIT_EVERY', '1') or 1)
         held = getattr(self.handle, 'held', None)
-        if every <= 1 or held is None:
+        if every <= 1 or held is None or not self.fitted or \
+                getattr(self.handle, 'owner', None) != (id(self), self._fit_count):
             return False
         n0 = held['X'].shape[0]
         same_model = held['kernel'] == (self.kernel_id, self.nu, self.length_scale, self.n_restarts_optimizer)
@@ -119,6 +150,7 @@ class DeviceGaussianProcess(object):
         self.optimizer_runs_ = None
         self.X_train_, self.y_train_ = X, y
         self.fitted = True
+        self._stamp()
         return True
 
     def _fit_runs(self, theta0, restarts):
@@ -133,23 +165,21 @@ class DeviceGaussianProcess(object):
         if size == 1 or len(starts) == 1 or os.environ.get('PLX_BO_DISTRIBUTED', '1') == '0':
             return self.handle.fit(theta0, restarts, THETA_BOUNDS)
         mine = starts[rank::size]
-        if mine:
-            _, _, part = self.handle.fit(mine[0], mine[1:], THETA_BOUNDS)
-        else:
-            part = np.zeros((0, 4))
         per = (len(starts) + size - 1) // size
-        torch = pdist.torch
-        dev = torch.device('cuda', self.handle.device)
-        pack = torch.full((per, 4), float('nan'), dtype=torch.float64, device=dev)
-        if len(part):
-            pack[:len(part)] = torch.from_numpy(np.ascontiguousarray(part)).to(dev)
-        out = torch.empty(size * per, 4, dtype=torch.float64, device=dev)
-        pdist.dist.all_gather_into_tensor(out, pack)
-        out = out.cpu().numpy().reshape(size, per, 4)
+        pack = np.full((per, 4), np.nan)
+        if mine:
+            # this rank's runs only: the posterior state is built below, at the winner of ALL runs.  (With the
+            # state built here a rank whose starts all give a non-positive-definite kernel matrix would raise
+            # before the collective and leave the other ranks waiting in it.)
+            part = self.handle.fit(mine[0], mine[1:], THETA_BOUNDS, apply=False)[2]
+            pack[:len(part)] = part
+        out = pdist.gather_rows(pack.ravel(), device=pdist.collective_device(self.handle.device))
+        out = out.reshape(size, per, 4)
         per_run = np.array([out[i % size, i // size] for i in range(len(starts))])
+        # sklearn: np.argmin over the list of -LML values (first minimum; -inf LML = +inf there, _gpr.py:336-337)
         best = int(np.argmin(-per_run[:, 2]))
         theta = float(per_run[best, 1])
-        self.handle.set_theta(theta)
+        self.handle.set_theta(theta)            # LinAlgError on every rank alike when no run was positive definite
         return theta, float(per_run[best, 2]), per_run
 
     @property
@@ -161,10 +191,10 @@ class DeviceGaussianProcess(object):
         return self.handle.get_state(want_L=False)[1]
 
     def predict(self, X, return_std=False):
-        if not self.fitted:
-            raise RuntimeError('DeviceGaussianProcess.predict called before fit')
+        h = self.ensure_state()
         X = np.atleast_2d(np.asarray(X, dtype=np.float64))
-        _, _, _, mean, std, _ = self.handle.sweep(X, _lib.ACQ_UCB, 0.0, kappa=0.0, dump=True)
+        _, _, _, mean, std, _ = h.sweep(X, _lib.ACQ_UCB, 0.0, kappa=0.0, dump=True)
+        _warn_clamped(std)
         return (mean, std) if return_std else mean
 
 
@@ -198,53 +228,63 @@ class UtilityFunction(object):
         the two counts; a seeded group re-creates the same state on every call (manager.py:30), so
         the candidate matrix of the previous call is still in device memory and neither the
         numpy draw nor the host->device copy is repeated.  On a hit the generator is moved to the
-        state it would have reached, so everything downstream sees the reference's stream."""
+        state it would have reached, so everything downstream sees the reference's stream.
+
+        Under torch.distributed every rank has the same generator state; each draws and keeps only its
+        own contiguous block of rows of that one matrix (the device jumps ahead in the MT19937 stream,
+        csrc/mt19937.cuh) and all ranks leave with the state after the whole matrix."""
         rng = self.random_generator
         d = bounds.shape[0]
+        rank, size = pdist.world()
+        if os.environ.get('PLX_BO_DISTRIBUTED', '1') == '0':
+            rank, size = 0, 1
+        lo, hi = pdist.shard_range(n_warmup, rank, size)
         key = None
         if os.environ.get('PLX_BO_CANDIDATE_CACHE', '1') != '0' and hasattr(rng, 'get_state'):
             state = rng.get_state()
             digest = hashlib.sha1(state[1].tobytes())
-            digest.update(repr((state[0], state[2], state[3], state[4], n_warmup, n_iter)).encode())
+            digest.update(repr((state[0], state[2], state[3], state[4], n_warmup, n_iter, rank, size)).encode())
             digest.update(bounds.tobytes())
             key = digest.hexdigest()
         cached = h.seed_cache.get(key) if key is not None else None
         if cached is not None and h.resident_key == key:
             x_seeds, state_after = cached
             rng.set_state(state_after)
-            max_acq, x_max = self._sweep_resident(h, acq, args, n_warmup)
+            max_acq, x_max = self._sweep_resident(h, acq, args, lo, hi, size)
             return max_acq, x_max, x_seeds.copy()
         drawn_on_device = False
         if key is not None and os.environ.get('PLX_BO_DEVICE_RNG', '1') != '0':
-            # numpy's MT19937 stream regenerated on the GPU, bit for bit (sweep.cuh); rng is moved on
-            drawn_on_device = h.candidates_draw(rng, bounds[:, 0], bounds[:, 1], n_warmup, key=key)
+            # numpy's MT19937 stream regenerated on the GPU, bit for bit; rng is moved past the whole matrix
+            drawn_on_device = h.candidates_draw(rng, bounds[:, 0], bounds[:, 1], n_warmup, key=key,
+                                                first=lo, count=hi - lo)
         if not drawn_on_device:
             x_tries = rng.uniform(bounds[:, 0], bounds[:, 1], size=(n_warmup, d))
         x_seeds = rng.uniform(bounds[:, 0], bounds[:, 1], size=(n_iter, d))
         if key is None:
-            max_acq, _, x_max = h.sweep(x_tries, acq, **args)
+            if size == 1:
+                max_acq, _, x_max = h.sweep(x_tries, acq, **args)
+            else:
+                value, index, x = h.sweep(x_tries[lo:hi], acq, idx_base=lo, **args)
+                max_acq, _, x_max = pdist.merge_best_x(value, index if hi > lo else -1, x,
+                                                       device=pdist.collective_device(h.device))
             return max_acq, x_max, x_seeds
         if not drawn_on_device:
-            h.candidates_set(x_tries, key=key)
+            h.candidates_set(x_tries, key=key)       # host draw (odd stream position): the whole matrix, rows lo..hi swept
         h.seed_cache.clear()                     # one resident matrix per handle
         h.seed_cache[key] = (x_seeds.copy(), rng.get_state())
-        max_acq, x_max = self._sweep_resident(h, acq, args, n_warmup)
+        max_acq, x_max = self._sweep_resident(h, acq, args, lo, hi, size)
         return max_acq, x_max, x_seeds
 
     @staticmethod
-    def _sweep_resident(h, acq, args, n_warmup):
-        """Sweep of the resident matrix.  Under torch.distributed (one process per GPU, every rank
-        holding the same generator state and therefore the same matrix) each rank sweeps a
-        contiguous slice and one all-gather of {value, index} merges the bests; the winning row is
-        then read from the rank's own copy, so no candidate data crosses the links."""
-        rank, size = pdist.world()
-        if size == 1 or os.environ.get('PLX_BO_DISTRIBUTED', '1') == '0':
-            value, _, x = h.sweep_resident(acq, **args)
+    def _sweep_resident(h, acq, args, lo, hi, size):
+        """Sweep of the resident rows.  With several ranks each sweeps its block and ONE all-gather of
+        {value, global index, row} records merges the bests with numpy.argmax order on every rank."""
+        if size == 1:
+            value, _, x = h.sweep_resident_range(lo, hi - lo, acq, **args)
             return value, x
-        lo, hi = pdist.shard_range(n_warmup, rank, size)
-        value, index, _ = h.sweep_resident_range(lo, hi - lo, acq, **args)
-        value, index = pdist.merge_best(value, index if hi > lo else -1, device=pdist.torch.device('cuda', h.device))
-        return value, h.candidates_get(index, 1, h.d)[0]
+        value, index, x = h.sweep_resident_range(lo, hi - lo, acq, **args)
+        value, _, x = pdist.merge_best_x(value, index if hi > lo else -1, x, device=pdist.collective_device(h.device))
+        return value, x
 
     def compute(self, x, y_max):
         """Acquisition values of the rows of x (acquisition_function.py:62-68)."""
@@ -252,14 +292,16 @@ class UtilityFunction(object):
         if acq is None:
             return None
         x = np.atleast_2d(np.asarray(x, dtype=np.float64))
-        return self.gaussian_process.handle.sweep(x, acq, dump=True, **args)[5]
+        out = self.gaussian_process.ensure_state().sweep(x, acq, dump=True, **args)
+        _warn_clamped(out[4])
+        return out[5]
 
     def max_compute(self, y_max, bounds, n_warmup=100000, n_iter=250):
         """arg max of the acquisition function (acquisition_function.py:70-115): `n_warmup` random
         candidates swept on the device, then `n_iter` bounded quasi-Newton refinements, batched."""
         acq, args = self._acq_args(y_max)
         bounds = np.asarray(bounds, dtype=np.float64)
-        h = self.gaussian_process.handle
+        h = self.gaussian_process.ensure_state()
         max_acq, x_max, x_seeds = self._warmup(h, acq, args, bounds, n_warmup, n_iter)
         if n_iter > 0:
             rank, size = pdist.world()
@@ -267,7 +309,7 @@ class UtilityFunction(object):
                 # seeds are dealt round-robin to the ranks, results gathered back in seed order
                 xs, values, success = h.refine(x_seeds[rank::size], bounds, acq, **args)
                 xs, values, success = pdist.gather_refined(xs, values, success, n_iter,
-                                                           device=pdist.torch.device('cuda', h.device))
+                                                           device=pdist.collective_device(h.device))
             else:
                 xs, values, success = h.refine(x_seeds, bounds, acq, **args)
             for x_ref, value, ok in zip(xs, values, success):

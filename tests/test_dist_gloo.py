@@ -126,3 +126,98 @@ def test_groups_are_dealt_to_ranks_and_gathered_over_gloo():
         assert mine_only[lo:hi] == want[lo:hi]
         assert all(s is None for s in mine_only[:lo] + mine_only[hi:])
     assert os.environ.get('PLX_BO_DISTRIBUTED') is None
+
+
+class _FakeHandle(object):
+    """Stands in for the C-ABI handle in the host-side tests of the sharded hyper-parameter fit and the sharded
+    warm-up sweep (no GPU here): every run converges where it started with LML = -(theta - 1)^2, except that
+    thetas above 5 are 'not positive definite' (LML = -inf), as a very long length scale is on real data."""
+    device = 0
+
+    def __init__(self):
+        self.set_theta_calls = []
+        self.held = None
+        self.owner = None
+        self.seed_cache = {}
+        self.resident_key = None
+
+    def fit(self, theta0, restarts=(), bounds=None, apply=True):
+        starts = [theta0] + list(restarts)
+        # a rank of a sharded fit must not build the posterior state from its own runs
+        assert apply is False or len(starts) == 1
+        rows = np.array([[t, t, -np.inf if t > 5 else -(t - 1.0) ** 2, 3.0] for t in starts])
+        best = int(np.argmin(-rows[:, 2]))
+        if apply:
+            self.set_theta(rows[best, 1])
+        return float(rows[best, 1]), float(rows[best, 2]), rows
+
+    def set_theta(self, theta):
+        if theta > 5:
+            raise np.linalg.LinAlgError('kernel matrix is not positive definite')
+        self.set_theta_calls.append(theta)
+
+
+def _fit_worker(rank, world, port, starts, out):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    from polyaxon_b200.hpsearch.search_managers.bayesian_optimization.acquisition_function import (
+        DeviceGaussianProcess)
+    gp = DeviceGaussianProcess('matern', 1.0, 1.5, len(starts) - 1, np.random.RandomState(1), handle=_FakeHandle())
+    try:
+        theta, lml, per_run = gp._fit_runs(starts[0], starts[1:])
+        out[rank] = ('ok', theta, lml, per_run.tolist(), gp.handle.set_theta_calls)
+    except np.linalg.LinAlgError as exc:
+        out[rank] = ('linalg', str(exc))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize('starts,want', [
+    ([0.0, 9.0, 2.0, 8.0, 1.5], ('ok', 1.5)),      # rank 1 gets 9.0 and 8.0: every one of its runs is non-PD
+    ([7.0, 9.0], ('linalg', None)),                # no run anywhere is PD: every rank raises, none hangs
+    ([0.5], ('ok', 0.5)),
+])
+def test_sharded_fit_survives_a_rank_without_a_positive_definite_run(starts, want):
+    """a rank whose share of the optimiser runs is all non-positive-definite used to raise before the
+    all-gather and leave the other rank blocked in it.  Now the ranks exchange their runs first and build the
+    state at the global winner (sklearn: argmin over -LML with -inf LML = +inf, _gpr.py:336-337)."""
+    port = _free_port()
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_fit_worker, args=(2, port, starts, out), nprocs=2, join=True)
+    for rank in range(2):
+        assert out[rank][0] == want[0]
+        if want[0] == 'ok':
+            _, theta, lml, per_run, calls = out[rank]
+            assert theta == want[1] and calls == [want[1]]
+            assert [row[0] for row in per_run] == starts        # gathered back in run order
+    if want[0] == 'ok' and len(starts) > 1:
+        assert out[0][1:4] == out[1][1:4]
+
+
+def _merge_x_worker(rank, world, port, out):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    # rank 0 holds rows 0..4, rank 1 rows 5..9; values tie at 3.0 on rows 2 and 7 -> the lower index wins
+    local = (3.0, 2 + 5 * rank, np.array([10.0 * rank + 1, 10.0 * rank + 2]))
+    res = [pd.merge_best_x(*local)]
+    # an empty shard contributes index -1 and is ignored
+    res.append(pd.merge_best_x(float('nan'), -1, np.zeros(2)) if rank == 0 else pd.merge_best_x(1.0, 8, np.array([7.0, 8.0])))
+    # a huge index survives the trip through the float64 record bit for bit
+    res.append(pd.merge_best(float(rank), (1 << 62) + 12345 + rank))
+    out[rank] = [(v, i) + ((x.tolist(),) if len(r) == 3 else ()) for r in res for v, i, *rest in [r]
+                 for x in [rest[0] if rest else None]]
+    dist.destroy_process_group()
+
+
+def test_single_record_merge_carries_index_bits_and_the_winning_row():
+    port = _free_port()
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_merge_x_worker, args=(2, port, out), nprocs=2, join=True)
+    for rank in range(2):
+        a, b, c = out[rank]
+        assert a == (3.0, 2, [1.0, 2.0])
+        assert b == (1.0, 8, [7.0, 8.0])
+        assert c == (1.0, (1 << 62) + 12346)

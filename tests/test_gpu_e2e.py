@@ -187,6 +187,40 @@ def test_device_mt19937_reproduces_numpy_bit_for_bit(d, n_cand, pre_draws):
         h.close()
 
 
+@pytest.mark.parametrize('d,n_cand,pre_draws,world', [(32, 2000000, 16, 2), (3, 5000000, 0, 1), (32, 300000, 2, 3),
+                                                      (1, 700, 1, 2), (7, 9, 0, 4)])
+def test_device_mt19937_draws_any_block_of_rows(d, n_cand, pre_draws, world):
+    """The sharded draw (plx_candidates_draw_mt19937_range): every rank of a multi-GPU job draws only its block of
+    rows of the SAME numpy matrix by jumping ahead in the MT19937 stream (csrc/mt19937.cuh), the blocks are cut
+    into per-CTA chunks that jump as well (the first two shapes are large enough for that), and every rank ends with
+    the generator state numpy reaches after the whole matrix."""
+    from polyaxon_b200 import _lib, dist as pdist
+    h = _lib.Handle(0)
+    try:
+        lo = np.linspace(-3.0, 2.0, d)
+        hi = lo + np.linspace(0.5, 7.0, d)
+        a = np.random.RandomState(99)
+        for _ in range(pre_draws):
+            a.uniform(-11.5, 11.5)
+        start = a.get_state()
+        want = a.uniform(lo, hi, size=(n_cand, d))
+        end = a.get_state()
+        for rank in range(world):
+            first, stop = pdist.shard_range(n_cand, rank, world)
+            b = np.random.RandomState()
+            b.set_state(start)
+            assert h.candidates_draw(b, lo, hi, n_cand, first=first, count=stop - first)
+            got = h.candidates_get(first, stop - first, d)
+            assert np.array_equal(got, want[first:stop]), rank
+            sb = b.get_state()
+            assert np.array_equal(sb[1], end[1]) and sb[2] == end[2], rank
+            if stop > first:
+                with pytest.raises(_lib.PlxError):
+                    h.candidates_get(stop, 1, d)              # outside the block this rank holds
+    finally:
+        h.close()
+
+
 def test_device_rng_and_host_rng_give_the_same_suggestion(monkeypatch):
     from polyaxon_b200 import device
     from polyaxon_b200.hpsearch.search_managers.bayesian_optimization.optimizer import BOOptimizer

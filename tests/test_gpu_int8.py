@@ -127,3 +127,31 @@ def test_two_cooperative_sweeps_from_two_handles_at_once():
         if not any(t.is_alive() for t in threads):
             for h in handles:
                 h.close()
+
+
+@pytest.mark.parametrize('impl', INT8_IMPLS)
+@pytest.mark.parametrize('n', [70, 600, 2048])
+def test_a_planes_through_tensor_memory_equal_shared_memory_operands(handle, impl, n):
+    """The candidate tile's digit planes reach the tensor core through tensor memory (tcgen05.cp into a ring of
+    8-column slots, option i8_operand = 0, the default) or straight from shared memory (1).  Both are the same exact
+    integer products in the same accumulation classes, so every output must be bit-identical -- also after many
+    stages, when every slot of the ring has been overwritten often."""
+    d = 9
+    X, y, _ = synthetic_problem(n, d, seed=5 + n)
+    handle.set_data(X, y, G.KERNEL_MATERN, 2.5)
+    handle.set_theta(0.2)
+    xc = np.random.RandomState(n + impl).uniform(0, 1, (128 * 148 * 2 + 31, d))
+    out = {}
+    try:
+        handle.set_option('sweep_impl', impl)
+        for operand in (0, 1):
+            handle.set_option('i8_operand', operand)
+            out[operand] = handle.sweep(xc, G.ACQ_EI, float(y.max()), eps=0.01, dump=True)
+    finally:
+        handle.set_option('i8_operand', 0)
+        handle.set_option('sweep_impl', 3)
+    assert out[0][1] == out[1][1] and out[0][0] == out[1][0]
+    for k in (3, 4, 5):
+        assert np.array_equal(out[0][k], out[1][k], equal_nan=True)
+    m, s = _oracle(X, y, 0.2, G.KERNEL_MATERN, 2.5, xc[:4096])
+    assert np.abs(out[0][4][:4096] ** 2 - s ** 2).max() <= 1e-9

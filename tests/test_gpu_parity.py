@@ -93,7 +93,7 @@ def test_mean_std_acquisition_match_reference(handle, name, impl):
 
 @pytest.mark.parametrize('impl', [5, 4, 2, 1, 0])   # int8-sliced cooperative / fused / two-kernel, FP64 DMMA + TMA ring, plain loads
 @pytest.mark.parametrize('name', CLOSED_FORM)
-def test_sweep_argmax_is_bit_exact(handle, name, impl):
+def test_sweep_argmax_is_bit_exact(handle, name, impl, record_property):
     g = load_golden(name)
     _setup(handle, g)
     xt = _x_tries(g)
@@ -107,7 +107,14 @@ def test_sweep_argmax_is_bit_exact(handle, name, impl):
         assert np.array_equal(x, g['x_warm'])
         assert val == pytest.approx(float(g['warm_acq']), rel=1e-9)
     else:
-        # ill-conditioned reference fixtures: the winning value must still agree
+        # ill-conditioned reference fixture (ref14: duplicated rows + 1e-10 jitter, cond 2e10): two FP64
+        # factorisations of that matrix differ by far more than the gaps between candidates, so only the winning
+        # value is held to the reference; whether the index happened to agree is recorded, not hidden
+        # ("known deviations")
+        matched = idx == int(g['argmax'])
+        record_property('argmax_index_matched_reference', matched)
+        print('%s impl %d: cond %.1e, arg-max index %s the reference (%d vs %d)' % (
+            name, impl, float(g['cond']), 'equals' if matched else 'differs from', idx, int(g['argmax'])))
         assert val == pytest.approx(float(g['warm_acq']), rel=1e-6)
 
 
@@ -244,7 +251,11 @@ def test_large_problem_against_oracle_and_shard_merge(handle):
     m, s = G.predict(xc[:2048], X, L, a, theta, G.KERNEL_MATERN, 1.5)
     assert np.abs(mean[:2048] - m).max() <= 1e-9 * max(1.0, np.abs(m).max())
     assert np.allclose(std[:2048], s, rtol=1e-9, atol=0)
-    assert idx == int(np.argmax(acq)) and val == acq[idx]
+    # arg-max against the oracle's own sweep of all 40 000 candidates (not against the device's dump)
+    ridx, rval, racq = G.sweep(xc, X, L, a, theta, G.KERNEL_MATERN, 1.5, G.ACQ_POI, y_max, 0.0, 0.0, chunk=8192)
+    assert idx == ridx
+    assert val == pytest.approx(rval, rel=1e-9)
+    assert val == acq[idx]
     assert np.array_equal(xb, xc[idx])
     best = (-np.inf, -1)
     for lo in range(0, 40000, 13337):

@@ -107,3 +107,30 @@ def test_refine_edge_cases(handle):
     xa, va, oa = handle.refine(seeds, b, **_args(g))
     xb, vb, ob = handle.refine(seeds[20:21], b, **_args(g))
     assert np.array_equal(xa[20], xb[0]) and va[20] == vb[0]
+
+
+def test_wide_one_hot_space_is_refined(handle):
+    """A search space whose encoded width is far beyond 128 (categoricals widen it quickly: one column per
+    choice).  The reference's scipy loop has no width limit (acquisition_function.py:95-111); the device
+    refinement keeps its per-seed gradient in 16 d bytes of shared memory and takes d up to 2048."""
+    from oracle.reference_path import synthetic_problem
+    d, n = 300, 40
+    X, y, bounds = synthetic_problem(n, d, seed=8)
+    theta = 1.5
+    handle.set_data(X, y, G.KERNEL_MATERN, 2.5)
+    handle.set_theta(theta)
+    L, a = G.posterior_state(X, y, theta, G.KERNEL_MATERN, 2.5)
+    seeds = np.random.RandomState(2).uniform(0, 1, (6, d))
+    y_max = float(y.max())
+    vals, grads = handle.acq_value_grad(seeds, G.ACQ_EI, y_max, eps=0.0)
+    for x, v, gr in zip(seeds, vals, grads):
+        rv, rg = G.acquisition_value_and_grad(x, X, L, a, theta, G.KERNEL_MATERN, 2.5, G.ACQ_EI, y_max, 0.0, 0.0)
+        assert v == pytest.approx(rv, rel=1e-9, abs=1e-13)
+        assert np.allclose(gr, rg, rtol=1e-7, atol=1e-9 * max(1.0, np.abs(rg).max()))
+    xs, got, ok = handle.refine(seeds, bounds, G.ACQ_EI, y_max, eps=0.0)
+    assert ok.all()
+    assert np.all(xs >= 0.0) and np.all(xs <= 1.0)
+    for x, v, v0 in zip(xs, got, vals):
+        m, s = G.predict(x[None, :], X, L, a, theta, G.KERNEL_MATERN, 2.5)
+        assert v == pytest.approx(G.acquisition(m, s, G.ACQ_EI, y_max, 0.0, 0.0)[0], rel=1e-9, abs=1e-13)
+        assert v >= v0 - 1e-12                     # never worse than where it started
