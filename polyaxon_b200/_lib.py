@@ -10,7 +10,8 @@ from ctypes import POINTER, c_char_p, c_double, c_int, c_longlong, c_void_p
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, 'libplxbo.so')
+# PLX_BO_LIB: another build of the same library (tools/*_phases.py load the -DPLX_PROFILE build through it)
+LIB_PATH = os.environ.get('PLX_BO_LIB') or os.path.join(HERE, 'libplxbo.so')
 
 PLX_OK, PLX_ERR_INVALID, PLX_ERR_CUDA, PLX_ERR_NOT_PD, PLX_ERR_STATE, PLX_ERR_UNSUPPORTED = range(6)
 KERNEL_RBF, KERNEL_MATERN = 0, 1

@@ -189,7 +189,7 @@ __global__ void __launch_bounds__(512, 1) sweep_i8c_kernel(const __grid_constant
             const uint64_t da0 = umma_desc_k(a0), db0 = umma_desc_k(a0 + I8_A_BYTES);
             const uint32_t fresh = (kc != 0);              // the first chunk of a half-block overwrites the accumulators
             if (elect_one()) {
-              issue_stage(tmem, da0, db0, fresh, ring, ip.a_from_smem != 0);
+              if (!PLX_DBG(p.dbg, 64)) issue_stage(tmem, da0, db0, fresh, ring, ip.a_from_smem != 0);
               umma_commit(bar0 + 8 * (I8_STAGES + s));       // stage free once these instructions have read it
             }
             ring += I8_KSTEPS * I8_S;

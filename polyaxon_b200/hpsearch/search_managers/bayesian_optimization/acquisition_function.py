@@ -129,8 +129,7 @@ class DeviceGaussianProcess(object):
         fit, keep theta and extend the posterior state row by row on the device (plx_gp_append)."""
         every = int(os.environ.get('PLX_BO_REFIT_EVERY', '1') or 1)
         held = getattr(self.handle, 'held', None)
-        if every <= 1 or held is None or not self.fitted or \
-                getattr(self.handle, 'owner', None) != (id(self), self._fit_count):
+        if every <= 1 or held is None:          # `held` is dropped whenever anybody replaces the handle's data or theta
             return False
         n0 = held['X'].shape[0]
         same_model = held['kernel'] == (self.kernel_id, self.nu, self.length_scale, self.n_restarts_optimizer)

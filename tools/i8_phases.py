@@ -1,4 +1,6 @@
-"""Time split of the fused int8-sliced sweep: whole, tensor instructions skipped (builder-bound), builders skipped."""
+"""Time split of the fused int8-sliced sweep: whole, tensor instructions skipped (builder-bound), builders skipped.
+Needs the profiling build:  python -m polyaxon_b200.build --profile
+                            PLX_BO_LIB=polyaxon_b200/libplxbo_profile.so python tools/i8_phases.py [impl] [i8_operand]"""
 import sys
 import numpy as np
 sys.path.insert(0, '.')
@@ -13,10 +15,11 @@ h.set_theta(1.2)
 xc = torch.rand(N, d, dtype=torch.float64, device='cuda')
 torch.cuda.synchronize()
 h.set_option('sweep_impl', int(sys.argv[1]) if len(sys.argv) > 1 else 5)
+h.set_option('i8_operand', int(sys.argv[2]) if len(sys.argv) > 2 else 0)
 for dbg in (0, 64, 128, 64 | 128):
     h.set_option('sweep_dbg', dbg)
     ms = []
     for _ in range(3):
         h.sweep_dev(xc.data_ptr(), N, _lib.ACQ_POI, float(y.max()))
         ms.append(h.last_sweep_stats()[0])
-    print('dbg %d: %.2f ms' % (dbg, min(ms)))
+    print('impl %s operand %s dbg %d: %.2f ms' % (sys.argv[1:2], sys.argv[2:3], dbg, min(ms)))
