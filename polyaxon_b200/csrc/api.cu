@@ -3,7 +3,7 @@
 #include "../../include/plxbo.h"
 #include "refine.cuh"
 #include "append.cuh"
-#include "sweep_i8c.cuh"
+#include "sweep_i8p.cuh"
 #include "mt19937.cuh"
 
 #include <cstdio>
@@ -69,7 +69,8 @@ struct plx_bo {
   double* d_i8mean = nullptr; size_t i8mean_cap = 0;
   double* d_i8part = nullptr; size_t i8part_cap = 0;             // cooperative form: partial sums per group
   unsigned* d_i8sync = nullptr; size_t i8sync_cap = 0;           //                   counters per group
-  CUtensorMap tmA8, tmB8;
+  CUtensorMap tmA8, tmB8, tmA8p;          // tmA8p: box of one plane (paired form, sweep_i8p.cuh)
+  int coop_cluster_ok = 1;                // cooperative + cluster launch accepted by the driver (tried once)
   long long i8_rows = 0; int i8_npad = 0;
   bool i8_state_valid = false;
 
@@ -210,9 +211,11 @@ extern "C" int plx_bo_create(int device, plx_bo_handle* out) {
       qres != cudaDriverEntryPointSuccess)
     return bail("cuTensorMapEncodeTiled not available from the driver");
   h->encode = reinterpret_cast<EncodeTiledFn>(fn);
+  if (const char* e = std::getenv("PLX_BO_NO_COOP_CLUSTER"))     // profilers that cannot replay a cooperative cluster launch
+    if (std::atoi(e) != 0) h->coop_cluster_ok = 0;
   if (const char* e = std::getenv("PLX_BO_SWEEP_IMPL")) {       // A/B switch for measurements; see plx_bo_set_option
     const int v = std::atoi(e);
-    if (v >= 0 && v <= 5) h->sweep_impl = v;
+    if (v >= 0 && v <= 6) h->sweep_impl = v;
   }
   // opt in to large dynamic shared memory once
   cudaFuncSetAttribute(potf2_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, POTF_SMEM);
@@ -226,6 +229,7 @@ extern "C" int plx_bo_create(int device, plx_bo_handle* out) {
   cudaFuncSetAttribute(sweep_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, I8_SMEM);
   cudaFuncSetAttribute(sweep_i8f_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, I8F_SMEM);
   cudaFuncSetAttribute(sweep_i8c_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, I8F_SMEM);
+  cudaFuncSetAttribute(sweep_i8p_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, I8F_SMEM);
   cudaFuncSetAttribute(kstar_slices_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, KSL_SMEM);
   cudaFuncSetAttribute(mt19937_draw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                        static_cast<int>(sizeof(unsigned) * MT_SEQ + sizeof(double) * 2 * 2048));
@@ -266,7 +270,7 @@ extern "C" int plx_bo_set_stream(plx_bo_handle h, void* stream) {
 
 extern "C" int plx_bo_set_option(plx_bo_handle h, const char* name, long long value) {
   if (!h || !name) return PLX_ERR_INVALID;
-  if (std::strcmp(name, "sweep_impl") == 0 && value >= 0 && value <= 5) { h->sweep_impl = static_cast<int>(value); return PLX_OK; }
+  if (std::strcmp(name, "sweep_impl") == 0 && value >= 0 && value <= 6) { h->sweep_impl = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "lml_batch_limit") == 0 && value >= 0) { h->lml_batch_limit = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "fit_apply") == 0 && (value == 0 || value == 1)) { h->fit_apply = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "i8_operand") == 0 && (value == 0 || value == 1)) { h->i8_a_from_smem = static_cast<int>(value); return PLX_OK; }
@@ -654,10 +658,11 @@ static void fill_params(plx_bo* h, SweepParams& p, const double* Xc_dev, long lo
 }
 
 // 3-D map over digit planes: `cols` bytes per row, `rows` rows per plane, I8_S planes; box = 64 bytes x box_rows x all planes
-static int make_map_i8(plx_bo* h, CUtensorMap* map, signed char* base, size_t cols, size_t rows, int box_rows) {
+static int make_map_i8(plx_bo* h, CUtensorMap* map, signed char* base, size_t cols, size_t rows, int box_rows,
+                       int box_planes = I8_S) {
   cuuint64_t dims[3] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows), static_cast<cuuint64_t>(I8_S)};
   cuuint64_t strides[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(cols) * rows};
-  cuuint32_t box[3] = {I8_KC, static_cast<cuuint32_t>(box_rows), I8_S};
+  cuuint32_t box[3] = {I8_KC, static_cast<cuuint32_t>(box_rows), static_cast<cuuint32_t>(box_planes)};
   cuuint32_t estr[3] = {1, 1, 1};
   const CUresult r = h->encode(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box, estr,
                                CU_TENSOR_MAP_INTERLEAVE_NONE, I8_KC == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B,
@@ -679,6 +684,7 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     if ((r = ensure(h, h->d_i8mean, h->i8mean_cap, static_cast<size_t>(rows))) != PLX_OK) return r;
     if ((r = make_map_i8(h, &h->tmA8, h->d_kplanes, npad, rows, 128)) != PLX_OK) return r;
     if ((r = make_map_i8(h, &h->tmB8, h->d_zplanes, npad, npad, 64)) != PLX_OK) return r;
+    if ((r = make_map_i8(h, &h->tmA8p, h->d_kplanes, npad, rows, 128, 1)) != PLX_OK) return r;
     h->i8_rows = rows; h->i8_npad = h->npad; h->i8_state_valid = false;
   }
   if (!h->i8_state_valid) {
@@ -689,8 +695,12 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     h->i8_state_valid = true;
   }
   if (e0) CK(cudaEventRecord(e0, st));
-  if (h->sweep_impl == 5 || (h->sweep_impl == 3 && p.n >= 1536)) {
-    // cooperative form: groups of four CTAs share a candidate tile so that the planes in flight stay in L2
+  if (h->sweep_impl == 5 || h->sweep_impl == 6 || (h->sweep_impl == 3 && p.n >= 1536)) {
+    // cooperative forms: groups of four CTAs share a candidate tile so that the planes in flight stay in L2.
+    // 6: the four are two clusters of two that fetch the A stream once per pair (TMA multicast); measured equal to 5
+    // (8.3 ms against 8.2 ms per 151 552 candidates: what a CTA receives, not what L2 reads, bounds the stream), so
+    // the default stays with the plain cooperative form
+    const bool paired = h->sweep_impl == 6;
     const int max_groups = h->num_sms / I8C_R;
     const int groups = static_cast<int>(std::min<long long>((p.N + 127) / 128, max_groups));
     if ((r = ensure(h, h->d_i8part, h->i8part_cap, static_cast<size_t>(max_groups) * 2 * I8C_R * 256)) != PLX_OK) return r;
@@ -702,10 +712,37 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     ip.N = p.N; ip.idx_base = p.idx_base; ip.n = p.n; ip.zscale = h->d_zscale; ip.mean = nullptr;
     ip.acq = p.acq; ip.kappa = p.kappa; ip.eps = p.eps; ip.y_max = p.y_max;
     ip.out_mean = p.out_mean; ip.out_std = p.out_std; ip.out_acq = p.out_acq;
-    ip.blk_val = h->d_blk_val; ip.blk_idx = h->d_blk_idx; ip.a_from_smem = h->i8_a_from_smem;
+    ip.blk_val = h->d_blk_val; ip.blk_idx = h->d_blk_idx; ip.a_from_smem = h->i8_a_from_smem; ip.zplanes_dbg = h->d_zplanes;
     // cooperative launch: the runtime starts the grid only when all its CTAs can be resident at once, which the
     // spin-waits between the CTAs of a group rely on (two such sweeps from different handles then run one after
     // the other instead of starving each other)
+    if (paired) {
+      void* args[] = {&h->tmA8p, &h->tmB8, &q, &ip, &h->d_i8part, &h->d_i8sync};
+      cudaLaunchConfig_t cfg{};
+      cfg.gridDim = dim3(groups * I8C_R); cfg.blockDim = dim3(512); cfg.dynamicSmemBytes = I8F_SMEM; cfg.stream = st;
+      cudaLaunchAttribute attrs[2];
+      attrs[0].id = cudaLaunchAttributeClusterDimension;
+      attrs[0].val.clusterDim.x = 2; attrs[0].val.clusterDim.y = 1; attrs[0].val.clusterDim.z = 1;
+      attrs[1].id = cudaLaunchAttributeCooperative;
+      attrs[1].val.cooperative = 1;
+      cfg.attrs = attrs;
+      cfg.numAttrs = h->coop_cluster_ok ? 2 : 1;
+      cudaError_t le = cudaLaunchKernelExC(&cfg, reinterpret_cast<const void*>(sweep_i8p_kernel), args);
+      if (le != cudaSuccess && cfg.numAttrs == 2) {
+        // a driver that refuses cooperative + cluster: the grid has one CTA per SM at most, so on an otherwise idle
+        // GPU all of it is resident anyway
+        (void)cudaGetLastError();
+        h->coop_cluster_ok = 0;
+        cfg.numAttrs = 1;
+        le = cudaLaunchKernelExC(&cfg, reinterpret_cast<const void*>(sweep_i8p_kernel), args);
+      }
+      CK(le);
+      LAUNCH_CHECK("sweep_i8p_kernel");
+      sweep_merge_kernel<<<1, 32, 0, st>>>(h->d_blk_val, h->d_blk_idx, groups * I8C_R, h->d_best_val, h->d_best_idx);
+      LAUNCH_CHECK("sweep_merge_kernel");
+      if (e1) CK(cudaEventRecord(e1, st));
+      return PLX_OK;
+    }
     {
       void* args[] = {&h->tmA8, &h->tmB8, &q, &ip, &h->d_i8part, &h->d_i8sync};
       CK(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(sweep_i8c_kernel), dim3(groups * I8C_R), dim3(512), args,
@@ -726,7 +763,7 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     ip.N = p.N; ip.idx_base = p.idx_base; ip.n = p.n; ip.zscale = h->d_zscale; ip.mean = nullptr;
     ip.acq = p.acq; ip.kappa = p.kappa; ip.eps = p.eps; ip.y_max = p.y_max;
     ip.out_mean = p.out_mean; ip.out_std = p.out_std; ip.out_acq = p.out_acq;
-    ip.blk_val = h->d_blk_val; ip.blk_idx = h->d_blk_idx; ip.a_from_smem = h->i8_a_from_smem;
+    ip.blk_val = h->d_blk_val; ip.blk_idx = h->d_blk_idx; ip.a_from_smem = h->i8_a_from_smem; ip.zplanes_dbg = h->d_zplanes;
     sweep_i8f_kernel<<<grid, 512, I8F_SMEM, st>>>(h->tmA8, h->tmB8, q, ip, h->d_i8mean);
     LAUNCH_CHECK("sweep_i8f_kernel");
     sweep_merge_kernel<<<1, 32, 0, st>>>(h->d_blk_val, h->d_blk_idx, grid, h->d_best_val, h->d_best_idx);
@@ -748,7 +785,7 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     ip.out_mean = p.out_mean ? p.out_mean + base : nullptr;
     ip.out_std = p.out_std ? p.out_std + base : nullptr;
     ip.out_acq = p.out_acq ? p.out_acq + base : nullptr;
-    ip.blk_val = h->d_blk_val; ip.blk_idx = h->d_blk_idx; ip.a_from_smem = h->i8_a_from_smem;
+    ip.blk_val = h->d_blk_val; ip.blk_idx = h->d_blk_idx; ip.a_from_smem = h->i8_a_from_smem; ip.zplanes_dbg = h->d_zplanes;
     sweep_i8_kernel<<<grid, 192, I8_SMEM, st>>>(h->tmA8, h->tmB8, ip);
     LAUNCH_CHECK("sweep_i8_kernel");
     sweep_merge_kernel<<<1, 32, 0, st>>>(h->d_blk_val, h->d_blk_idx, grid, h->d_best_val, h->d_best_idx);

@@ -28,7 +28,10 @@
 
 namespace plx {
 
-constexpr int I8_KC = 64;                             // observations (= bytes) per K chunk: 32 or 64 (measured equal)
+#ifndef PLX_I8_KC
+#define PLX_I8_KC 64
+#endif
+constexpr int I8_KC = PLX_I8_KC;                      // observations (= bytes) per K chunk: 32 or 64
 constexpr int I8_KSTEPS = I8_KC / 32;                 // k32 tensor instructions per chunk and digit pair
 constexpr int I8_CPH = 64 / I8_KC;                    // chunks per 64 observations
 constexpr int I8_A_SLICE = 128 * I8_KC;               // one plane of the candidate tile chunk
@@ -49,6 +52,7 @@ struct I8Params {
   double kappa, eps, y_max;
   double* out_mean; double* out_std; double* out_acq;       // optional dumps, indexed like the candidates of this launch
   double* blk_val; long long* blk_idx;
+  const signed char* zplanes_dbg;   // PLX_PROFILE experiments only
   int a_from_smem;             // 1: both tensor-core operands from shared memory (A/B measurement), 0: A planes via tensor memory
 };
 
@@ -149,48 +153,52 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&u)[16]) {
 }
 
 // Drain of one finished half-block for one candidate (= TMEM lane): the I8_S class accumulators of 64 columns are
-// recombined in FP64, smallest class first, scaled by zs[.] and their squares added to sumsq.  The loads of several
-// classes are in flight together (one wait per batch: the round trip of tcgen05.ld, not its bandwidth, is what
-// the tensor pipe waits for while TMEM cannot be double-buffered), and the accumulators are handed back
-// (bar_acce) as soon as the last load has landed, before the arithmetic on it.
+// recombined, scaled by zs[.] and their squares added to sumsq.  The recombination is done in INTEGER arithmetic:
+// classes 0..3 and classes 4..6 are each folded into one 64-bit integer (|sum of a class| < 2^28, so 2^52 and 2^44:
+// exact), and only those two are converted to FP64 and added (one rounding, against seven in an FMA chain over the
+// classes).  This matters for speed, not only accuracy: the FP64 pipe is shared with the eight builder warps, and the
+// accumulators can only be handed back to the tensor pipe (bar_acce) when the last tcgen05.ld has landed, which the
+// FP64 work of the earlier columns used to delay.  The loads of several classes are in flight together (one wait per
+// batch: the round trip of tcgen05.ld, not its bandwidth, is what the tensor pipe waits for while TMEM cannot be
+// double-buffered).
 __device__ __forceinline__ void drain_halfblock(uint32_t taddr, const double* __restrict__ zs, double& sumsq,
                                                 uint32_t bar_acce) {
-  constexpr int HI = (I8_S + 1) / 2;                     // classes I8_S-1 .. I8_S-HI first, then the rest
+  static_assert(I8_S == 7, "the integer recombination below is written for 7 digit planes");
+  const double w_hi = __longlong_as_double(static_cast<long long>(1023 - 40) << 52);   // 256^-(3+2): class 3 is the unit of `hi`
+  const double w_lo = __longlong_as_double(static_cast<long long>(1023 - 64) << 52);   // 256^-(6+2): class 6 is the unit of `lo`
 #pragma unroll 1
   for (int c0 = 0; c0 < 64; c0 += 16) {
-    double v[16];
-#pragma unroll
-    for (int i = 0; i < 16; ++i) v[i] = 0.0;
+    long long hi[16], lo[16];
     {
-      uint32_t u[HI][16];
+      uint32_t u[4][16];
 #pragma unroll
-      for (int k = 0; k < HI; ++k) tmem_ld16(taddr + (I8_S - 1 - k) * 64 + c0, u[k]);
+      for (int k = 0; k < 4; ++k) tmem_ld16(taddr + k * 64 + c0, u[k]);
       asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
 #pragma unroll
-      for (int k = 0; k < HI; ++k) {
-        const double w = __longlong_as_double(static_cast<long long>(1023 - 8 * (I8_S - 1 - k + 2)) << 52);   // 256^-(cls+2)
-#pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] = fma(static_cast<double>(static_cast<int>(u[k][i])), w, v[i]);
-      }
+      for (int i = 0; i < 16; ++i)
+        hi[i] = ((static_cast<long long>(static_cast<int>(u[0][i])) * 256 + static_cast<int>(u[1][i])) * 256 +
+                 static_cast<int>(u[2][i])) * 256 + static_cast<int>(u[3][i]);
     }
     {
-      uint32_t u[I8_S - HI][16];
+      uint32_t u[3][16];
 #pragma unroll
-      for (int k = 0; k < I8_S - HI; ++k) tmem_ld16(taddr + (I8_S - HI - 1 - k) * 64 + c0, u[k]);
+      for (int k = 0; k < 3; ++k) tmem_ld16(taddr + (4 + k) * 64 + c0, u[k]);
       asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
       if (c0 == 48) {                                     // every column of every class has been read
         asm volatile("tcgen05.fence::before_thread_sync;\n");
         mbar_arrive(bar_acce);
       }
 #pragma unroll
-      for (int k = 0; k < I8_S - HI; ++k) {
-        const double w = __longlong_as_double(static_cast<long long>(1023 - 8 * (I8_S - HI - 1 - k + 2)) << 52);
-#pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] = fma(static_cast<double>(static_cast<int>(u[k][i])), w, v[i]);
-      }
+      for (int i = 0; i < 16; ++i)
+        lo[i] = (static_cast<long long>(static_cast<int>(u[0][i])) * 256 + static_cast<int>(u[1][i])) * 256 +
+                static_cast<int>(u[2][i]);
     }
 #pragma unroll
-    for (int i = 0; i < 16; ++i) { const double x = v[i] * zs[c0 + i]; sumsq = fma(x, x, sumsq); }
+    for (int i = 0; i < 16; ++i) {
+      const double v = fma(static_cast<double>(hi[i]), w_hi, static_cast<double>(lo[i]) * w_lo);
+      const double x = v * zs[c0 + i];
+      sumsq = fma(x, x, sumsq);
+    }
   }
 }
 

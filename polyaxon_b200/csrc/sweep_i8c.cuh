@@ -167,6 +167,19 @@ __global__ void __launch_bounds__(512, 1) sweep_i8c_kernel(const __grid_constant
             mbar_wait(bar0 + 8 * (I8_STAGES + s), ph ^ 1);
             const uint32_t full = bar0 + 8 * s;
             mbar_expect_tx(full, I8_STAGE);
+#ifdef PLX_PROFILE
+            if (PLX_DBG(p.dbg, 256)) {
+              // experiment: the same bytes as two contiguous bulk copies (what a chunk-major plane layout would allow)
+              const int nch = p.npad / I8_KC;
+              const signed char* srcA = p.planes + (static_cast<size_t>(g * 2 + b) * nch + kc) * I8_A_BYTES;
+              const signed char* srcB = ip.zplanes_dbg + (static_cast<size_t>(h) * nch + kc) * I8_B_BYTES;
+              asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n"
+                           :: "r"(s0 + s * I8_STAGE), "l"(srcA), "r"(I8_A_BYTES), "r"(full) : "memory");
+              asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n"
+                           :: "r"(s0 + s * I8_STAGE + I8_A_BYTES), "l"(srcB), "r"(I8_B_BYTES), "r"(full) : "memory");
+              continue;
+            }
+#endif
             tma_load_3d(s0 + s * I8_STAGE, &tmA, kc * I8_KC, buf_row0 + 128 * static_cast<int>(b), 0, full);
             tma_load_3d(s0 + s * I8_STAGE + I8_A_BYTES, &tmB, kc * I8_KC, h * 64, 0, full);
           }

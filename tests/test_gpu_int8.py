@@ -1,4 +1,4 @@
-"""The int8-sliced sweeps (sweep_i8*.cuh: cooperative = 5, fused = 4, two kernels = 2) at sizes and in corners the
+"""The int8-sliced sweeps (sweep_i8*.cuh: paired cooperative = 6, cooperative = 5, fused = 4, two kernels = 2) at sizes and in corners the
 goldens do not reach, against the CPU oracle and against the FP64 DMMA kernel (1).
 
 Tolerances as in test_gpu_parity.py: posterior variance 1e-9 absolute (k(x,x) = 1) -- max(1e-9, 100 eps cond(K)) on
@@ -15,7 +15,7 @@ from oracle.reference_path import synthetic_problem
 
 pytestmark = pytest.mark.gpu
 EPS = np.finfo(float).eps
-INT8_IMPLS = (5, 4, 2)
+INT8_IMPLS = (6, 5, 4, 2)
 
 
 @pytest.fixture(scope='module')

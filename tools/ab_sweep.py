@@ -14,7 +14,7 @@ h.set_theta(1.2)
 rs = np.random.RandomState(0)
 Xc = rs.uniform(0, 1, (N, d))
 ref = None
-for impl in (1, 2, 4, 5):
+for impl in (1, 2, 4, 5, 6):
     h.set_option('sweep_impl', impl)
     ms = []
     for _ in range(3):

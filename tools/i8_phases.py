@@ -16,7 +16,7 @@ xc = torch.rand(N, d, dtype=torch.float64, device='cuda')
 torch.cuda.synchronize()
 h.set_option('sweep_impl', int(sys.argv[1]) if len(sys.argv) > 1 else 5)
 h.set_option('i8_operand', int(sys.argv[2]) if len(sys.argv) > 2 else 0)
-for dbg in (0, 64, 128, 64 | 128):
+for dbg in [int(a) for a in sys.argv[3].split(',')] if len(sys.argv) > 3 else (0, 64, 128, 64 | 128):
     h.set_option('sweep_dbg', dbg)
     ms = []
     for _ in range(3):
