@@ -54,6 +54,11 @@ int plx_bo_set_stream(plx_bo_handle h, void* stream);
  * 1 = always FP64 DMMA with the TMA ring; 0 = plain-load cross-check); "i8_operand" (0 [default] = the digit planes of
  * the candidate tile reach the tensor core through tensor memory, 1 = both operands from shared memory; same
  * results, kept for A/B timing);
+ * "fit_small" (1 [default]: with at most 64 observations plx_gp_fit runs every optimiser run from start to
+ * convergence in ONE launch, optimiser included; 2: the same up to 128 observations (slower than the batched
+ * sequence there, kept for tests); 0: always the batched launch sequence used for larger sets);
+ * "refine_persist" (1 [default]: with at most 256 observations plx_acq_refine runs every seed from start to
+ * convergence in one launch; 0: four launches per round, as for larger sets);
  * "fit_apply" (1 [default]: plx_gp_fit ends by building the posterior state at the best theta; 0: it returns the
  * optimiser runs only -- a rank's share of a fit whose runs are dealt to several GPUs);
  * "lml_batch_limit" (k > 0: at most k thetas per pass of plx_gp_lml / plx_gp_fit; 0 = as many as fit

@@ -5,6 +5,7 @@
 #include "append.cuh"
 #include "sweep_i8p.cuh"
 #include "mt19937.cuh"
+#include "fit_small.cuh"
 
 #include <cstdio>
 #include <cstdlib>
@@ -81,7 +82,8 @@ struct plx_bo {
   double* d_out[3] = {nullptr, nullptr, nullptr}; size_t out_cap = 0;
   cudaEvent_t ev_copy[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
   std::vector<cudaEvent_t> ev_pool;
-  int sweep_impl = 3, sweep_dbg = 0, lml_batch_limit = 0, i8_a_from_smem = 0, fit_apply = 1;      // 3 = choose per GP state, see launch_sweep
+  int sweep_impl = 3, sweep_dbg = 0, lml_batch_limit = 0, i8_a_from_smem = 0, fit_apply = 1, fit_small = 1, refine_persist = 1;
+  double* d_fs = nullptr; size_t fs_cap = 0;      // one-launch fit (fit_small.cuh): starts | per-run results      // 3 = choose per GP state, see launch_sweep
   double last_ms = 0.0; long long last_launches = 0;
 
   // resident candidate matrix (iteration-invariant for a seeded group)
@@ -231,6 +233,10 @@ extern "C" int plx_bo_create(int device, plx_bo_handle* out) {
   cudaFuncSetAttribute(sweep_i8c_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, I8F_SMEM);
   cudaFuncSetAttribute(sweep_i8p_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, I8F_SMEM);
   cudaFuncSetAttribute(kstar_slices_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, KSL_SMEM);
+  cudaFuncSetAttribute(refine_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                       static_cast<int>(sizeof(double) * rf_persist_smem_doubles(RF_PERSIST_ZSMEM, RF_PERSIST_ZSMEM, RF_PERSIST_DSMEM)));
+  cudaFuncSetAttribute(fit_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FS_SMEM);
+  cudaFuncSetAttribute(state_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FS_SMEM);
   cudaFuncSetAttribute(mt19937_draw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                        static_cast<int>(sizeof(unsigned) * MT_SEQ + sizeof(double) * 2 * 2048));
   if (cudaGetLastError() != cudaSuccess) return bail("cudaFuncSetAttribute failed (is the library built for this GPU?)");
@@ -252,7 +258,7 @@ extern "C" void plx_bo_destroy(plx_bo_handle h) {
                   h->d_blk_val, h->d_blk_idx, h->d_best_val, h->d_best_idx, h->dcand[0], h->dcand[1],
                   h->d_out[0], h->d_out[1], h->d_out[2], h->rf_kv, h->rf_kp, h->rf_v, h->rf_w, h->rf_vec,
                   h->rf_bounds, h->rf_val, h->rf_grad, h->rf_sc, h->rf_active, h->d_resident, h->d_misc, h->d_app,
-                  h->d_kplanes, h->d_zplanes, h->d_zscale, h->d_i8mean, h->d_i8part, h->d_i8sync};
+                  h->d_kplanes, h->d_zplanes, h->d_zscale, h->d_i8mean, h->d_i8part, h->d_i8sync, h->d_fs};
   for (void* p : ptrs) if (p) cudaFree(p);
   for (int i = 0; i < 2; ++i) { if (h->ev_copy[i]) cudaEventDestroy(h->ev_copy[i]); if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]); }
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
@@ -272,6 +278,8 @@ extern "C" int plx_bo_set_option(plx_bo_handle h, const char* name, long long va
   if (!h || !name) return PLX_ERR_INVALID;
   if (std::strcmp(name, "sweep_impl") == 0 && value >= 0 && value <= 6) { h->sweep_impl = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "lml_batch_limit") == 0 && value >= 0) { h->lml_batch_limit = static_cast<int>(value); return PLX_OK; }
+  if (std::strcmp(name, "refine_persist") == 0 && (value == 0 || value == 1)) { h->refine_persist = static_cast<int>(value); return PLX_OK; }
+  if (std::strcmp(name, "fit_small") == 0 && value >= 0 && value <= 2) { h->fit_small = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "fit_apply") == 0 && (value == 0 || value == 1)) { h->fit_apply = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "i8_operand") == 0 && (value == 0 || value == 1)) { h->i8_a_from_smem = static_cast<int>(value); return PLX_OK; }
 #ifdef PLX_PROFILE
@@ -491,12 +499,19 @@ extern "C" int plx_gp_set_theta(plx_bo_handle h, double theta) {
   if (!h->have_data) return fail(h, PLX_ERR_STATE, "gp_set_theta: call plx_gp_set_data first");
   CK(cudaSetDevice(h->device));
   h->have_state = false;
-  double lml;
-  int r = eval_lml(h, &theta, 1, &lml, nullptr);
-  if (r != PLX_OK) return r;
-  if (std::isinf(lml) && lml < 0)
-    return fail(h, PLX_ERR_NOT_PD, "kernel matrix is not positive definite at theta=" + std::to_string(theta));
+  int r;
   const size_t mat = static_cast<size_t>(h->npad) * h->npad;
+  const bool small = h->fit_small && h->n <= (h->fit_small == 2 ? FS_NMAX : FS_NUSE);
+  if (small) {
+    if ((r = ensure_batch(h, 1)) != PLX_OK) return r;           // L lives in the fit workspace (plx_gp_get_state, plx_gp_append)
+    h->state_factor_valid = false;
+  } else {
+    double lml;
+    r = eval_lml(h, &theta, 1, &lml, nullptr);
+    if (r != PLX_OK) return r;
+    if (std::isinf(lml) && lml < 0)
+      return fail(h, PLX_ERR_NOT_PD, "kernel matrix is not positive definite at theta=" + std::to_string(theta));
+  }
   if ((r = ensure(h, h->dZ, h->z_cap, mat)) != PLX_OK) return r;
   if ((r = ensure(h, h->d_alpha_state, h->as_cap, static_cast<size_t>(h->npad))) != PLX_OK) return r;
   if ((r = ensure(h, h->dKs, h->ks_cap, static_cast<size_t>(h->num_sms) * 128 * h->npad)) != PLX_OK) return r;
@@ -504,10 +519,26 @@ extern "C" int plx_gp_set_theta(plx_bo_handle h, double theta) {
   scale_transpose_x_kernel<<<dim3((h->npad + 255) / 256, h->d), 256, 0, h->stream>>>(h->dX, h->n, h->d, h->npad,
                                                                                    std::exp(theta), h->dXt);
   LAUNCH_CHECK("scale_transpose_x_kernel");
-  transpose_kernel<<<dim3(h->npad / 32, h->npad / 32), 256, 0, h->stream>>>(h->bp.U, h->dZ, h->npad);
-  LAUNCH_CHECK("transpose_kernel");
-  CK(cudaMemcpyAsync(h->d_alpha_state, h->d_alpha, sizeof(double) * h->npad, cudaMemcpyDeviceToDevice, h->stream));
-  CK(cudaStreamSynchronize(h->stream));
+  if (small) {
+    // small observation sets: factor, inverse and alpha in one launch of one CTA (fit_small.cuh)
+    if ((r = ensure(h, h->d_fs, h->fs_cap, 8)) != PLX_OK) return r;
+    if ((r = ensure(h, h->d_xs, h->xs_cap, static_cast<size_t>(h->n) * h->d)) != PLX_OK) return r;
+    FitSmallParams fp{};
+    fp.X = h->dX; fp.y = h->dy; fp.n = h->n; fp.d = h->d; fp.kind = h->kind; fp.R = 1; fp.mg = h->mg;
+    fp.jitter = h->jitter; fp.xs = h->d_xs;
+    state_small_kernel<<<1, FS_THREADS, FS_SMEM, h->stream>>>(fp, theta, h->npad, h->bp.L, h->dZ, h->d_alpha_state, h->d_fs);
+    LAUNCH_CHECK("state_small_kernel");
+    double st[2] = {0.0, 0.0};
+    CK(cudaMemcpyAsync(st, h->d_fs, sizeof(double) * 2, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    if (st[0] != 0.0)
+      return fail(h, PLX_ERR_NOT_PD, "kernel matrix is not positive definite at theta=" + std::to_string(theta));
+  } else {
+    transpose_kernel<<<dim3(h->npad / 32, h->npad / 32), 256, 0, h->stream>>>(h->bp.U, h->dZ, h->npad);
+    LAUNCH_CHECK("transpose_kernel");
+    CK(cudaMemcpyAsync(h->d_alpha_state, h->d_alpha, sizeof(double) * h->npad, cudaMemcpyDeviceToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+  }
   if ((r = make_map(h, &h->tmZ, h->dZ, h->npad, h->npad)) != PLX_OK) return r;
   if ((r = make_map(h, &h->tmK, h->dKs, static_cast<size_t>(h->num_sms) * 128, h->npad)) != PLX_OK) return r;
   h->theta = theta; h->have_state = true; h->state_factor_valid = true; h->i8_state_valid = false;
@@ -613,6 +644,30 @@ extern "C" int plx_gp_fit(plx_bo_handle h, double theta0, const double* theta_re
   if (!h->have_data) return fail(h, PLX_ERR_STATE, "gp_fit: call plx_gp_set_data first");
   CK(cudaSetDevice(h->device));
   const int R = n_restarts + 1;
+  if (h->fit_small && h->n <= (h->fit_small == 2 ? FS_NMAX : FS_NUSE)) {
+    // small observation sets: every run from start to convergence in one launch (fit_small.cuh)
+    int r;
+    if ((r = ensure(h, h->d_fs, h->fs_cap, static_cast<size_t>(5) * R)) != PLX_OK) return r;
+    if ((r = ensure(h, h->d_xs, h->xs_cap, static_cast<size_t>(R) * h->n * h->d)) != PLX_OK) return r;
+    std::vector<double> st(R), out(static_cast<size_t>(4) * R);
+    for (int i = 0; i < R; ++i) st[i] = (i == 0) ? theta0 : theta_restarts[i - 1];
+    CK(cudaMemcpyAsync(h->d_fs, st.data(), sizeof(double) * R, cudaMemcpyHostToDevice, h->stream));
+    FitSmallParams fp;
+    fp.X = h->dX; fp.y = h->dy; fp.n = h->n; fp.d = h->d; fp.kind = h->kind; fp.R = R; fp.mg = h->mg;
+    fp.jitter = h->jitter; fp.lo = theta_lo; fp.hi = theta_hi; fp.starts = h->d_fs; fp.xs = h->d_xs;
+    fp.per_run = h->d_fs + R;
+    fit_small_kernel<<<R, FS_THREADS, FS_SMEM, h->stream>>>(fp);
+    LAUNCH_CHECK("fit_small_kernel");
+    CK(cudaMemcpyAsync(out.data(), h->d_fs + R, sizeof(double) * 4 * R, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    int best = 0;
+    for (int i = 1; i < R; ++i) if (-out[4 * i + 2] < -out[4 * best + 2]) best = i;     // first minimum of -LML
+    if (per_run) std::memcpy(per_run, out.data(), sizeof(double) * 4 * R);
+    if (theta_star) *theta_star = out[4 * best + 1];
+    if (lml_star) *lml_star = out[4 * best + 2];
+    if (!h->fit_apply) return PLX_OK;
+    return plx_gp_set_theta(h, out[4 * best + 1]);
+  }
   std::vector<Lbfgsb1D> runs(R);
   std::vector<double> starts(R);
   for (int r = 0; r < R; ++r) {
@@ -1181,6 +1236,13 @@ extern "C" int plx_acq_refine(plx_bo_handle h, const double* seeds, int S, const
   const long long max_rounds = 15000;                  // scipy's maxfun
   int active = S;
   long long rounds = 0;
+  if (h->refine_persist && h->n <= RF_PERSIST_NMAX) {
+    // small observation sets: every seed start to finish in one launch (refine.cuh)
+    refine_persist_kernel<<<S, 128, sizeof(double) * rf_persist_smem_doubles(p.n, p.npad, p.d), h->stream>>>(
+        p, static_cast<int>(max_rounds));
+    LAUNCH_CHECK("refine_persist_kernel");
+    active = 0;
+  }
   while (active > 0 && rounds < max_rounds) {
     for (int k = 0; k < 4 && rounds < max_rounds; ++k, ++rounds)
       if ((r = launch_refine_round(h, p)) != PLX_OK) return r;

@@ -163,24 +163,24 @@ struct Lbfgsb1D {
 
   static constexpr double epsmch = 2.220446049250313e-16;
 
-  double projgr() const {
+  PLX_HD double projgr() const {
     double gi = g;
-    if (gi < 0.0) gi = std::max(x - hi, gi); else gi = std::min(x - lo, gi);
-    return std::fabs(gi);
+    if (gi < 0.0) gi = hd_max(x - hi, gi); else gi = hd_min(x - lo, gi);
+    return hd_abs(gi);
   }
 
-  void start(double x0) {
-    x = std::min(std::max(x0, lo), hi);
+  PLX_HD void start(double x0) {
+    x = hd_min(hd_max(x0, lo), hi);
     x_eval = x; waiting_first = true; done = false; iter = 0; nfev = 0; have_pair = false; B = 1.0;
   }
 
-  void finish(int st, const char* msg) { done = true; status = st; message = msg; }
+  PLX_HD void finish(int st, const char* msg) { done = true; status = st; message = msg; }
 
-  void begin_iteration() {
+  PLX_HD void begin_iteration() {
     for (;;) {
       // generalised Cauchy point of the one-variable quadratic model
       const double neggi = -g;
-      double tb = INFINITY;
+      double tb = HUGE_VAL;
       if (neggi < 0.0) tb = (x - lo) / (-neggi); else if (neggi > 0.0) tb = (hi - x) / neggi;
       const double dtm = 1.0 / (have_pair ? B : 1.0);
       if (dtm < tb) z = x + dtm * neggi; else z = (neggi < 0.0) ? lo : hi;
@@ -199,7 +199,7 @@ struct Lbfgsb1D {
 
   // returns true when the machine is waiting for f/g at x_eval or has finished;
   // false when the caller must restart the iteration with a reset model
-  bool line_search_step(bool first) {
+  PLX_HD bool line_search_step(bool first) {
     gd = g * d;
     bool fail = false;
     if (first) { gdold = gd; if (gd >= 0.0) fail = true; }
@@ -230,12 +230,12 @@ struct Lbfgsb1D {
     return false;
   }
 
-  void finish_iteration() {
+  PLX_HD void finish_iteration() {
     ++iter;
     if (iter >= maxiter) { finish(1, "STOP: TOTAL NO. OF ITERATIONS REACHED LIMIT"); return; }
     if (nfev > maxfun) { finish(1, "STOP: TOTAL NO. OF F,G EVALUATIONS EXCEEDS LIMIT"); return; }
     if (projgr() <= pgtol) { finish(0, "CONVERGENCE: NORM OF PROJECTED GRADIENT <= PGTOL"); return; }
-    const double ddum0 = std::max(std::fabs(ft), std::max(std::fabs(f), 1.0));
+    const double ddum0 = hd_max(hd_abs(ft), hd_max(hd_abs(f), 1.0));
     if (ft - f <= epsmch * factr * ddum0) { finish(0, "CONVERGENCE: RELATIVE REDUCTION OF F <= FACTR*EPSMCH"); return; }
     const double r = g - gt, rr = r * r;
     double dr, ddum;
@@ -246,7 +246,7 @@ struct Lbfgsb1D {
   }
 
   // hand the objective and derivative at x_eval back to the machine
-  void feed(double fval, double gval) {
+  PLX_HD void feed(double fval, double gval) {
     if (done) return;
     f = fval; g = gval;
     if (waiting_first) {

@@ -320,18 +320,16 @@ __device__ void rf_advance(const RefineParams& p, int s, RefineScalars& sc, int 
   rf_begin_iteration(p, s, sc, lane);
 }
 
-// One CTA (128 threads) per seed: reductions over the observations, the acquisition and its
-// gradient, then (unless in evaluation-only mode) one optimiser transition by warp 0.
-__global__ void __launch_bounds__(128) refine_step_kernel(RefineParams p) {
+// Reductions over the observations for seed s, the acquisition and its gradient, then (unless in evaluation-only
+// mode) one optimiser transition by warp 0.  Called by all 128 threads of a CTA; grad_smem holds 2 d doubles.
+__device__ __forceinline__ void refine_step_body(const RefineParams& p, int s, double* grad_smem) {
   __shared__ double red_mu[4], red_s2[4];
   __shared__ double gsum[4][2][32];
-  extern __shared__ double rf_grad_smem[];        // gm[d] | gv[d]
-  double* gm = rf_grad_smem;
-  double* gv = rf_grad_smem + p.d;
   __shared__ double sh_mu, sh_s2;
-  const int s = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double* gm = grad_smem;
+  double* gv = grad_smem + p.d;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const bool eval_only = p.val_out != nullptr;
-  if (!eval_only && p.sc[s].phase == 2) return;
   const double* kv = p.kv + static_cast<size_t>(s) * p.npad;
   const double* kp = p.kp + static_cast<size_t>(s) * p.npad;
   const double* v = p.v + static_cast<size_t>(s) * p.npad;
@@ -394,6 +392,125 @@ __global__ void __launch_bounds__(128) refine_step_kernel(RefineParams p) {
   sc.f = -acq;
   rf_advance(p, s, sc, lane);
   if (lane == 0) p.sc[s] = sc;
+}
+
+// One CTA (128 threads) per seed, one round: used with refine_kstar / refine_v / refine_w kernels for large n.
+__global__ void __launch_bounds__(128) refine_step_kernel(RefineParams p) {
+  extern __shared__ double rf_grad_smem[];        // gm[d] | gv[d]
+  const int s = blockIdx.x;
+  if (p.val_out == nullptr && p.sc[s].phase == 2) return;
+  refine_step_body(p, s, rf_grad_smem);
+}
+
+// The whole refinement of a seed in ONE launch (n <= RF_PERSIST_NMAX): the CTA of seed s loops over rounds -- k* and
+// its derivative, v = L^-1 k*, w = L^-T v, acquisition, gradient and the optimiser transition -- until the seed has
+// converged.  Same arithmetic and the same state machine as the round-by-round kernels above, which need four
+// launches per round and a device->host check every few rounds: for small n that latency was the whole cost (config
+// C1: 0.7 ms for microseconds of arithmetic).  The seed's optimiser vectors and k*, v, w live in shared memory for
+// the duration (when they fit: d <= RF_PERSIST_DSMEM), and so does L^-1 up to 128 observations (128 KB); above that
+// it is streamed from L2, several rows in flight per warp.
+constexpr int RF_PERSIST_NMAX = 256;
+constexpr int RF_PERSIST_DSMEM = 256;             // per-seed vectors in shared memory up to this many dimensions
+constexpr int RF_PERSIST_ZSMEM = 128;             // L^-1 in shared memory up to this many observations
+
+// dynamic shared memory of refine_persist_kernel, in doubles (the host passes the same number)
+inline size_t rf_persist_smem_doubles(int n, int npad, int d) {
+  size_t t = static_cast<size_t>(2) * d + static_cast<size_t>(4) * npad;
+  if (d <= RF_PERSIST_DSMEM) t += rf_vec_stride(d);
+  if (n <= RF_PERSIST_ZSMEM) t += static_cast<size_t>(n) * n;
+  return t;
+}
+
+__global__ void __launch_bounds__(128) refine_persist_kernel(RefineParams p, int max_rounds) {
+  extern __shared__ double rf_grad_smem[];        // gm[d] | gv[d] | k* | k*' | v | w | [seed vectors] | [L^-1]
+  __shared__ int sh_phase;
+  const int s = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double* kvs = rf_grad_smem + 2 * p.d;
+  double* kps = kvs + p.npad;
+  double* vs = kps + p.npad;
+  double* ws = vs + p.npad;
+  double* next = ws + p.npad;
+  // q: the view of this seed with its working vectors redirected to shared memory (index s still selects them)
+  RefineParams q = p;
+  q.kv = kvs - static_cast<size_t>(s) * p.npad; q.kp = kps - static_cast<size_t>(s) * p.npad;
+  q.v = vs - static_cast<size_t>(s) * p.npad; q.w = ws - static_cast<size_t>(s) * p.npad;
+  const bool vec_smem = p.d <= RF_PERSIST_DSMEM;
+  double* gvec = p.vec + static_cast<size_t>(s) * p.vec_stride;
+  if (vec_smem) {
+    for (size_t e = tid; e < p.vec_stride; e += 128) next[e] = gvec[e];
+    q.vec = next - static_cast<size_t>(s) * p.vec_stride;
+    next += p.vec_stride;
+  }
+  const double* Zp = p.Z;
+  int zld = p.npad;
+  if (p.n <= RF_PERSIST_ZSMEM) {
+    for (int e = tid; e < p.n * p.n; e += 128) {
+      const int i = e / p.n, j = e - i * p.n;
+      next[e] = (j <= i) ? p.Z[static_cast<size_t>(i) * p.npad + j] : 0.0;
+    }
+    Zp = next; zld = p.n;
+  }
+  __syncthreads();
+  for (int round = 0; round < max_rounds; ++round) {
+    if (tid == 0) sh_phase = q.sc[s].phase;
+    __syncthreads();
+    if (sh_phase == 2) break;
+    const double* x = rf_x(q, s);
+    for (int j = tid; j < p.npad; j += 128) {
+      double kv = 0.0, kp = 0.0;
+      if (j < p.n) {
+        const double* xj = p.X + static_cast<size_t>(j) * p.d;
+        double r2 = 0.0;
+        for (int c = 0; c < p.d; ++c) { const double df = x[c] / p.ell - xj[c] / p.ell; r2 += df * df; }
+        kv = kern_value(p.kind, r2, p.mg);
+        kp = kern_dr2(p.kind, r2, p.mg);
+      }
+      kvs[j] = kv; kps[j] = kp;
+    }
+    __syncthreads();
+    // v_i = sum_{j <= i} Z[i][j] k*_j: four rows per warp in flight (lane-strided partial sums as in refine_v_kernel)
+    for (int i0 = warp * 4; i0 < p.n; i0 += 16) {
+      double a[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int i = i0 + r;
+        if (i < p.n) {
+          const double* Zi = Zp + static_cast<size_t>(i) * zld;
+          for (int j = lane; j <= i; j += 32) a[r] += Zi[j] * kvs[j];
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) a[r] += __shfl_xor_sync(0xffffffffu, a[r], o);
+        if (lane == 0 && i0 + r < p.n) vs[i0 + r] = a[r];
+      }
+    }
+    __syncthreads();
+    // w_j = sum_{i >= j} Z[i][j] v_i, a thread per column: eight rows in flight (the loads come from L2 above 128
+    // observations, and their latency, not their number, is what a lone CTA waits for)
+    for (int j = tid; j < p.n; j += 128) {
+      double acc[4] = {0.0, 0.0, 0.0, 0.0};
+      int i = j;
+      for (; i + 8 <= p.n; i += 8) {
+        double z[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) z[u] = Zp[static_cast<size_t>(i + u) * zld + j];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) acc[u & 3] += z[u] * vs[i + u];
+      }
+      for (; i < p.n; ++i) acc[0] += Zp[static_cast<size_t>(i) * zld + j] * vs[i];
+      ws[j] = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+    }
+    __syncthreads();
+    refine_step_body(q, s, rf_grad_smem);
+    __syncthreads();
+  }
+  if (vec_smem) {
+    // the host reads the final point (first d doubles of the block); the rest is kept consistent too
+    const double* mine = rf_x(q, s);
+    for (size_t e = tid; e < p.vec_stride; e += 128) gvec[e] = mine[e];
+  }
 }
 
 }  // namespace plx

@@ -164,6 +164,34 @@ def test_fit_reaches_the_reference_optimum(handle, name):
     assert np.allclose(per_run[:, 2], ref[:, 2], rtol=1e-8, atol=1e-7)
 
 
+@pytest.mark.parametrize('name', [n for n in CLOSED_FORM if load_golden(n)['X'].shape[0] <= 128])
+def test_one_launch_fit_equals_the_batched_launch_sequence(handle, name):
+    """Small observation sets (by default up to 64, here forced up to the kernel's capacity of 128) are fitted with
+    every optimiser run from start to convergence inside one kernel (fit_small.cuh: factorisation, gradient and the
+    L-BFGS-B state machine on the device); larger sets use the batched launch sequence driven from the host.  Same optimiser code, the factorisation differs in summation order only."""
+    g = load_golden(name)
+    handle.set_data(g['X'], g['y'], int(g['kernel']), float(g['nu']))
+    starts = np.concatenate([g['theta_inits'], [-3.0, 0.4, 2.5, 9.0, -9.0]])
+    out = {}
+    try:
+        for flag in (2, 0):
+            handle.set_option('fit_small', flag)
+            out[flag] = handle.fit(np.log(float(g['length_scale'])), starts)
+    finally:
+        handle.set_option('fit_small', 1)
+    well = float(g['cond']) < 1e8
+    assert out[2][0] == pytest.approx(out[0][0], abs=1e-6 if well else 1e-3)
+    assert out[2][1] == pytest.approx(out[0][1], rel=1e-9 if well else 1e-6, abs=1e-8)
+    a, b = out[2][2], out[0][2]
+    assert np.array_equal(a[:, 0], b[:, 0])
+    finite = np.isfinite(b[:, 2])
+    assert np.array_equal(np.isfinite(a[:, 2]), finite)
+    assert np.allclose(a[finite, 2], b[finite, 2], rtol=1e-8 if well else 1e-5, atol=1e-7)
+    if well:
+        assert np.allclose(a[:, 1], b[:, 1], atol=1e-5)
+        assert np.array_equal(a[:, 3], b[:, 3])                      # the same number of evaluations per run
+
+
 @pytest.mark.parametrize('n_cand', [0, 1, 127, 128, 129, 1000])
 def test_ragged_candidate_counts(handle, n_cand):
     g = load_golden('c5_d16_n128_m25_ei')

@@ -134,3 +134,24 @@ def test_wide_one_hot_space_is_refined(handle):
         m, s = G.predict(x[None, :], X, L, a, theta, G.KERNEL_MATERN, 2.5)
         assert v == pytest.approx(G.acquisition(m, s, G.ACQ_EI, y_max, 0.0, 0.0)[0], rel=1e-9, abs=1e-13)
         assert v >= v0 - 1e-12                     # never worse than where it started
+
+
+@pytest.mark.parametrize('name', [n for n in WELL if 'n2048' not in n and 'n512' not in n])
+def test_one_launch_refinement_equals_round_by_round(handle, name):
+    """Up to 256 observations every seed is refined from start to finish in one launch (refine_persist_kernel);
+    larger sets take four launches per round.  Same state machine, same arithmetic up to the summation order of
+    one matrix-vector product: the two must land on the same optimum."""
+    g = load_golden(name)
+    handle.set_data(g['X'], g['y'], int(g['kernel']), float(g['nu']))
+    handle.set_theta(float(g['theta']))
+    seeds = np.vstack([g['x_seeds'], g['x_tries_head'][:6]])
+    out = {}
+    try:
+        for flag in (1, 0):
+            handle.set_option('refine_persist', flag)
+            out[flag] = handle.refine(seeds, g['bounds'], want_nfev=True, **_args(g))
+    finally:
+        handle.set_option('refine_persist', 1)
+    assert np.array_equal(out[1][2], out[0][2])                       # success flags
+    assert np.allclose(out[1][1], out[0][1], rtol=1e-8, atol=1e-10)   # values reached
+    assert np.allclose(out[1][0], out[0][0], atol=1e-5)               # points reached
