@@ -65,6 +65,13 @@ int plx_bo_set_stream(plx_bo_handle h, void* stream);
  * in the free device memory, which is also what bounds a batch too large for one pass). */
 int plx_bo_set_option(plx_bo_handle h, const char* name, long long value);
 
+/* Allocate, ahead of time, every workspace a problem of this shape needs (n observations of d encoded dimensions,
+ * `runs` optimiser runs = 1 + n_restarts_optimizer, `seeds` refinement seeds = n_iter, `candidates` resident warm-up
+ * rows = n_warmup; zeros skip a part), so that the first call of a group carries no cudaMalloc.  Workspaces are keyed
+ * on n rounded up to 128.  Call it before plx_gp_set_data.  No counterpart in the reference (numpy allocates as it
+ * goes); the caller is the worker start-up of cmd/celery_worker, once per process. */
+int plx_bo_reserve(plx_bo_handle h, int n, int d, int runs, int seeds, long long candidates);
+
 /* Observations.  Replaces the arguments of GaussianProcessRegressor.fit(X, y) at optimizer.py:21
  * and the kernel construction at acquisition_function.py:36-46.  nu must be 0.5, 1.5, 2.5 or inf
  * for PLX_KERNEL_MATERN; jitter is sklearn's `alpha` (1e-10 in the reference). */

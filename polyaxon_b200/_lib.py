@@ -28,6 +28,7 @@ SIGNATURES = {
     'plx_version': (c_char_p, []),
     'plx_bo_set_stream': (c_int, [c_void_p, c_void_p]),
     'plx_bo_set_option': (c_int, [c_void_p, c_char_p, c_longlong]),
+    'plx_bo_reserve': (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_longlong]),
     'plx_gp_set_data': (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_double, c_double]),
     'plx_gp_lml': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     'plx_gp_fit': (c_int, [c_void_p, c_double, c_void_p, c_int, c_double, c_double, _dp, _dp, c_void_p]),
@@ -136,6 +137,10 @@ class Handle(object):
 
     def set_option(self, name, value):
         self._check(self.lib.plx_bo_set_option(self._h, name.encode(), int(value)))
+
+    def reserve(self, n, d, runs=1, seeds=0, candidates=0):
+        """Allocate the workspaces of an (n, d) problem now, so the first call of a group carries no cudaMalloc."""
+        self._check(self.lib.plx_bo_reserve(self._h, int(n), int(d), int(runs), int(seeds), int(candidates)))
 
     def set_data(self, X, y, kernel, nu=1.5, jitter=1e-10):
         X = _f64(X)

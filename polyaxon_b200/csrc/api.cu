@@ -726,9 +726,8 @@ static int make_map_i8(plx_bo* h, CUtensorMap* map, signed char* base, size_t co
   return PLX_OK;
 }
 
-// Variant 2 (sweep_i8.cuh): chunks of candidates; per chunk the digit planes of K*, then the sliced contraction.
-static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cudaEvent_t e1) {
-  cudaStream_t st = h->stream;
+// plane buffers, row scales and tensor maps of the int8-sliced sweeps for the current padded size
+static int ensure_i8(plx_bo* h) {
   const long long rows = static_cast<long long>(h->num_sms) * 128 * 2;
   const size_t npad = h->npad;
   int r;
@@ -740,8 +739,21 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     if ((r = make_map_i8(h, &h->tmA8, h->d_kplanes, npad, rows, 128)) != PLX_OK) return r;
     if ((r = make_map_i8(h, &h->tmB8, h->d_zplanes, npad, npad, 64)) != PLX_OK) return r;
     if ((r = make_map_i8(h, &h->tmA8p, h->d_kplanes, npad, rows, 128, 1)) != PLX_OK) return r;
+    const int max_groups = h->num_sms / I8C_R;
+    if ((r = ensure(h, h->d_i8part, h->i8part_cap, static_cast<size_t>(max_groups) * 2 * I8C_R * 256)) != PLX_OK) return r;
+    if ((r = ensure(h, h->d_i8sync, h->i8sync_cap, static_cast<size_t>(max_groups) * 8)) != PLX_OK) return r;
     h->i8_rows = rows; h->i8_npad = h->npad; h->i8_state_valid = false;
   }
+  return PLX_OK;
+}
+
+// Variant 2 (sweep_i8.cuh): chunks of candidates; per chunk the digit planes of K*, then the sliced contraction.
+static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cudaEvent_t e1) {
+  cudaStream_t st = h->stream;
+  const long long rows = static_cast<long long>(h->num_sms) * 128 * 2;
+  const size_t npad = h->npad;
+  int r;
+  if ((r = ensure_i8(h)) != PLX_OK) return r;
   if (!h->i8_state_valid) {
     // columns of the K* planes beyond the observations are never written by the slicing kernel: keep them zero
     CK(cudaMemsetAsync(h->d_kplanes, 0, static_cast<size_t>(I8_S) * rows * npad, st));
@@ -1262,6 +1274,48 @@ extern "C" int plx_acq_refine(plx_bo_handle h, const double* seeds, int S, const
     if (nfev_out) nfev_out[s] = sc[s].nfev;
   }
   return PLX_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// plx_bo_reserve: allocate every workspace a problem of the given shape will need, so that the first
+// plx_gp_set_data / plx_gp_fit / plx_acq_sweep* / plx_acq_refine of a group does not pay for cudaMalloc (a
+// device-wide synchronising call) inside its latency.  Workspaces are keyed on the padded observation count
+// (n rounded up to 128): a later problem with the same padded size, at most `runs` optimiser runs, `seeds`
+// refinement seeds and `candidates` resident rows allocates nothing.  The kernels themselves are loaded when
+// the handle is created (every kernel of the library is touched there).
+// ---------------------------------------------------------------------------------------------
+static int ensure_refine(plx_bo* h, int S);
+
+extern "C" int plx_bo_reserve(plx_bo_handle h, int n, int d, int runs, int seeds, long long candidates) {
+  if (!h || n <= 0 || d <= 0 || runs < 0 || seeds < 0 || candidates < 0)
+    return h ? fail(h, PLX_ERR_INVALID, "bo_reserve: bad arguments") : PLX_ERR_INVALID;
+  if (h->have_data) return fail(h, PLX_ERR_STATE, "bo_reserve: call it before plx_gp_set_data");
+  CK(cudaSetDevice(h->device));
+  const int n0 = h->n, d0 = h->d, npad0 = h->npad, nb0 = h->nb;
+  h->n = n; h->d = d; h->npad = (n + 127) / 128 * 128; h->nb = h->npad / 128;
+  int r = PLX_OK;
+  const size_t mat = static_cast<size_t>(h->npad) * h->npad;
+  do {
+    if ((r = ensure(h, h->dX, h->x_cap, static_cast<size_t>(h->npad) * d)) != PLX_OK) break;
+    if ((r = ensure(h, h->dy, h->y_cap, static_cast<size_t>(h->npad))) != PLX_OK) break;
+    if ((r = ensure_batch(h, std::max(runs, 1))) != PLX_OK) break;
+    if ((r = ensure(h, h->d_xs, h->xs_cap, static_cast<size_t>(std::max(runs, 1)) * n * d)) != PLX_OK) break;
+    if ((r = ensure(h, h->d_fs, h->fs_cap, static_cast<size_t>(5) * std::max(runs, 2))) != PLX_OK) break;
+    if ((r = ensure(h, h->dZ, h->z_cap, mat)) != PLX_OK) break;
+    if ((r = ensure(h, h->d_alpha_state, h->as_cap, static_cast<size_t>(h->npad))) != PLX_OK) break;
+    if ((r = ensure(h, h->dKs, h->ks_cap, static_cast<size_t>(h->num_sms) * 128 * h->npad)) != PLX_OK) break;
+    if ((r = ensure(h, h->dXt, h->xt_cap, static_cast<size_t>(d) * h->npad)) != PLX_OK) break;
+    if (n >= 256 && (r = ensure_i8(h)) != PLX_OK) break;
+    if (seeds > 0 && (r = ensure_refine(h, seeds)) != PLX_OK) break;
+    if (candidates > 0) {
+      if ((r = ensure(h, h->d_resident, h->resident_cap, static_cast<size_t>(candidates) * d)) != PLX_OK) break;
+      if ((r = ensure(h, h->d_misc, h->misc_cap, static_cast<size_t>(2 * d) + 640)) != PLX_OK) break;
+    }
+    if ((r = need_events(h, 2)) != PLX_OK) break;
+  } while (false);
+  h->n = n0; h->d = d0; h->npad = npad0; h->nb = nb0;
+  if (r == PLX_OK) CK(cudaDeviceSynchronize());
+  return r;
 }
 
 // ---------------------------------------------------------------------------------------------

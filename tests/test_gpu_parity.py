@@ -318,3 +318,26 @@ def test_inner_loop_kernel_values_to_a_few_ulp(handle, kernel, nu):
     ulp = np.abs(got[ok] - want[ok]) / np.spacing(want[ok])
     assert ulp.max() <= 4.0, ulp.max()
     assert got[0] == 1.0
+
+
+def test_reserved_workspaces_change_nothing_but_the_first_call():
+    """plx_bo_reserve allocates the workspaces of a shape ahead of time (no cudaMalloc inside the first call of a
+    group); results are those of an unreserved handle, and it is refused once data has been set."""
+    from polyaxon_b200 import _lib
+    g = load_golden('c2_d8_n256_rbf_ei')
+    out = []
+    for reserve in (True, False):
+        h = _lib.Handle(0)
+        try:
+            if reserve:
+                h.reserve(256, 8, runs=3, seeds=4, candidates=8192)
+            h.set_data(g['X'], g['y'], int(g['kernel']), float(g['nu']))
+            theta, lml, _ = h.fit(0.0, [1.0, -1.0])
+            val, idx, x = h.sweep(_x_tries(g), **_acq_args(g))
+            xs, vals, ok = h.refine(g['x_seeds'], g['bounds'], **_acq_args(g))
+            out.append((theta, lml, val, idx, vals.tolist()))
+            with pytest.raises(_lib.PlxError):
+                h.reserve(64, 2)
+        finally:
+            h.close()
+    assert out[0] == out[1]
