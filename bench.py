@@ -46,7 +46,7 @@ UNIT = 'evals/s'
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the kernel over 151 552 candidates, from the
 # `ncu --set full` capture of this build kept under profiles/ (a constant from that file, not measured in this run)
 TRAFFIC = {
-    'sweep_i8c_kernel': ('profiles/r02_ncu_sweep_i8c_full_summary.csv', None, 151552),
+    'sweep_i8c_kernel': ('profiles/r02_ncu_sweep_i8c_full_summary.csv', 2.525030e9 + 2.207921e9, 151552),
     'sweep_tma_kernel': ('profiles/r01_ncu_sweep_tma_v3_summary.csv', 18.701e9 + 2.490e9, 151552),
 }
 
@@ -492,10 +492,11 @@ def main():
         traffic_file, traffic_bytes, traffic_cands = TRAFFIC.get(kernel, (None, None, 1))
         roofline = {'bound': 'tensor', 'kernel': kernel, 'kernel_ms_per_launch': kernel_ms,
                     'candidates_per_launch': n_local,
-                    'traffic': traffic_bytes,
-                    'traffic_note': ('dram__bytes_read.sum + dram__bytes_write.sum of one launch over %d candidates, a '
-                                     'constant from %s (ncu --set full of this kernel); algorithmic bytes are 256 per '
-                                     'candidate' % (traffic_cands, traffic_file)) if traffic_bytes else
+                    'traffic': traffic_bytes / traffic_cands * n_local if traffic_bytes else None,
+                    'traffic_note': ('dram__bytes_read.sum + dram__bytes_write.sum of one launch over %d candidates (%.3e '
+                                     'bytes, a constant from %s: ncu --set full of this kernel), scaled per candidate to '
+                                     'this launch; algorithmic bytes are 256 per candidate, the rest is the digit planes '
+                                     'of K* spilling from L2' % (traffic_cands, traffic_bytes, traffic_file)) if traffic_bytes else
                                     'no ncu capture of this kernel form under profiles/',
                     'traffic_candidates': traffic_cands if traffic_bytes else None,
                     'fp64_equivalent_tflops': fp64_equiv, 'flops_per_eval': fpe, 'dgemm_tflops': dgemm,

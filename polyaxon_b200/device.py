@@ -35,6 +35,11 @@ def get_handle(device=None):
         h = _handles.get(key)
         if h is None:
             h = _handles[key] = _lib.Handle(device)
+            # PLX_BO_RESERVE="n,d,runs,seeds,candidates": allocate the workspaces of that shape when the worker's
+            # handle is opened, so that no call of a group pays for device allocations (plx_bo_reserve)
+            spec = os.environ.get('PLX_BO_RESERVE')
+            if spec:
+                h.reserve(*[int(v) for v in spec.split(',')])
     return h
 
 
