@@ -33,9 +33,10 @@ def test_c4_batched_lml_over_33_thetas(handle, n):
         assert grad[i] == pytest.approx(rg, rel=max(1e-8, tol), abs=max(1e-7, tol * abs(rl)))
 
 
-def test_c4_largest_shape_runs_and_is_consistent(handle):
-    """n_obs = 4096: the oracle would need minutes per evaluation, so check self-consistency:
-    d LML/d theta against a central difference of the device LML, and batch invariance."""
+def test_c4_largest_shape_against_the_oracle(handle):
+    """n_obs = 4096, the top of C4's range: LML and its gradient against one oracle evaluation (a few seconds of
+    LAPACK), the posterior on a candidate block against the oracle, and the size-independent properties: the
+    gradient against a central difference of the device LML, and batch invariance."""
     X, y, _ = synthetic_problem(4096, 32)
     handle.set_data(X, y, G.KERNEL_MATERN, 1.5)
     th = 1.1
@@ -45,6 +46,19 @@ def test_c4_largest_shape_runs_and_is_consistent(handle):
     assert grad[1] == pytest.approx(fd, rel=1e-5)
     alone, galone = handle.lml([th])
     assert alone[0] == lml[1] and galone[0] == grad[1]            # bit-identical whatever the batch
+    rl, rg = G.log_marginal_likelihood(X, y, th, G.KERNEL_MATERN, 1.5)
+    K = G.kernel_matrix(X, th, G.KERNEL_MATERN, 1.5)
+    tol = max(1e-10, 100 * EPS * np.linalg.cond(K + 1e-10 * np.eye(4096)))
+    assert lml[1] == pytest.approx(rl, rel=tol, abs=1e-8)
+    assert grad[1] == pytest.approx(rg, rel=max(1e-8, tol), abs=max(1e-7, tol * abs(rl)))
+    handle.set_theta(th)
+    L, a = G.posterior_state(X, y, th, G.KERNEL_MATERN, 1.5)
+    xc = np.random.RandomState(4).uniform(0, 1, (1500, 32))
+    val, idx, _, mean, std, acq = handle.sweep(xc, G.ACQ_POI, float(y.max()), eps=0.0, dump=True)
+    m, s = G.predict(xc, X, L, a, th, G.KERNEL_MATERN, 1.5)
+    assert np.abs(mean - m).max() <= max(1e-9, tol) * max(1.0, np.abs(m).max())
+    assert np.abs(std ** 2 - s ** 2).max() <= max(1e-9, tol)
+    assert idx == int(np.argmax(G.acquisition(m, s, G.ACQ_POI, float(y.max()), 0.0, 0.0)))
 
 
 def test_c5_independent_groups_on_one_device(handle):
