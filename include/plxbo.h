@@ -162,6 +162,9 @@ int plx_acq_sweep_resident_range(plx_bo_handle h, long long first, long long cou
 /* Device time in milliseconds of the main sweep kernel(s) of the last plx_acq_sweep* call, measured
  * with CUDA events on the launching stream, and how many kernels that call launched. */
 int plx_last_sweep_stats(plx_bo_handle h, double* kernel_ms, long long* launches);
+/* How many candidates of the last plx_acq_sweep* had a negative posterior variance set to zero: the event sklearn's
+ * predict warns about (_gpr.py:485-491, reached from acquisition_function.py:49); the host layer raises the warning. */
+int plx_last_sweep_clamped(plx_bo_handle h, long long* count);
 
 /* Measured issue rate, in TOP/s, of the int8 tensor instruction the sliced sweep is built on
  * (tcgen05.mma kind::i8, m128 n128 k32, operands resident in shared memory, one CTA per SM): the roofline

@@ -51,6 +51,7 @@ SIGNATURES = {
     'plx_acq_sweep_resident_range': (c_int, [c_void_p, c_longlong, c_longlong, c_int, c_double, c_double, c_double,
                                              _dp, POINTER(c_longlong), c_void_p]),
     'plx_last_sweep_stats': (c_int, [c_void_p, _dp, POINTER(c_longlong)]),
+    'plx_last_sweep_clamped': (c_int, [c_void_p, POINTER(c_longlong)]),
     'plx_measure_i8_peak': (c_int, [c_void_p, _dp]),
     'plx_launch_count': (c_longlong, [c_void_p]),
     'plx_acq_refine': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_double, c_double, c_double, c_int,
@@ -306,6 +307,12 @@ class Handle(object):
         ms, nl = c_double(), c_longlong()
         self._check(self.lib.plx_last_sweep_stats(self._h, ctypes.byref(ms), ctypes.byref(nl)))
         return ms.value, nl.value
+
+    def last_sweep_clamped(self):
+        """Candidates of the last sweep whose negative variance was set to zero."""
+        n = c_longlong()
+        self._check(self.lib.plx_last_sweep_clamped(self._h, ctypes.byref(n)))
+        return n.value
 
     def measure_i8_peak(self):
         tops = c_double()

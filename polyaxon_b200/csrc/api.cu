@@ -78,6 +78,7 @@ struct plx_bo {
   // sweep buffers
   double* d_blk_val = nullptr; long long* d_blk_idx = nullptr;
   double* d_best_val = nullptr; long long* d_best_idx = nullptr;
+  unsigned long long* d_clamped = nullptr; long long last_clamped = 0;     // negative variances set to zero by the last sweep
   double* dcand[2] = {nullptr, nullptr}; size_t cand_cap = 0;
   double* d_out[3] = {nullptr, nullptr, nullptr}; size_t out_cap = 0;
   cudaEvent_t ev_copy[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
@@ -243,7 +244,8 @@ extern "C" int plx_bo_create(int device, plx_bo_handle* out) {
   if (cudaMalloc(&h->d_blk_val, sizeof(double) * 1024) != cudaSuccess ||
       cudaMalloc(&h->d_blk_idx, sizeof(long long) * 1024) != cudaSuccess ||
       cudaMalloc(&h->d_best_val, sizeof(double)) != cudaSuccess ||
-      cudaMalloc(&h->d_best_idx, sizeof(long long)) != cudaSuccess)
+      cudaMalloc(&h->d_best_idx, sizeof(long long)) != cudaSuccess ||
+      cudaMalloc(&h->d_clamped, sizeof(unsigned long long)) != cudaSuccess)
     return bail("cudaMalloc failed");
   *out = h;
   return PLX_OK;
@@ -255,7 +257,7 @@ extern "C" void plx_bo_destroy(plx_bo_handle h) {
   cudaDeviceSynchronize();
   void* ptrs[] = {h->dX, h->dy, h->bp.A, h->bp.L, h->bp.U, h->bp.W, h->bp.T, h->d_thetas, h->d_logdet, h->d_w,
                   h->d_alpha, h->d_partial, h->d_lml, h->d_grad, h->d_xs, h->d_info, h->dZ, h->d_alpha_state, h->dKs, h->dXt,
-                  h->d_blk_val, h->d_blk_idx, h->d_best_val, h->d_best_idx, h->dcand[0], h->dcand[1],
+                  h->d_blk_val, h->d_blk_idx, h->d_best_val, h->d_best_idx, h->d_clamped, h->dcand[0], h->dcand[1],
                   h->d_out[0], h->d_out[1], h->d_out[2], h->rf_kv, h->rf_kp, h->rf_v, h->rf_w, h->rf_vec,
                   h->rf_bounds, h->rf_val, h->rf_grad, h->rf_sc, h->rf_active, h->d_resident, h->d_misc, h->d_app,
                   h->d_kplanes, h->d_zplanes, h->d_zscale, h->d_i8mean, h->d_i8part, h->d_i8sync, h->d_fs};
@@ -709,7 +711,7 @@ static void fill_params(plx_bo* h, SweepParams& p, const double* Xc_dev, long lo
   p.kind = h->kind; p.mg = h->mg; p.acq = acq; p.kappa = kappa; p.eps = eps; p.y_max = y_max;
   p.Ks = h->dKs; p.out_mean = p.out_std = p.out_acq = nullptr;
   p.planes = nullptr; p.plane_stride = 0;
-  p.blk_val = h->d_blk_val; p.blk_idx = h->d_blk_idx; p.dbg = h->sweep_dbg;
+  p.blk_val = h->d_blk_val; p.blk_idx = h->d_blk_idx; p.clamped = h->d_clamped; p.dbg = h->sweep_dbg;
 }
 
 // 3-D map over digit planes: `cols` bytes per row, `rows` rows per plane, I8_S planes; box = 64 bytes x box_rows x all planes
@@ -779,7 +781,7 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     ip.N = p.N; ip.idx_base = p.idx_base; ip.n = p.n; ip.zscale = h->d_zscale; ip.mean = nullptr;
     ip.acq = p.acq; ip.kappa = p.kappa; ip.eps = p.eps; ip.y_max = p.y_max;
     ip.out_mean = p.out_mean; ip.out_std = p.out_std; ip.out_acq = p.out_acq;
-    ip.blk_val = h->d_blk_val; ip.blk_idx = h->d_blk_idx; ip.a_from_smem = h->i8_a_from_smem; ip.zplanes_dbg = h->d_zplanes;
+    ip.blk_val = h->d_blk_val; ip.blk_idx = h->d_blk_idx; ip.a_from_smem = h->i8_a_from_smem; ip.zplanes_dbg = h->d_zplanes; ip.clamped = h->d_clamped;
     // cooperative launch: the runtime starts the grid only when all its CTAs can be resident at once, which the
     // spin-waits between the CTAs of a group rely on (two such sweeps from different handles then run one after
     // the other instead of starving each other)
@@ -830,7 +832,7 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     ip.N = p.N; ip.idx_base = p.idx_base; ip.n = p.n; ip.zscale = h->d_zscale; ip.mean = nullptr;
     ip.acq = p.acq; ip.kappa = p.kappa; ip.eps = p.eps; ip.y_max = p.y_max;
     ip.out_mean = p.out_mean; ip.out_std = p.out_std; ip.out_acq = p.out_acq;
-    ip.blk_val = h->d_blk_val; ip.blk_idx = h->d_blk_idx; ip.a_from_smem = h->i8_a_from_smem; ip.zplanes_dbg = h->d_zplanes;
+    ip.blk_val = h->d_blk_val; ip.blk_idx = h->d_blk_idx; ip.a_from_smem = h->i8_a_from_smem; ip.zplanes_dbg = h->d_zplanes; ip.clamped = h->d_clamped;
     sweep_i8f_kernel<<<grid, 512, I8F_SMEM, st>>>(h->tmA8, h->tmB8, q, ip, h->d_i8mean);
     LAUNCH_CHECK("sweep_i8f_kernel");
     sweep_merge_kernel<<<1, 32, 0, st>>>(h->d_blk_val, h->d_blk_idx, grid, h->d_best_val, h->d_best_idx);
@@ -852,7 +854,7 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     ip.out_mean = p.out_mean ? p.out_mean + base : nullptr;
     ip.out_std = p.out_std ? p.out_std + base : nullptr;
     ip.out_acq = p.out_acq ? p.out_acq + base : nullptr;
-    ip.blk_val = h->d_blk_val; ip.blk_idx = h->d_blk_idx; ip.a_from_smem = h->i8_a_from_smem; ip.zplanes_dbg = h->d_zplanes;
+    ip.blk_val = h->d_blk_val; ip.blk_idx = h->d_blk_idx; ip.a_from_smem = h->i8_a_from_smem; ip.zplanes_dbg = h->d_zplanes; ip.clamped = h->d_clamped;
     sweep_i8_kernel<<<grid, 192, I8_SMEM, st>>>(h->tmA8, h->tmB8, ip);
     LAUNCH_CHECK("sweep_i8_kernel");
     sweep_merge_kernel<<<1, 32, 0, st>>>(h->d_blk_val, h->d_blk_idx, grid, h->d_best_val, h->d_best_idx);
@@ -889,6 +891,7 @@ static int reset_best(plx_bo* h) {
   const double ninf = -INFINITY; const long long big = 0x7fffffffffffffffLL;
   CK(cudaMemcpyAsync(h->d_best_val, &ninf, sizeof(double), cudaMemcpyHostToDevice, h->stream));
   CK(cudaMemcpyAsync(h->d_best_idx, &big, sizeof(long long), cudaMemcpyHostToDevice, h->stream));
+  CK(cudaMemsetAsync(h->d_clamped, 0, sizeof(unsigned long long), h->stream));
   return PLX_OK;
 }
 
@@ -922,6 +925,7 @@ extern "C" int plx_acq_sweep_dev(plx_bo_handle h, const double* Xc_dev, long lon
   if ((r = launch_sweep(h, p, h->ev_pool[0], h->ev_pool[1])) != PLX_OK) return r;
   CK(cudaMemcpyAsync(best_value, h->d_best_val, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   CK(cudaMemcpyAsync(best_index, h->d_best_idx, sizeof(long long), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaMemcpyAsync(&h->last_clamped, h->d_clamped, sizeof(long long), cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
   float ms = 0.f;
   if (N > 0) CK(cudaEventElapsedTime(&ms, h->ev_pool[0], h->ev_pool[1]));
@@ -938,7 +942,7 @@ extern "C" int plx_acq_sweep(plx_bo_handle h, const double* Xc, long long N, lon
   if (r != PLX_OK) return r;
   CK(cudaSetDevice(h->device));
   const long long l0 = h->launches;
-  if (N == 0) { *best_index = -1; *best_value = NAN; h->last_ms = 0; h->last_launches = 0; return PLX_OK; }
+  if (N == 0) { *best_index = -1; *best_value = NAN; h->last_ms = 0; h->last_launches = 0; h->last_clamped = 0; return PLX_OK; }
   const int d = h->d;
   // chunk: a whole number of waves of 128-candidate tiles, at most ~64 MiB of candidates
   const long long wave = 128LL * h->num_sms;
@@ -981,6 +985,7 @@ extern "C" int plx_acq_sweep(plx_bo_handle h, const double* Xc, long long N, lon
   }
   CK(cudaMemcpyAsync(best_value, h->d_best_val, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   CK(cudaMemcpyAsync(best_index, h->d_best_idx, sizeof(long long), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaMemcpyAsync(&h->last_clamped, h->d_clamped, sizeof(long long), cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
   double total = 0.0;
   for (long long c = 0; c < nchunks; ++c) {
@@ -1115,6 +1120,12 @@ extern "C" int plx_measure_i8_peak(plx_bo_handle h, double* tops) {
   float ms = 0.f;
   CK(cudaEventElapsedTime(&ms, h->ev_pool[0], h->ev_pool[1]));
   *tops = 2.0 * 128 * 128 * 128 * static_cast<double>(repeats) * h->num_sms / (ms * 1e-3) / 1e12;
+  return PLX_OK;
+}
+
+extern "C" int plx_last_sweep_clamped(plx_bo_handle h, long long* count) {
+  if (!h || !count) return PLX_ERR_INVALID;
+  *count = h->last_clamped;
   return PLX_OK;
 }
 
@@ -1423,7 +1434,7 @@ extern "C" int plx_acq_sweep_noalloc(int device, void* stream, const double* Xc_
   p.X = X_dev; p.Xt = nullptr; p.alpha = alpha_dev; p.Z = Zpad; p.ell = std::exp(theta);
   p.kind = kind; p.mg = (kind == K_GEN) ? make_matern_gen(nu) : MaternGen{}; p.acq = acq; p.kappa = kappa; p.eps = eps; p.y_max = y_max;
   p.Ks = Ks; p.out_mean = p.out_std = p.out_acq = nullptr;
-  p.blk_val = blk_val; p.blk_idx = blk_idx; p.dbg = 0;
+  p.blk_val = blk_val; p.blk_idx = blk_idx; p.clamped = nullptr; p.dbg = 0;
   const long long ntiles = (N + 127) / 128;
   const int grid = static_cast<int>(std::min<long long>(ntiles, NOALLOC_GRID));
   sweep_simple_kernel<<<grid, 256, SWEEP_SIMPLE_SMEM, st>>>(p);

@@ -49,6 +49,7 @@ struct SweepParams {
   size_t plane_stride;     //            bytes between planes
   double* out_mean; double* out_std; double* out_acq;   // optional per-candidate dumps [N]
   double* blk_val; long long* blk_idx;                  // per-CTA best
+  unsigned long long* clamped;                          // nullable: counts negative variances set to zero (sklearn _gpr.py:485-491 warns)
   int dbg;                 // read only in PLX_PROFILE builds (tools/*_phases.py): bits skip parts of the work to time the rest
 };
 
@@ -189,7 +190,7 @@ __device__ __forceinline__ void tile_epilogue(const SweepParams& p, long long ti
   const long long ci = tile * 128 + c;
   if (ci >= p.N) return;
   double var = 1.0 - (part[c] + part[128 + c]);
-  if (var < 0.0) var = 0.0;                 // sklearn clamps negative variances to zero
+  if (var < 0.0) { var = 0.0; if (p.clamped) atomicAdd(p.clamped, 1ULL); }   // sklearn clamps negative variances to zero, and says so
   const double sd = sqrt(var), mean = mean_s[c];
   const double a = acq_value(p.acq, mean, sd, p.y_max, p.kappa, p.eps);
   if (p.out_mean) p.out_mean[ci] = mean;

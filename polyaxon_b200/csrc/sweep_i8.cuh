@@ -52,6 +52,7 @@ struct I8Params {
   double kappa, eps, y_max;
   double* out_mean; double* out_std; double* out_acq;       // optional dumps, indexed like the candidates of this launch
   double* blk_val; long long* blk_idx;
+  unsigned long long* clamped; // nullable: counts negative variances set to zero
   const signed char* zplanes_dbg;   // PLX_PROFILE experiments only
   int a_from_smem;             // 1: both tensor-core operands from shared memory (A/B measurement), 0: A planes via tensor memory
 };
@@ -293,7 +294,7 @@ __global__ void __launch_bounds__(192, 1) sweep_i8_kernel(const __grid_constant_
       const long long ci = tile * 128 + tid;
       if (ci < p.N) {
         double var = 1.0 - sumsq;
-        if (var < 0.0) var = 0.0;                 // sklearn clamps negative variances to zero
+        if (var < 0.0) { var = 0.0; if (p.clamped) atomicAdd(p.clamped, 1ULL); }   // sklearn clamps negative variances to zero, and says so
         const double sd = sqrt(var), mean = p.mean[ci];
         const double a = acq_value(p.acq, mean, sd, p.y_max, p.kappa, p.eps);
         if (p.out_mean) p.out_mean[ci] = mean;

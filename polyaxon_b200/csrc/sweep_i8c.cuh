@@ -130,7 +130,7 @@ __global__ void __launch_bounds__(512, 1) sweep_i8c_kernel(const __grid_constant
       const long long ci = tile * 128 + row;
       if (ci < ip.N) {
         double var = 1.0 - ss;
-        if (var < 0.0) var = 0.0;                 // sklearn clamps negative variances to zero
+        if (var < 0.0) { var = 0.0; if (ip.clamped) atomicAdd(ip.clamped, 1ULL); }   // sklearn clamps negative variances to zero, and says so
         const double sd = sqrt(var);
         const double a = acq_value(ip.acq, mean, sd, ip.y_max, ip.kappa, ip.eps);
         if (ip.out_mean) ip.out_mean[ci] = mean;

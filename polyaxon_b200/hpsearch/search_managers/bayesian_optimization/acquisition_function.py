@@ -34,11 +34,11 @@ from polyaxon_b200.schemas.hptuning import (
 THETA_BOUNDS = (float(np.log(1e-5)), float(np.log(1e5)))      # sklearn's default length_scale_bounds
 
 
-def _warn_clamped(std):
+def _warn_clamped(handle):
     """sklearn warns when predicted variances come out negative and sets them to zero
-    (_gpr.py:485-491, reached from acquisition_function.py:49); the kernels clamp, the warning is raised here
-    for the per-candidate outputs the caller asked for (an exact zero is what the clamp leaves)."""
-    if std is not None and np.any(std == 0.0):
+    (_gpr.py:485-491, reached from acquisition_function.py:49); the kernels clamp and count, the warning is
+    raised here with sklearn's text."""
+    if handle.last_sweep_clamped() > 0:
         import warnings
         warnings.warn('Predicted variances smaller than 0. Setting those variances to 0.')
 
@@ -193,7 +193,7 @@ class DeviceGaussianProcess(object):
         h = self.ensure_state()
         X = np.atleast_2d(np.asarray(X, dtype=np.float64))
         _, _, _, mean, std, _ = h.sweep(X, _lib.ACQ_UCB, 0.0, kappa=0.0, dump=True)
-        _warn_clamped(std)
+        _warn_clamped(h)
         return (mean, std) if return_std else mean
 
 
@@ -291,8 +291,9 @@ class UtilityFunction(object):
         if acq is None:
             return None
         x = np.atleast_2d(np.asarray(x, dtype=np.float64))
-        out = self.gaussian_process.ensure_state().sweep(x, acq, dump=True, **args)
-        _warn_clamped(out[4])
+        h = self.gaussian_process.ensure_state()
+        out = h.sweep(x, acq, dump=True, **args)
+        _warn_clamped(h)
         return out[5]
 
     def max_compute(self, y_max, bounds, n_warmup=100000, n_iter=250):
@@ -302,6 +303,7 @@ class UtilityFunction(object):
         bounds = np.asarray(bounds, dtype=np.float64)
         h = self.gaussian_process.ensure_state()
         max_acq, x_max, x_seeds = self._warmup(h, acq, args, bounds, n_warmup, n_iter)
+        _warn_clamped(h)
         if n_iter > 0:
             rank, size = pdist.world()
             if size > 1 and os.environ.get('PLX_BO_DISTRIBUTED', '1') != '0':

@@ -341,3 +341,30 @@ def test_reserved_workspaces_change_nothing_but_the_first_call():
         finally:
             h.close()
     assert out[0] == out[1]
+
+
+def test_negative_variances_are_counted_and_warned_about(handle):
+    """sklearn sets negative predicted variances to zero and warns (_gpr.py:485-491).  The kernels clamp and count;
+    the drop-in predict raises the same warning.  Candidates ON observations with a tiny jitter make 1 - |L^-1 k|^2
+    round below zero for some of them."""
+    from polyaxon_b200.hpsearch.search_managers.bayesian_optimization.acquisition_function import DeviceGaussianProcess
+    X, y, _ = synthetic_problem(300, 3, seed=11)
+    gp = DeviceGaussianProcess('rbf', 1.0, 1.5, 0, np.random.RandomState(1), handle=handle)
+    gp.alpha = 1e-14
+    gp.n_restarts_optimizer = 0
+    handle.set_data(X, y, G.KERNEL_RBF, 1.5, jitter=1e-14)
+    handle.set_theta(-0.5)
+    for impl in (3, 1):
+        handle.set_option('sweep_impl', impl)
+        _, _, _, mean, std, _ = handle.sweep(np.repeat(X, 4, axis=0), G.ACQ_UCB, 0.0, kappa=0.0, dump=True)
+        clamped = handle.last_sweep_clamped()
+        assert clamped == int(np.sum(std == 0.0))
+    handle.set_option('sweep_impl', 3)
+    gp.X_train_, gp.y_train_, gp.theta_, gp.fitted = X, y, -0.5, True
+    gp._stamp()
+    with warnings.catch_warnings(record=True) as caught:
+        warnings.simplefilter('always')
+        gp.predict(np.repeat(X, 4, axis=0), return_std=True)
+    assert (clamped > 0) == any('Predicted variances smaller than 0' in str(w.message) for w in caught)
+    _, _, _ = handle.sweep(np.random.RandomState(0).uniform(2, 3, (500, 3)), G.ACQ_UCB, 0.0, kappa=1.0)
+    assert handle.last_sweep_clamped() == 0                      # far from every observation: nothing to clamp
