@@ -47,7 +47,8 @@ const char* plx_version(void);
 /* Use the caller's CUDA stream (a cudaStream_t passed as void*); NULL restores the handle's own. */
 int plx_bo_set_stream(plx_bo_handle h, void* stream);
 
-/* Options: "sweep_impl" (3 [default] = int8-sliced sweep on the tcgen05 tensor cores from 256 observations up
+/* Options: "sweep_impl" (3 [default] = a thread per candidate against the state in shared memory up to 64 observations
+ * (sweep_small.cuh; 7 = the same rule, named), int8-sliced sweep on the tcgen05 tensor cores from 256 observations up
  * (fused form below 1536 observations, cooperative form from there) and the FP64 DMMA kernel below 256; 5 = always the cooperative int8-sliced sweep (four CTAs per
  * candidate tile); 6 = the cooperative form with the four CTAs as two clusters of two that share the candidate planes'
  * stream by TMA multicast (same results, measured equal in speed); 4 = the fused int8-sliced sweep (one CTA per tile); 2 = int8-sliced as two kernels per chunk;

@@ -9,7 +9,7 @@ CSRC = os.path.join(HERE, 'csrc')
 OUT = os.path.join(HERE, 'libplxbo.so')
 OUT_PROFILE = os.path.join(HERE, 'libplxbo_profile.so')     # separate file: never loaded by the product
 SOURCES = ['api.cu']
-HEADERS = ['mma_f64.cuh', 'tma_ring.cuh', 'gp_kernels.cuh', 'sweep.cuh', 'sweep_i8.cuh', 'sweep_i8f.cuh', 'sweep_i8c.cuh', 'sweep_i8p.cuh', 'mt19937.cuh', 'mt19937_jump.inc', 'fit_small.cuh', 'append.cuh', 'refine.cuh', 'lbfgsb1d.h', os.path.join('..', '..', 'include', 'plxbo.h')]
+HEADERS = ['mma_f64.cuh', 'tma_ring.cuh', 'gp_kernels.cuh', 'sweep.cuh', 'sweep_i8.cuh', 'sweep_i8f.cuh', 'sweep_i8c.cuh', 'sweep_i8p.cuh', 'mt19937.cuh', 'mt19937_jump.inc', 'fit_small.cuh', 'sweep_small.cuh', 'append.cuh', 'refine.cuh', 'lbfgsb1d.h', os.path.join('..', '..', 'include', 'plxbo.h')]
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
               '-shared', '-Xcompiler', '-fPIC']
 

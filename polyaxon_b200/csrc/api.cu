@@ -6,6 +6,7 @@
 #include "sweep_i8p.cuh"
 #include "mt19937.cuh"
 #include "fit_small.cuh"
+#include "sweep_small.cuh"
 
 #include <cstdio>
 #include <cstdlib>
@@ -77,8 +78,11 @@ struct plx_bo {
 
   // sweep buffers
   double* d_blk_val = nullptr; long long* d_blk_idx = nullptr;
-  double* d_best_val = nullptr; long long* d_best_idx = nullptr;
-  unsigned long long* d_clamped = nullptr; long long last_clamped = 0;     // negative variances set to zero by the last sweep
+  // result record of a sweep on the device: [0] best value, [1] best index, [2] clamped-variance count, [3..] winning row;
+  // it comes back in ONE copy into pinned host memory (a pageable device->host copy blocks per call)
+  double* d_rec = nullptr; size_t rec_cap = 0; double* h_pin = nullptr; size_t pin_cap = 0;
+  double* d_best_val = nullptr; long long* d_best_idx = nullptr;           // = d_rec, d_rec + 1
+  unsigned long long* d_clamped = nullptr; long long last_clamped = 0;     // = d_rec + 2: negative variances set to zero by the last sweep
   double* dcand[2] = {nullptr, nullptr}; size_t cand_cap = 0;
   double* d_out[3] = {nullptr, nullptr, nullptr}; size_t out_cap = 0;
   cudaEvent_t ev_copy[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
@@ -218,7 +222,7 @@ extern "C" int plx_bo_create(int device, plx_bo_handle* out) {
     if (std::atoi(e) != 0) h->coop_cluster_ok = 0;
   if (const char* e = std::getenv("PLX_BO_SWEEP_IMPL")) {       // A/B switch for measurements; see plx_bo_set_option
     const int v = std::atoi(e);
-    if (v >= 0 && v <= 6) h->sweep_impl = v;
+    if (v >= 0 && v <= 7) h->sweep_impl = v;
   }
   // opt in to large dynamic shared memory once
   cudaFuncSetAttribute(potf2_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, POTF_SMEM);
@@ -236,6 +240,8 @@ extern "C" int plx_bo_create(int device, plx_bo_handle* out) {
   cudaFuncSetAttribute(kstar_slices_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, KSL_SMEM);
   cudaFuncSetAttribute(refine_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                        static_cast<int>(sizeof(double) * rf_persist_smem_doubles(RF_PERSIST_ZSMEM, RF_PERSIST_ZSMEM, RF_PERSIST_DSMEM)));
+  cudaFuncSetAttribute(sweep_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                       static_cast<int>(sweep_small_smem(SS_NMAX, SS_XMAX / SS_NMAX)));
   cudaFuncSetAttribute(fit_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FS_SMEM);
   cudaFuncSetAttribute(state_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FS_SMEM);
   cudaFuncSetAttribute(mt19937_draw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -243,10 +249,12 @@ extern "C" int plx_bo_create(int device, plx_bo_handle* out) {
   if (cudaGetLastError() != cudaSuccess) return bail("cudaFuncSetAttribute failed (is the library built for this GPU?)");
   if (cudaMalloc(&h->d_blk_val, sizeof(double) * 1024) != cudaSuccess ||
       cudaMalloc(&h->d_blk_idx, sizeof(long long) * 1024) != cudaSuccess ||
-      cudaMalloc(&h->d_best_val, sizeof(double)) != cudaSuccess ||
-      cudaMalloc(&h->d_best_idx, sizeof(long long)) != cudaSuccess ||
-      cudaMalloc(&h->d_clamped, sizeof(unsigned long long)) != cudaSuccess)
+      cudaMalloc(&h->d_rec, sizeof(double) * (3 + 2048)) != cudaSuccess ||
+      cudaHostAlloc(&h->h_pin, sizeof(double) * (3 + 2048), cudaHostAllocDefault) != cudaSuccess)
     return bail("cudaMalloc failed");
+  h->rec_cap = h->pin_cap = 3 + 2048;
+  h->d_best_val = h->d_rec; h->d_best_idx = reinterpret_cast<long long*>(h->d_rec + 1);
+  h->d_clamped = reinterpret_cast<unsigned long long*>(h->d_rec + 2);
   *out = h;
   return PLX_OK;
 }
@@ -257,11 +265,12 @@ extern "C" void plx_bo_destroy(plx_bo_handle h) {
   cudaDeviceSynchronize();
   void* ptrs[] = {h->dX, h->dy, h->bp.A, h->bp.L, h->bp.U, h->bp.W, h->bp.T, h->d_thetas, h->d_logdet, h->d_w,
                   h->d_alpha, h->d_partial, h->d_lml, h->d_grad, h->d_xs, h->d_info, h->dZ, h->d_alpha_state, h->dKs, h->dXt,
-                  h->d_blk_val, h->d_blk_idx, h->d_best_val, h->d_best_idx, h->d_clamped, h->dcand[0], h->dcand[1],
+                  h->d_blk_val, h->d_blk_idx, h->d_rec, h->dcand[0], h->dcand[1],
                   h->d_out[0], h->d_out[1], h->d_out[2], h->rf_kv, h->rf_kp, h->rf_v, h->rf_w, h->rf_vec,
                   h->rf_bounds, h->rf_val, h->rf_grad, h->rf_sc, h->rf_active, h->d_resident, h->d_misc, h->d_app,
                   h->d_kplanes, h->d_zplanes, h->d_zscale, h->d_i8mean, h->d_i8part, h->d_i8sync, h->d_fs};
   for (void* p : ptrs) if (p) cudaFree(p);
+  if (h->h_pin) cudaFreeHost(h->h_pin);
   for (int i = 0; i < 2; ++i) { if (h->ev_copy[i]) cudaEventDestroy(h->ev_copy[i]); if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]); }
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
@@ -278,7 +287,7 @@ extern "C" int plx_bo_set_stream(plx_bo_handle h, void* stream) {
 
 extern "C" int plx_bo_set_option(plx_bo_handle h, const char* name, long long value) {
   if (!h || !name) return PLX_ERR_INVALID;
-  if (std::strcmp(name, "sweep_impl") == 0 && value >= 0 && value <= 6) { h->sweep_impl = static_cast<int>(value); return PLX_OK; }
+  if (std::strcmp(name, "sweep_impl") == 0 && value >= 0 && value <= 7) { h->sweep_impl = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "lml_batch_limit") == 0 && value >= 0) { h->lml_batch_limit = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "refine_persist") == 0 && (value == 0 || value == 1)) { h->refine_persist = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "fit_small") == 0 && value >= 0 && value <= 2) { h->fit_small = static_cast<int>(value); return PLX_OK; }
@@ -530,7 +539,7 @@ extern "C" int plx_gp_set_theta(plx_bo_handle h, double theta) {
     fp.jitter = h->jitter; fp.xs = h->d_xs;
     state_small_kernel<<<1, FS_THREADS, FS_SMEM, h->stream>>>(fp, theta, h->npad, h->bp.L, h->dZ, h->d_alpha_state, h->d_fs);
     LAUNCH_CHECK("state_small_kernel");
-    double st[2] = {0.0, 0.0};
+    double* st = h->h_pin;
     CK(cudaMemcpyAsync(st, h->d_fs, sizeof(double) * 2, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
     if (st[0] != 0.0)
@@ -653,15 +662,19 @@ extern "C" int plx_gp_fit(plx_bo_handle h, double theta0, const double* theta_re
     if ((r = ensure(h, h->d_xs, h->xs_cap, static_cast<size_t>(R) * h->n * h->d)) != PLX_OK) return r;
     std::vector<double> st(R), out(static_cast<size_t>(4) * R);
     for (int i = 0; i < R; ++i) st[i] = (i == 0) ? theta0 : theta_restarts[i - 1];
-    CK(cudaMemcpyAsync(h->d_fs, st.data(), sizeof(double) * R, cudaMemcpyHostToDevice, h->stream));
+    const bool pinned = static_cast<size_t>(5) * R <= h->pin_cap;      // small transfers through pinned memory: no blocking copies
+    double* stage = pinned ? h->h_pin : st.data();
+    if (pinned) std::memcpy(stage, st.data(), sizeof(double) * R);
+    CK(cudaMemcpyAsync(h->d_fs, stage, sizeof(double) * R, cudaMemcpyHostToDevice, h->stream));
     FitSmallParams fp;
     fp.X = h->dX; fp.y = h->dy; fp.n = h->n; fp.d = h->d; fp.kind = h->kind; fp.R = R; fp.mg = h->mg;
     fp.jitter = h->jitter; fp.lo = theta_lo; fp.hi = theta_hi; fp.starts = h->d_fs; fp.xs = h->d_xs;
     fp.per_run = h->d_fs + R;
     fit_small_kernel<<<R, FS_THREADS, FS_SMEM, h->stream>>>(fp);
     LAUNCH_CHECK("fit_small_kernel");
-    CK(cudaMemcpyAsync(out.data(), h->d_fs + R, sizeof(double) * 4 * R, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(pinned ? h->h_pin + R : out.data(), h->d_fs + R, sizeof(double) * 4 * R, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
+    if (pinned) std::memcpy(out.data(), h->h_pin + R, sizeof(double) * 4 * R);
     int best = 0;
     for (int i = 1; i < R; ++i) if (-out[4 * i + 2] < -out[4 * best + 2]) best = i;     // first minimum of -LML
     if (per_run) std::memcpy(per_run, out.data(), sizeof(double) * 4 * R);
@@ -764,12 +777,13 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     h->i8_state_valid = true;
   }
   if (e0) CK(cudaEventRecord(e0, st));
-  if (h->sweep_impl == 5 || h->sweep_impl == 6 || (h->sweep_impl == 3 && p.n >= 1536)) {
+  const int impl_i8 = h->sweep_impl == 7 ? 3 : h->sweep_impl;
+  if (impl_i8 == 5 || impl_i8 == 6 || (impl_i8 == 3 && p.n >= 1536)) {
     // cooperative forms: groups of four CTAs share a candidate tile so that the planes in flight stay in L2.
     // 6: the four are two clusters of two that fetch the A stream once per pair (TMA multicast); measured equal to 5
     // (8.3 ms against 8.2 ms per 151 552 candidates: what a CTA receives, not what L2 reads, bounds the stream), so
     // the default stays with the plain cooperative form
-    const bool paired = h->sweep_impl == 6;
+    const bool paired = impl_i8 == 6;
     const int max_groups = h->num_sms / I8C_R;
     const int groups = static_cast<int>(std::min<long long>((p.N + 127) / 128, max_groups));
     if ((r = ensure(h, h->d_i8part, h->i8part_cap, static_cast<size_t>(max_groups) * 2 * I8C_R * 256)) != PLX_OK) return r;
@@ -823,7 +837,7 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     if (e1) CK(cudaEventRecord(e1, st));
     return PLX_OK;
   }
-  if (h->sweep_impl != 2) {
+  if (impl_i8 != 2) {
     // fused form: one persistent launch, the planes of the next tile are built while the current one is contracted
     const int grid = static_cast<int>(std::min<long long>((p.N + 127) / 128, h->num_sms));
     SweepParams q = p;
@@ -871,7 +885,19 @@ static int launch_sweep(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cudaEve
   // 3 (default): the int8-sliced sweep from 256 observations up (measured break-even between 128 and 256; fused
   // form up to 1535 observations, cooperative form -- four CTAs per tile, planes L2-resident -- from 1536),
   // FP64 DMMA below and for the general-nu Matern kernel, whose Bessel evaluation dominates anyway
-  const bool sliced = h->sweep_impl == 2 || h->sweep_impl >= 4 || (h->sweep_impl == 3 && p.n >= 256);
+  if ((h->sweep_impl == 3 || h->sweep_impl == 7) && p.n <= SS_NMAX) {
+    // small observation sets: a thread per candidate against the state in shared memory (sweep_small.cuh)
+    const int g = static_cast<int>(std::min<long long>((p.N + SS_THREADS - 1) / SS_THREADS, 4LL * h->num_sms));
+    if (e0) CK(cudaEventRecord(e0, h->stream));
+    sweep_small_kernel<<<g, SS_THREADS, sweep_small_smem(p.n, p.d), h->stream>>>(p);
+    LAUNCH_CHECK("sweep_small_kernel");
+    if (e1) CK(cudaEventRecord(e1, h->stream));
+    sweep_merge_kernel<<<1, 32, 0, h->stream>>>(h->d_blk_val, h->d_blk_idx, g, h->d_best_val, h->d_best_idx);
+    LAUNCH_CHECK("sweep_merge_kernel");
+    return PLX_OK;
+  }
+  const int impl = h->sweep_impl == 7 ? 3 : h->sweep_impl;       // 7 = 3 with the small-set kernel forced on (it is on by default)
+  const bool sliced = impl == 2 || impl >= 4 || (impl == 3 && p.n >= 256);
   if (sliced && p.kind != K_GEN) return launch_sweep_i8(h, p, e0, e1);
   if (e0) CK(cudaEventRecord(e0, h->stream));
   if (h->sweep_impl >= 1) {
@@ -887,11 +913,31 @@ static int launch_sweep(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cudaEve
   return PLX_OK;
 }
 
+__global__ void sweep_reset_kernel(double* rec) {
+  rec[0] = -INFINITY;
+  reinterpret_cast<long long*>(rec)[1] = 0x7fffffffffffffffLL;
+  reinterpret_cast<unsigned long long*>(rec)[2] = 0ULL;
+}
+// rec[3 .. 3 + d) <- the candidate row the record's index names (all candidates of the sweep in one device array)
+__global__ void sweep_gather_row_kernel(double* rec, const double* __restrict__ Xc, long long idx_base, long long N, int d) {
+  const long long i = reinterpret_cast<const long long*>(rec)[1] - idx_base;
+  if (i < 0 || i >= N) return;
+  for (int q = threadIdx.x; q < d; q += blockDim.x) rec[3 + q] = Xc[i * d + q];
+}
+
 static int reset_best(plx_bo* h) {
-  const double ninf = -INFINITY; const long long big = 0x7fffffffffffffffLL;
-  CK(cudaMemcpyAsync(h->d_best_val, &ninf, sizeof(double), cudaMemcpyHostToDevice, h->stream));
-  CK(cudaMemcpyAsync(h->d_best_idx, &big, sizeof(long long), cudaMemcpyHostToDevice, h->stream));
-  CK(cudaMemsetAsync(h->d_clamped, 0, sizeof(unsigned long long), h->stream));
+  sweep_reset_kernel<<<1, 1, 0, h->stream>>>(h->d_rec);
+  LAUNCH_CHECK("sweep_reset_kernel");
+  return PLX_OK;
+}
+
+// the record (and `extra` doubles after its three scalars) to the host: one copy, one synchronisation
+static int fetch_record(plx_bo* h, int extra, double* best_value, long long* best_index) {
+  CK(cudaMemcpyAsync(h->h_pin, h->d_rec, sizeof(double) * (3 + extra), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  *best_value = h->h_pin[0];
+  *best_index = reinterpret_cast<const long long*>(h->h_pin)[1];
+  h->last_clamped = reinterpret_cast<const long long*>(h->h_pin)[2];
   return PLX_OK;
 }
 
@@ -923,15 +969,18 @@ extern "C" int plx_acq_sweep_dev(plx_bo_handle h, const double* Xc_dev, long lon
   SweepParams p;
   fill_params(h, p, Xc_dev, N, idx_base, acq, kappa, eps, y_max);
   if ((r = launch_sweep(h, p, h->ev_pool[0], h->ev_pool[1])) != PLX_OK) return r;
-  CK(cudaMemcpyAsync(best_value, h->d_best_val, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-  CK(cudaMemcpyAsync(best_index, h->d_best_idx, sizeof(long long), cudaMemcpyDeviceToHost, h->stream));
-  CK(cudaMemcpyAsync(&h->last_clamped, h->d_clamped, sizeof(long long), cudaMemcpyDeviceToHost, h->stream));
-  CK(cudaStreamSynchronize(h->stream));
+  const bool row = best_x != nullptr && N > 0 && static_cast<size_t>(3 + h->d) <= h->rec_cap;
+  if (row) {
+    sweep_gather_row_kernel<<<1, 128, 0, h->stream>>>(h->d_rec, Xc_dev, idx_base, N, h->d);
+    LAUNCH_CHECK("sweep_gather_row_kernel");
+  }
+  if ((r = fetch_record(h, row ? h->d : 0, best_value, best_index)) != PLX_OK) return r;
   float ms = 0.f;
   if (N > 0) CK(cudaEventElapsedTime(&ms, h->ev_pool[0], h->ev_pool[1]));
   h->last_ms = ms; h->last_launches = h->launches - l0;
   if (N == 0) { *best_index = -1; *best_value = NAN; return PLX_OK; }
-  if (best_x) CK(cudaMemcpy(best_x, Xc_dev + (*best_index - idx_base) * h->d, sizeof(double) * h->d, cudaMemcpyDeviceToHost));
+  if (row) std::memcpy(best_x, h->h_pin + 3, sizeof(double) * h->d);
+  else if (best_x) CK(cudaMemcpy(best_x, Xc_dev + (*best_index - idx_base) * h->d, sizeof(double) * h->d, cudaMemcpyDeviceToHost));
   return PLX_OK;
 }
 
@@ -983,10 +1032,7 @@ extern "C" int plx_acq_sweep(plx_bo_handle h, const double* Xc, long long N, lon
       if (acq_values) CK(cudaMemcpyAsync(acq_values + off, h->d_out[2], sizeof(double) * cn, cudaMemcpyDeviceToHost, h->stream));
     }
   }
-  CK(cudaMemcpyAsync(best_value, h->d_best_val, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-  CK(cudaMemcpyAsync(best_index, h->d_best_idx, sizeof(long long), cudaMemcpyDeviceToHost, h->stream));
-  CK(cudaMemcpyAsync(&h->last_clamped, h->d_clamped, sizeof(long long), cudaMemcpyDeviceToHost, h->stream));
-  CK(cudaStreamSynchronize(h->stream));
+  if ((r = fetch_record(h, 0, best_value, best_index)) != PLX_OK) return r;
   double total = 0.0;
   for (long long c = 0; c < nchunks; ++c) {
     float ms = 0.f;
@@ -1269,16 +1315,30 @@ extern "C" int plx_acq_refine(plx_bo_handle h, const double* seeds, int S, const
   while (active > 0 && rounds < max_rounds) {
     for (int k = 0; k < 4 && rounds < max_rounds; ++k, ++rounds)
       if ((r = launch_refine_round(h, p)) != PLX_OK) return r;
-    CK(cudaMemcpyAsync(&active, h->rf_active, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    int* pinned_active = reinterpret_cast<int*>(h->h_pin);
+    CK(cudaMemcpyAsync(pinned_active, h->rf_active, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
+    active = *pinned_active;
   }
   h->last_refine_rounds = rounds;
   std::vector<RefineScalars> sc(S);
   const size_t stride = rf_vec_stride(d);
-  CK(cudaMemcpyAsync(sc.data(), h->rf_sc, sizeof(RefineScalars) * S, cudaMemcpyDeviceToHost, h->stream));
-  CK(cudaMemcpy2DAsync(x_out, static_cast<size_t>(d) * 8, h->rf_vec, stride * 8, static_cast<size_t>(d) * 8, S,
-                       cudaMemcpyDeviceToHost, h->stream));
-  CK(cudaStreamSynchronize(h->stream));
+  const size_t sc_bytes = (sizeof(RefineScalars) * S + 7) / 8 * 8, x_bytes = sizeof(double) * S * d;
+  if (sc_bytes + x_bytes <= h->pin_cap * sizeof(double)) {
+    // both results into pinned memory: the copies queue behind the kernels and one synchronisation collects them
+    unsigned char* pin = reinterpret_cast<unsigned char*>(h->h_pin);
+    CK(cudaMemcpyAsync(pin, h->rf_sc, sizeof(RefineScalars) * S, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpy2DAsync(pin + sc_bytes, static_cast<size_t>(d) * 8, h->rf_vec, stride * 8, static_cast<size_t>(d) * 8, S,
+                         cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    std::memcpy(sc.data(), pin, sizeof(RefineScalars) * S);
+    std::memcpy(x_out, pin + sc_bytes, x_bytes);
+  } else {
+    CK(cudaMemcpyAsync(sc.data(), h->rf_sc, sizeof(RefineScalars) * S, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpy2DAsync(x_out, static_cast<size_t>(d) * 8, h->rf_vec, stride * 8, static_cast<size_t>(d) * 8, S,
+                         cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+  }
   for (int s = 0; s < S; ++s) {
     acq_out[s] = -sc[s].f;
     success_out[s] = (sc[s].phase == 2 && sc[s].status == 0) ? 1 : 0;

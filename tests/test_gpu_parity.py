@@ -67,7 +67,7 @@ def test_posterior_state_matches_reference(handle, name):
     assert resid <= 100 * EPS * max(1.0, np.sqrt(cond)) * n
 
 
-@pytest.mark.parametrize('impl', [6, 5, 4, 2, 1, 0])   # int8-sliced paired / cooperative / fused / two-kernel, FP64 DMMA + TMA ring, plain loads
+@pytest.mark.parametrize('impl', [7, 6, 5, 4, 2, 1, 0])   # default rule (small sets: a thread per candidate), int8-sliced paired / cooperative / fused / two-kernel, FP64 DMMA + TMA ring, plain loads
 @pytest.mark.parametrize('name', CLOSED_FORM)
 def test_mean_std_acquisition_match_reference(handle, name, impl):
     g = load_golden(name)
@@ -91,7 +91,7 @@ def test_mean_std_acquisition_match_reference(handle, name, impl):
         assert np.allclose(acq[ok], ref[ok], rtol=0, atol=1e-9 * max(1.0, np.abs(ref[ok]).max()))
 
 
-@pytest.mark.parametrize('impl', [6, 5, 4, 2, 1, 0])   # int8-sliced paired / cooperative / fused / two-kernel, FP64 DMMA + TMA ring, plain loads
+@pytest.mark.parametrize('impl', [7, 6, 5, 4, 2, 1, 0])   # default rule (small sets: a thread per candidate), int8-sliced paired / cooperative / fused / two-kernel, FP64 DMMA + TMA ring, plain loads
 @pytest.mark.parametrize('name', CLOSED_FORM)
 def test_sweep_argmax_is_bit_exact(handle, name, impl, record_property):
     g = load_golden(name)
