@@ -349,12 +349,16 @@ def measure_dgemm_tflops(torch, dev, n=8192, reps=6):
 def sweep_kernel_name(impl, n):
     if impl == 0:
         return 'sweep_simple_kernel'
-    if impl == 1 or (impl == 3 and n < 256):
+    if impl in (3, 7) and n <= 64:
+        return 'sweep_small_kernel'
+    if impl == 1 or (impl in (3, 7) and n < 256):
         return 'sweep_tma_kernel'
     if impl == 2:
         return 'kstar_slices_kernel + sweep_i8_kernel'
-    if impl == 4 or (impl == 3 and n < 1536):
+    if impl == 4 or (impl in (3, 7) and n < 1536):
         return 'sweep_i8f_kernel'
+    if impl == 6:
+        return 'sweep_i8p_kernel'
     return 'sweep_i8c_kernel'
 
 
@@ -367,7 +371,7 @@ def main():
     ap.add_argument('--candidates', type=int, default=1 << 24)
     ap.add_argument('--cpu-sample', type=int, default=1 << 18)
     ap.add_argument('--sweep-impl', type=int, default=3,
-                    help='3 = library default (cooperative int8-sliced sweep from 1536 observations), 5 = the same forced, '
+                    help='3 = library default (cooperative int8-sliced sweep from 1536 observations), 5 = the same forced, 6 = its paired form, '
                          '4 = fused int8-sliced (one CTA per tile), '
                          '2 = int8-sliced as two kernels, 1 = FP64 DMMA, 0 = plain-load cross-check')
     ap.add_argument('--i8-operand', type=int, default=0, help='0 = A planes through tensor memory, 1 = from shared memory')

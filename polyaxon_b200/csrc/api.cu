@@ -87,7 +87,7 @@ struct plx_bo {
   double* d_out[3] = {nullptr, nullptr, nullptr}; size_t out_cap = 0;
   cudaEvent_t ev_copy[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
   std::vector<cudaEvent_t> ev_pool;
-  int sweep_impl = 3, sweep_dbg = 0, lml_batch_limit = 0, i8_a_from_smem = 0, fit_apply = 1, fit_small = 1, refine_persist = 1;
+  int sweep_impl = 3, sweep_dbg = 0, lml_batch_limit = 0, i8_a_from_smem = 0, fit_apply = 1, fit_small = 1, refine_persist = 1, potf_fused = 1;
   double* d_fs = nullptr; size_t fs_cap = 0;      // one-launch fit (fit_small.cuh): starts | per-run results      // 3 = choose per GP state, see launch_sweep
   double last_ms = 0.0; long long last_launches = 0;
 
@@ -226,6 +226,7 @@ extern "C" int plx_bo_create(int device, plx_bo_handle* out) {
   }
   // opt in to large dynamic shared memory once
   cudaFuncSetAttribute(potf2_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, POTF_SMEM);
+  cudaFuncSetAttribute(potf2_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, POTF_SMEM);
   cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FIT_SMEM);
   cudaFuncSetAttribute(chol_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FIT_SMEM);
   cudaFuncSetAttribute(trtri_t_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FIT_SMEM);
@@ -289,6 +290,7 @@ extern "C" int plx_bo_set_option(plx_bo_handle h, const char* name, long long va
   if (!h || !name) return PLX_ERR_INVALID;
   if (std::strcmp(name, "sweep_impl") == 0 && value >= 0 && value <= 7) { h->sweep_impl = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "lml_batch_limit") == 0 && value >= 0) { h->lml_batch_limit = static_cast<int>(value); return PLX_OK; }
+  if (std::strcmp(name, "potf_fused") == 0 && (value == 0 || value == 1)) { h->potf_fused = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "refine_persist") == 0 && (value == 0 || value == 1)) { h->refine_persist = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "fit_small") == 0 && value >= 0 && value <= 2) { h->fit_small = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "fit_apply") == 0 && (value == 0 || value == 1)) { h->fit_apply = static_cast<int>(value); return PLX_OK; }
@@ -402,7 +404,8 @@ static int launch_lml(plx_bo* h, int B, bool want_grad) {
   cudaStream_t s2 = h->fact_stream;
   cudaEvent_t ev_diag = h->ev_copy[0], ev_fact = h->ev_done[0];
   auto syrk_tiles = [&](int jlo, int jhi) { int t = 0; for (int j = jlo; j < jhi; ++j) t += nb - j; return t; };
-  potf2_inv_kernel<<<B, 256, POTF_SMEM, st>>>(h->bp, 0, n, npad, h->d_logdet, h->d_info);
+  auto potf2 = h->potf_fused ? potf2_fused_kernel : potf2_inv_kernel;     // factor + inverse in one pass of 128 steps, or in two
+  potf2<<<B, 256, POTF_SMEM, st>>>(h->bp, 0, n, npad, h->d_logdet, h->d_info);
   LAUNCH_CHECK("potf2_inv_kernel");
   for (int p0 = 0; p0 < nb; p0 += PANEL) {
     const int p1 = std::min(p0 + PANEL, nb);
@@ -422,7 +425,7 @@ static int launch_lml(plx_bo* h, int B, bool want_grad) {
       LAUNCH_CHECK("chol_syrk_kernel");
       CK(cudaEventRecord(ev_diag, st));
       CK(cudaStreamWaitEvent(s2, ev_diag, 0));
-      potf2_inv_kernel<<<B, 256, POTF_SMEM, s2>>>(h->bp, k + 1, n, npad, h->d_logdet, h->d_info);
+      potf2<<<B, 256, POTF_SMEM, s2>>>(h->bp, k + 1, n, npad, h->d_logdet, h->d_info);
       LAUNCH_CHECK("potf2_inv_kernel");
       CK(cudaEventRecord(ev_fact, s2));
       if (tiles > 1) {

@@ -591,6 +591,166 @@ __global__ void __launch_bounds__(256) potf2_inv_kernel(BatchPtrs bp, int k, int
 }
 
 // ---------------------------------------------------------------------------------------------
+// Fused form of the diagonal-block kernel: the factorisation and the inversion of the factor advance TOGETHER, one
+// column step each per barrier, instead of 128 steps of one after 128 steps of the other.  Both updates of step j
+// need the same thing, column j of L:
+//   trailing matrix   A[i][c] -= L[i][j] L[c][j]                (i, c > j)
+//   rows of L^-1      R[i][c] -= L[i][j] W[j][c]                (i > j, c <= j),  W[j][.] = R[j][.] / l_jj
+// (R starts as the identity; row j of R is complete after step j - 1 and is published UNSCALED, because l_jj is only
+// known at step j; it is scaled where it is consumed).  The serial chain per step is the factor's alone -- pivot,
+// reciprocal root, next column -- so the 2 x 128 dependent steps of potf2_inv_kernel become 128.
+// Same register tiling: thread (ti, tc) holds A[ti + 16 a][tc + 16 q] and R[ti + 16 a][tc + 16 q]; in block column
+// BJ the live parts are a, q >= BJ of A and a >= BJ, q <= BJ of R (column block BJ of R is created when it is
+// first needed, which keeps the live registers at 9 (8 - BJ) values).
+// ---------------------------------------------------------------------------------------------
+template <int BJ>
+__device__ __forceinline__ bool potf_fused_cols(double (&accA)[8][8], double (&accW)[8][8], double* S,
+                                                double (*colbuf)[128], double (*rowbuf)[128], double* dl, double* wdiag,
+                                                int* bad, int k, int m, int ti, int tc, int tid) {
+  // column block BJ of R: the identity (rows of earlier blocks never reach it)
+#pragma unroll
+  for (int a = BJ; a < 8; ++a) accW[a][BJ] = (a == BJ && ti == tc) ? 1.0 : 0.0;
+#pragma unroll 1
+  for (int jj = 0; jj < 16; ++jj) {
+    const int j = 16 * BJ + jj;
+    if (j >= m) return false;
+    const double* cb = colbuf[j & 1];
+    double* cnx = colbuf[(j + 1) & 1];
+    const double* rb = rowbuf[j & 1];
+    double* rnx = rowbuf[(j + 1) & 1];
+    double ajj = cb[j];
+    if (!(ajj > 0.0)) {                 // non-positive or NaN pivot: not positive definite
+      if (tid == 0 && *bad == 0) *bad = k * 128 + j + 1;
+      ajj = 1.0;
+    }
+    double y0;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y0) : "d"(ajj));
+    const double e0 = fma(ajj, -(y0 * y0), 1.0);
+    double inv = fma(fma(e0, 0.375, 0.5), y0 * e0, y0);
+    double ljj = ajj * inv;
+    ljj = fma(fma(ljj, -ljj, ajj), 0.5 * inv, ljj);
+    inv = fma(fma(-ljj, inv, 1.0), inv, inv);            // 1 / ljj
+    double li[8], lc[8], wr[8];
+#pragma unroll
+    for (int a = BJ; a < 8; ++a) { li[a] = cb[ti + 16 * a] * inv; lc[a] = cb[tc + 16 * a] * inv; }
+#pragma unroll
+    for (int q = 0; q <= BJ; ++q) wr[q] = rb[tc + 16 * q] * inv;          // W[j][tc + 16 q] (zero beyond column j)
+    if (jj < 15) {
+      if (tc == jj + 1) {
+#pragma unroll
+        for (int a = BJ; a < 8; ++a) cnx[ti + 16 * a] = fma(-li[a], lc[BJ], accA[a][BJ]);
+      }
+      if (ti == jj + 1) {
+#pragma unroll
+        for (int q = 0; q <= BJ; ++q) rnx[tc + 16 * q] = fma(-li[BJ], wr[q], accW[BJ][q]);
+      }
+    } else if constexpr (BJ < 7) {
+      if (tc == 0) {
+#pragma unroll
+        for (int a = BJ + 1; a < 8; ++a) cnx[ti + 16 * a] = fma(-li[a], lc[BJ + 1], accA[a][BJ + 1]);
+      }
+      if (ti == 0) {
+#pragma unroll
+        for (int q = 0; q <= BJ; ++q) rnx[tc + 16 * q] = fma(-li[BJ + 1], wr[q], accW[BJ + 1][q]);
+        rnx[tc + 16 * (BJ + 1)] = (tc == 0) ? 1.0 : 0.0;                  // the identity part of row j + 1
+      }
+    }
+    if (tc == jj) {
+#pragma unroll
+      for (int a = BJ; a < 8; ++a) { const int i = ti + 16 * a; if (i > j) S[i * POTF_LD + j] = li[a]; }
+    }
+    if (tid < j) S[tid * POTF_LD + j] = rb[tid] * inv;                    // W[j][c], c < j, parked at S[c][j]
+    if (tid == 0) { dl[j] = ljj; wdiag[j] = inv; }
+    __syncthreads();
+#pragma unroll
+    for (int a = BJ; a < 8; ++a) {
+#pragma unroll
+      for (int q = BJ; q < 8; ++q) accA[a][q] = fma(-li[a], lc[q], accA[a][q]);
+#pragma unroll
+      for (int q = 0; q <= BJ; ++q) accW[a][q] = fma(-li[a], wr[q], accW[a][q]);
+    }
+  }
+  return true;
+}
+
+__global__ void __launch_bounds__(256) potf2_fused_kernel(BatchPtrs bp, int k, int n, int npad,
+                                                          double* __restrict__ logdet, int* __restrict__ info) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double* S = reinterpret_cast<double*>(smem_raw);        // S[i][j] at S[i*129 + j]
+  double* dl = S + 128 * POTF_LD;                         // diagonal of L
+  double* wdiag = dl + 128;                               // diagonal of W
+  const int b = blockIdx.x, tid = threadIdx.x;
+  const size_t ld = npad;
+  const double* A = bp.A + b * bp.mat_stride + (static_cast<size_t>(k) * 128) * ld + k * 128;
+  for (int e = tid; e < 128 * 128; e += 256) {
+    const int i = e >> 7, j = e & 127;
+    S[i * POTF_LD + j] = A[i * ld + j];
+  }
+  __shared__ int bad;
+  __shared__ double colbuf[2][128];
+  __shared__ double rowbuf[2][128];
+  if (tid == 0) bad = 0;
+  const int m = min(128, max(0, n - k * 128));
+  const int tc = tid & 15, ti = tid >> 4;
+  double accA[8][8], accW[8][8];
+  __syncthreads();
+#pragma unroll
+  for (int a = 0; a < 8; ++a)
+#pragma unroll
+    for (int q = 0; q < 8; ++q) accA[a][q] = S[(ti + 16 * a) * POTF_LD + tc + 16 * q];
+  if (tc == 0) {
+#pragma unroll
+    for (int a = 0; a < 8; ++a) colbuf[0][ti + 16 * a] = accA[a][0];
+  }
+  if (tid < 128) rowbuf[0][tid] = (tid == 0) ? 1.0 : 0.0;        // row 0 of R = e_0
+  __syncthreads();
+  // everything the column steps do not write must read as zero afterwards (strict upper triangle beyond the
+  // parked rows, rows and columns of the identity padding)
+  for (int e = tid; e < 128 * POTF_LD; e += 256) S[e] = 0.0;
+  if (tid < 128) { dl[tid] = 1.0; wdiag[tid] = 1.0; }
+  __syncthreads();
+  potf_fused_cols<0>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid) &&
+      potf_fused_cols<1>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid) &&
+      potf_fused_cols<2>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid) &&
+      potf_fused_cols<3>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid) &&
+      potf_fused_cols<4>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid) &&
+      potf_fused_cols<5>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid) &&
+      potf_fused_cols<6>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid) &&
+      potf_fused_cols<7>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid);
+  __syncthreads();
+  if (tid < 128) S[tid * POTF_LD + tid] = dl[tid];
+  __syncthreads();
+  double* Lo = bp.L + b * bp.mat_stride + (static_cast<size_t>(k) * 128) * ld + k * 128;
+  double* Uo = bp.U + b * bp.mat_stride + (static_cast<size_t>(k) * 128) * ld + k * 128;
+  double* Wo = bp.W + b * bp.blk_stride + static_cast<size_t>(k) * 128 * 128;
+  double* Zo = bp.A + b * bp.mat_stride + (static_cast<size_t>(k) * 128) * ld + k * 128;
+  for (int e = tid; e < 128 * 128; e += 256) {
+    const int i = e >> 7, j = e & 127;
+    double l, w;
+    if (i > j) { l = S[i * POTF_LD + j]; w = S[j * POTF_LD + i]; }
+    else if (i == j) { l = S[i * POTF_LD + i]; w = wdiag[i]; }
+    else { l = 0.0; w = 0.0; }
+    Lo[i * ld + j] = l;
+    Wo[i * 128 + j] = w;
+    Zo[i * ld + j] = w;
+    double u;
+    if (j > i) u = S[i * POTF_LD + j]; else if (i == j) u = wdiag[i]; else u = 0.0;
+    Uo[i * ld + j] = u;
+  }
+  if (tid < 32) {
+    double s = 0.0;
+    for (int i = tid; i < 128; i += 32)
+      if (k * 128 + i < n) s += log(S[i * POTF_LD + i]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (tid == 0) {
+      logdet[b] += s;
+      if (bad != 0 && info[b] == 0) info[b] = bad;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // 128x128-tile DMMA kernels of the blocked algorithms.  Each CTA: one output tile, 384 threads:
 // warps 0-7 run the tensor pipe (232 registers), warps 8-11 are the producer warpgroup (40
 // registers), whose elected lane streams 16-wide K-chunks of both operands through a ring of
