@@ -221,3 +221,63 @@ def test_single_record_merge_carries_index_bits_and_the_winning_row():
         assert a == (3.0, 2, [1.0, 2.0])
         assert b == (1.0, 8, [7.0, 8.0])
         assert c == (1.0, (1 << 62) + 12346)
+
+
+class _FakeSweepHandle(_FakeHandle):
+    """Host-side stand-in with a toy acquisition (sum of the coordinates) so that the sharded warm-up of
+    UtilityFunction can run on CPU: every rank holds the candidates it was given and sweeps the rows it is asked for."""
+    d = 3
+
+    def candidates_draw(self, rng, low, high, N, key=None, first=0, count=None):
+        return False                                     # "odd stream position": the caller draws on the host
+
+    def candidates_set(self, Xc, key=None):
+        self.Xc = np.asarray(Xc)
+        self.resident_key = key
+
+    def sweep_resident_range(self, first, count, acq, y_max=0.0, kappa=0.0, eps=0.0):
+        if count == 0:
+            return float('nan'), -1, np.zeros(self.d)
+        ys = self.Xc[first:first + count].sum(axis=1)
+        j = int(np.argmax(ys))
+        return float(ys[j]), first + j, self.Xc[first + j].copy()
+
+    def last_sweep_clamped(self):
+        return 0
+
+
+def _warmup_worker(rank, world, port, out):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    from polyaxon_b200.hpsearch.search_managers.bayesian_optimization.acquisition_function import UtilityFunction
+    uf = UtilityFunction.__new__(UtilityFunction)
+    uf.random_generator = np.random.RandomState(42)
+    h = _FakeSweepHandle()
+    bounds = np.array([[0.0, 1.0], [-1.0, 2.0], [5.0, 6.0]])
+    res = []
+    for _ in range(2):                                   # second call: the resident-matrix cache of the group is hit
+        uf.random_generator = np.random.RandomState(42)
+        max_acq, x_max, x_seeds = uf._warmup(h, 0, dict(y_max=0.0, kappa=0.0, eps=0.0), bounds, 1001, 4)
+        res.append((max_acq, x_max.tolist(), x_seeds.tolist(), uf.random_generator.uniform()))
+    out[rank] = res
+    dist.destroy_process_group()
+
+
+def test_sharded_warmup_returns_the_single_process_answer_on_every_rank():
+    """Each rank sweeps its block of the one candidate matrix and a single all-gather of {value, index, row} records
+    gives every rank the global winner's row and leaves every generator where numpy would be."""
+    port = _free_port()
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_warmup_worker, args=(2, port, out), nprocs=2, join=True)
+    rs = np.random.RandomState(42)
+    bounds = np.array([[0.0, 1.0], [-1.0, 2.0], [5.0, 6.0]])
+    x_tries = rs.uniform(bounds[:, 0], bounds[:, 1], size=(1001, 3))
+    x_seeds = rs.uniform(bounds[:, 0], bounds[:, 1], size=(4, 3))
+    nxt = rs.uniform()
+    j = int(np.argmax(x_tries.sum(axis=1)))
+    for rank in range(2):
+        for max_acq, x_max, seeds, after in out[rank]:
+            assert max_acq == x_tries[j].sum() and x_max == x_tries[j].tolist()
+            assert seeds == x_seeds.tolist() and after == nxt

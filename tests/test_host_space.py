@@ -198,3 +198,52 @@ def test_bo_iteration_config_round_trip():
         get_iteration_config(SearchAlgorithms.BO, None)
     with pytest.raises(ValueError):
         BOIterationConfig.from_dict({'iteration': 1, 'experiments_metrics': [[1, 2, 3]]})
+
+
+def test_models_sharing_a_handle_put_their_own_state_back():
+    """every model of a thread shares one C-ABI handle; in the reference each UtilityFunction owns its
+    GaussianProcessRegressor.  A model that finds another model's state on the handle re-establishes its own
+    before predicting, and an unfitted model refuses."""
+    import numpy as np
+    import pytest
+    from polyaxon_b200.hpsearch.search_managers.bayesian_optimization.acquisition_function import DeviceGaussianProcess
+
+    class Handle(object):
+        device = 0
+
+        def __init__(self):
+            self.calls, self.owner, self.held = [], None, None
+
+        def set_data(self, X, y, kernel, nu, jitter):
+            self.calls.append(('set_data', float(X[0, 0])))
+            self.owner = None
+
+        def fit(self, theta0, restarts, bounds, apply=True):
+            self.calls.append(('fit',))
+            return 0.5, -1.0, np.array([[theta0, 0.5, -1.0, 3.0]])
+
+        def set_theta(self, theta):
+            self.calls.append(('set_theta', theta))
+
+        def sweep(self, X, acq, y_max, kappa=0.0, dump=False):
+            self.calls.append(('sweep',))
+            return 0.0, 0, X[0], np.zeros(len(X)), np.ones(len(X)), np.zeros(len(X))
+
+        def last_sweep_clamped(self):
+            return 0
+
+    h = Handle()
+    a = DeviceGaussianProcess('rbf', 1.0, 1.5, 0, np.random.RandomState(1), handle=h)
+    b = DeviceGaussianProcess('rbf', 1.0, 1.5, 0, np.random.RandomState(1), handle=h)
+    with pytest.raises(RuntimeError):
+        a.predict(np.zeros((1, 2)))
+    a.fit(np.full((3, 2), 1.0), np.arange(3.0))
+    b.fit(np.full((3, 2), 2.0), np.arange(3.0))
+    del h.calls[:]
+    b.predict(np.zeros((1, 2)))                            # b's state is on the handle: nothing to restore
+    assert h.calls == [('sweep',)]
+    a.predict(np.zeros((1, 2)))                            # a's is not: data and theta go back first
+    assert h.calls[1:] == [('set_data', 1.0), ('set_theta', 0.5), ('sweep',)]
+    del h.calls[:]
+    a.predict(np.zeros((1, 2)))
+    assert h.calls == [('sweep',)]
