@@ -22,6 +22,9 @@
 #pragma once
 #include "sweep.cuh"
 #include "lbfgsb1d.h"
+#ifdef PLX_PROFILE
+#include <cstdio>
+#endif
 
 namespace plx {
 
@@ -412,12 +415,14 @@ __global__ void __launch_bounds__(128) refine_step_kernel(RefineParams p) {
 constexpr int RF_PERSIST_NMAX = 256;
 constexpr int RF_PERSIST_DSMEM = 256;             // per-seed vectors in shared memory up to this many dimensions
 constexpr int RF_PERSIST_ZSMEM = 128;             // L^-1 in shared memory up to this many observations
+constexpr int RF_PERSIST_CHUNK = 32;              // above that: rows of L^-1 staged per pass through shared memory
 
 // dynamic shared memory of refine_persist_kernel, in doubles (the host passes the same number)
 inline size_t rf_persist_smem_doubles(int n, int npad, int d) {
   size_t t = static_cast<size_t>(2) * d + static_cast<size_t>(4) * npad;
   if (d <= RF_PERSIST_DSMEM) t += rf_vec_stride(d);
-  if (n <= RF_PERSIST_ZSMEM) t += static_cast<size_t>(n) * n;
+  if (n <= RF_PERSIST_ZSMEM) t += static_cast<size_t>(n) * (n | 1);
+  else t += static_cast<size_t>(RF_PERSIST_CHUNK) * (n | 1);          // staging of RF_PERSIST_CHUNK rows of L^-1 at a time
   return t;
 }
 
@@ -444,17 +449,27 @@ __global__ void __launch_bounds__(128) refine_persist_kernel(RefineParams p, int
   const double* Zp = p.Z;
   int zld = p.npad;
   if (p.n <= RF_PERSIST_ZSMEM) {
+    zld = p.n | 1;                                   // odd leading dimension: a thread per ROW reads without bank conflicts
     for (int e = tid; e < p.n * p.n; e += 128) {
       const int i = e / p.n, j = e - i * p.n;
-      next[e] = (j <= i) ? p.Z[static_cast<size_t>(i) * p.npad + j] : 0.0;
+      next[i * zld + j] = (j <= i) ? p.Z[static_cast<size_t>(i) * p.npad + j] : 0.0;
     }
-    Zp = next; zld = p.n;
+    Zp = next;
   }
+  double* chunk = next;                              // n > RF_PERSIST_ZSMEM: staging of RF_PERSIST_CHUNK rows
+  const bool staged = p.n > RF_PERSIST_ZSMEM;
+  if (staged) zld = p.n | 1;
   __syncthreads();
+#ifdef PLX_PROFILE
+  long long tk = 0, tv = 0, tw = 0, ts = 0; int nr = 0;
+#endif
   for (int round = 0; round < max_rounds; ++round) {
     if (tid == 0) sh_phase = q.sc[s].phase;
     __syncthreads();
     if (sh_phase == 2) break;
+#ifdef PLX_PROFILE
+    long long c0 = clock64(); ++nr;
+#endif
     const double* x = rf_x(q, s);
     for (int j = tid; j < p.npad; j += 128) {
       double kv = 0.0, kp = 0.0;
@@ -468,44 +483,112 @@ __global__ void __launch_bounds__(128) refine_persist_kernel(RefineParams p, int
       kvs[j] = kv; kps[j] = kp;
     }
     __syncthreads();
-    // v_i = sum_{j <= i} Z[i][j] k*_j: four rows per warp in flight (lane-strided partial sums as in refine_v_kernel)
-    for (int i0 = warp * 4; i0 < p.n; i0 += 16) {
-      double a[4] = {0.0, 0.0, 0.0, 0.0};
+#ifdef PLX_PROFILE
+    long long c1 = clock64(); tk += c1 - c0;
+#endif
+    if (!staged) {
+      // v_i = sum_{j <= i} Z[i][j] k*_j: a thread per row, eight products in flight (row-wise reads are free of bank
+      // conflicts thanks to the odd leading dimension)
+      for (int i = tid; i < p.n; i += 128) {
+        const double* Zi = Zp + static_cast<size_t>(i) * zld;
+        double acc[4] = {0.0, 0.0, 0.0, 0.0};
+        int j = 0;
+        for (; j + 8 <= i + 1; j += 8) {
+          double z[8];
 #pragma unroll
-      for (int r = 0; r < 4; ++r) {
-        const int i = i0 + r;
-        if (i < p.n) {
-          const double* Zi = Zp + static_cast<size_t>(i) * zld;
-          for (int j = lane; j <= i; j += 32) a[r] += Zi[j] * kvs[j];
+          for (int u = 0; u < 8; ++u) z[u] = Zi[j + u];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) acc[u & 3] += z[u] * kvs[j + u];
         }
+        for (; j <= i; ++j) acc[0] += Zi[j] * kvs[j];
+        vs[i] = (acc[0] + acc[1]) + (acc[2] + acc[3]);
       }
+      __syncthreads();
+#ifdef PLX_PROFILE
+      tv += clock64() - c1;
+#endif
+      // w_j = sum_{i >= j} Z[i][j] v_i, a thread per column
+      for (int j = tid; j < p.n; j += 128) {
+        double acc[4] = {0.0, 0.0, 0.0, 0.0};
+        int i = j;
+        for (; i + 8 <= p.n; i += 8) {
+          double z[8];
 #pragma unroll
-      for (int r = 0; r < 4; ++r) {
+          for (int u = 0; u < 8; ++u) z[u] = Zp[static_cast<size_t>(i + u) * zld + j];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) a[r] += __shfl_xor_sync(0xffffffffu, a[r], o);
-        if (lane == 0 && i0 + r < p.n) vs[i0 + r] = a[r];
+          for (int u = 0; u < 8; ++u) acc[u & 3] += z[u] * vs[i + u];
+        }
+        for (; i < p.n; ++i) acc[0] += Zp[static_cast<size_t>(i) * zld + j] * vs[i];
+        ws[j] = (acc[0] + acc[1]) + (acc[2] + acc[3]);
       }
+      __syncthreads();
+    } else {
+      // ONE pass over L^-1 from L2: RF_PERSIST_CHUNK rows at a time are staged in shared memory with all threads'
+      // loads in flight; v of those rows needs only k*, and w accumulates the rows' contributions right away
+      for (int j = tid; j < p.n; j += 128) ws[j] = 0.0;
+      for (int r0 = 0; r0 < p.n; r0 += RF_PERSIST_CHUNK) {
+        const int rows = min(RF_PERSIST_CHUNK, p.n - r0), width = r0 + rows;      // columns that can be non-zero
+        // warp w stages rows w, w + 4, ... two at a time: 16 independent loads per thread in flight (n <= 256)
+        for (int rp = warp; rp < rows; rp += 8) {
+          double z[2][8];
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            const int ri = rp + 4 * u;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+              const int j = lane + 32 * c;
+              z[u][c] = (ri < rows && j <= r0 + ri) ? p.Z[static_cast<size_t>(r0 + ri) * p.npad + j] : 0.0;
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            const int ri = rp + 4 * u;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+              const int j = lane + 32 * c;
+              if (ri < rows && j < width) chunk[ri * zld + j] = z[u][c];
+            }
+          }
+        }
+        __syncthreads();
+        {                                                    // four threads per row
+          const int ri = tid >> 2, seg = tid & 3;
+          double a = 0.0;
+          if (ri < rows)
+            for (int j = seg; j <= r0 + ri; j += 4) a += chunk[ri * zld + j] * kvs[j];
+          a += __shfl_xor_sync(0xffffffffu, a, 1);
+          a += __shfl_xor_sync(0xffffffffu, a, 2);
+          if (seg == 0 && ri < rows) vs[r0 + ri] = a;
+        }
+        __syncthreads();
+        for (int j = tid; j < width; j += 128) {
+          double a = 0.0;
+          for (int ri = 0; ri < rows; ++ri) a += chunk[ri * zld + j] * vs[r0 + ri];
+          ws[j] += a;
+        }
+        __syncthreads();
+      }
+#ifdef PLX_PROFILE
+      tv += clock64() - c1;
+#endif
     }
-    __syncthreads();
-    // w_j = sum_{i >= j} Z[i][j] v_i, a thread per column: eight rows in flight (the loads come from L2 above 128
-    // observations, and their latency, not their number, is what a lone CTA waits for)
-    for (int j = tid; j < p.n; j += 128) {
-      double acc[4] = {0.0, 0.0, 0.0, 0.0};
-      int i = j;
-      for (; i + 8 <= p.n; i += 8) {
-        double z[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) z[u] = Zp[static_cast<size_t>(i + u) * zld + j];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) acc[u & 3] += z[u] * vs[i + u];
-      }
-      for (; i < p.n; ++i) acc[0] += Zp[static_cast<size_t>(i) * zld + j] * vs[i];
-      ws[j] = (acc[0] + acc[1]) + (acc[2] + acc[3]);
-    }
-    __syncthreads();
+#ifdef PLX_PROFILE
+    long long c2 = clock64();
+#endif
+#ifdef PLX_PROFILE
+    long long c3 = clock64(); tw += c3 - c2;   // (v and w are timed together under tv)
+#endif
     refine_step_body(q, s, rf_grad_smem);
     __syncthreads();
+#ifdef PLX_PROFILE
+    ts += clock64() - c3;
+#endif
   }
+#ifdef PLX_PROFILE
+  if (tid == 0 && nr > 0)
+    printf("refine seed %d n=%d d=%d rounds %d: kstar %lld v %lld w %lld step %lld clk per round\n", s, p.n, p.d, nr, tk / nr, tv / nr,
+           tw / nr, ts / nr);
+#endif
   if (vec_smem) {
     // the host reads the final point (first d doubles of the block); the rest is kept consistent too
     const double* mine = rf_x(q, s);
