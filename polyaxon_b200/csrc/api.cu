@@ -384,13 +384,12 @@ static int ensure_batch(plx_bo* h, int B) {
 static int launch_lml(plx_bo* h, int B, bool want_grad) {
   cudaStream_t st = h->stream;
   const int npad = h->npad, nb = h->nb, n = h->n;
-  CK(cudaMemsetAsync(h->d_logdet, 0, sizeof(double) * B, st));
-  CK(cudaMemsetAsync(h->d_info, 0, sizeof(int) * B, st));
   {
     int r;
     if ((r = ensure(h, h->d_xs, h->xs_cap, static_cast<size_t>(B) * n * h->d)) != PLX_OK) return r;
   }
-  scale_x_batch_kernel<<<dim3((n * h->d + 255) / 256, B), 256, 0, st>>>(h->dX, n * h->d, h->d_thetas, h->d_xs);
+  scale_x_batch_kernel<<<dim3((n * h->d + 255) / 256, B), 256, 0, st>>>(h->dX, n * h->d, h->d_thetas, h->d_xs, h->d_logdet,
+                                                                       h->d_info);
   LAUNCH_CHECK("scale_x_batch_kernel");
   const int t32 = npad / 32;
   kmat_kernel<0><<<dim3(t32 * (t32 + 1) / 2, 1, B), 256, 0, st>>>(h->d_xs, n, h->d, npad, h->kind, h->mg, h->jitter,
@@ -480,11 +479,25 @@ static int eval_lml(plx_bo* h, const double* thetas, int B, double* lml, double*
     const int b = std::min(limit, B - first);
     if ((r = ensure_batch(h, b)) != PLX_OK) return r;
     h->state_factor_valid = false;
-    CK(cudaMemcpyAsync(h->d_thetas, thetas + first, sizeof(double) * b, cudaMemcpyHostToDevice, h->stream));
+    // thetas in and results out through pinned memory: the copies queue on the stream and one synchronisation
+    // collects both results (pageable device->host copies block one by one)
+    const bool pinned = static_cast<size_t>(3) * b <= h->pin_cap;
+    if (pinned) {
+      std::memcpy(h->h_pin, thetas + first, sizeof(double) * b);
+      CK(cudaMemcpyAsync(h->d_thetas, h->h_pin, sizeof(double) * b, cudaMemcpyHostToDevice, h->stream));
+    } else {
+      CK(cudaMemcpyAsync(h->d_thetas, thetas + first, sizeof(double) * b, cudaMemcpyHostToDevice, h->stream));
+    }
     if ((r = launch_lml(h, b, grad != nullptr)) != PLX_OK) return r;
-    CK(cudaMemcpyAsync(lml + first, h->d_lml, sizeof(double) * b, cudaMemcpyDeviceToHost, h->stream));
-    if (grad) CK(cudaMemcpyAsync(grad + first, h->d_grad, sizeof(double) * b, cudaMemcpyDeviceToHost, h->stream));
+    double* out_l = pinned ? h->h_pin + b : lml + first;
+    double* out_g = pinned ? h->h_pin + 2 * b : (grad ? grad + first : nullptr);
+    CK(cudaMemcpyAsync(out_l, h->d_lml, sizeof(double) * b, cudaMemcpyDeviceToHost, h->stream));
+    if (grad) CK(cudaMemcpyAsync(out_g, h->d_grad, sizeof(double) * b, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
+    if (pinned) {
+      std::memcpy(lml + first, out_l, sizeof(double) * b);
+      if (grad) std::memcpy(grad + first, out_g, sizeof(double) * b);
+    }
   }
   return PLX_OK;
 }

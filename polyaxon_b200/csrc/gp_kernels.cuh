@@ -282,10 +282,12 @@ struct BatchPtrs {
 constexpr int DCH = 32;
 
 // X / length_scale for every theta of the batch: Xs[b][n][d] (the division sklearn does, done once)
+// (also clears the batch member's log-determinant and status cells: the first kernel of every evaluation)
 __global__ void scale_x_batch_kernel(const double* __restrict__ X, int nd, const double* __restrict__ thetas,
-                                     double* __restrict__ Xs) {
+                                     double* __restrict__ Xs, double* __restrict__ logdet, int* __restrict__ info) {
   const int b = blockIdx.y, e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e < nd) Xs[static_cast<size_t>(b) * nd + e] = X[e] / exp(thetas[b]);
+  if (e == 0) { logdet[b] = 0.0; info[b] = 0; }
 }
 
 template <int MODE>
