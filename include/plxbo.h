@@ -58,6 +58,8 @@ int plx_bo_set_stream(plx_bo_handle h, void* stream);
  * "fit_small" (1 [default]: with at most 64 observations plx_gp_fit runs every optimiser run from start to
  * convergence in ONE launch, optimiser included; 2: the same up to 128 observations (slower than the batched
  * sequence there, kept for tests); 0: always the batched launch sequence used for larger sets);
+ * "blocking_sync" (0 [default]: calls wait for the GPU by spinning on the stream; 1: the host thread sleeps on an
+ * event instead -- for processes whose worker threads outnumber their cores);
  * "potf_fused" (1 [default]: the diagonal 128-blocks of the fit are factorised and inverted in one pass of 128 column
  * steps; 0: in two passes, the round-1 kernel, kept for A/B runs);
  * "refine_persist" (1 [default]: with at most 256 observations plx_acq_refine runs every seed from start to

@@ -87,7 +87,8 @@ struct plx_bo {
   double* d_out[3] = {nullptr, nullptr, nullptr}; size_t out_cap = 0;
   cudaEvent_t ev_copy[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
   std::vector<cudaEvent_t> ev_pool;
-  int sweep_impl = 3, sweep_dbg = 0, lml_batch_limit = 0, i8_a_from_smem = 0, fit_apply = 1, fit_small = 1, refine_persist = 1, potf_fused = 1;
+  int sweep_impl = 3, sweep_dbg = 0, lml_batch_limit = 0, i8_a_from_smem = 0, fit_apply = 1, fit_small = 1, refine_persist = 1, potf_fused = 1, blocking_sync = 0;
+  cudaEvent_t ev_block = nullptr;
   double* d_fs = nullptr; size_t fs_cap = 0;      // one-launch fit (fit_small.cuh): starts | per-run results      // 3 = choose per GP state, see launch_sweep
   double last_ms = 0.0; long long last_launches = 0;
 
@@ -106,6 +107,19 @@ struct plx_bo {
   int* rf_active = nullptr;
   long long last_refine_rounds = 0;
 };
+
+// Wait for the handle's stream.  The default spins on the stream (lowest latency); with the "blocking_sync" option the
+// host thread sleeps on an event instead, which is what a process wants whose worker threads outnumber its cores
+// (polyaxon_b200.groups: 8 threads per rank, 8 ranks per box).
+static cudaError_t sync_stream(plx_bo* h) {
+  if (!h->blocking_sync) return cudaStreamSynchronize(h->stream);
+  if (!h->ev_block) {
+    const cudaError_t e = cudaEventCreateWithFlags(&h->ev_block, cudaEventBlockingSync | cudaEventDisableTiming);
+    if (e != cudaSuccess) return e;
+  }
+  const cudaError_t e = cudaEventRecord(h->ev_block, h->stream);
+  return e != cudaSuccess ? e : cudaEventSynchronize(h->ev_block);
+}
 
 #define CK(call)                                                                            \
   do {                                                                                      \
@@ -274,6 +288,7 @@ extern "C" void plx_bo_destroy(plx_bo_handle h) {
   if (h->h_pin) cudaFreeHost(h->h_pin);
   for (int i = 0; i < 2; ++i) { if (h->ev_copy[i]) cudaEventDestroy(h->ev_copy[i]); if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]); }
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
+  if (h->ev_block) cudaEventDestroy(h->ev_block);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
   if (h->fact_stream) cudaStreamDestroy(h->fact_stream);
@@ -290,6 +305,7 @@ extern "C" int plx_bo_set_option(plx_bo_handle h, const char* name, long long va
   if (!h || !name) return PLX_ERR_INVALID;
   if (std::strcmp(name, "sweep_impl") == 0 && value >= 0 && value <= 7) { h->sweep_impl = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "lml_batch_limit") == 0 && value >= 0) { h->lml_batch_limit = static_cast<int>(value); return PLX_OK; }
+  if (std::strcmp(name, "blocking_sync") == 0 && (value == 0 || value == 1)) { h->blocking_sync = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "potf_fused") == 0 && (value == 0 || value == 1)) { h->potf_fused = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "refine_persist") == 0 && (value == 0 || value == 1)) { h->refine_persist = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "fit_small") == 0 && value >= 0 && value <= 2) { h->fit_small = static_cast<int>(value); return PLX_OK; }
@@ -323,7 +339,7 @@ extern "C" int plx_gp_set_data(plx_bo_handle h, const double* X, const double* y
   CK(cudaMemsetAsync(h->dy, 0, sizeof(double) * h->npad, h->stream));
   CK(cudaMemcpyAsync(h->dX, X, sizeof(double) * n * d, cudaMemcpyHostToDevice, h->stream));
   CK(cudaMemcpyAsync(h->dy, y, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
-  CK(cudaStreamSynchronize(h->stream));
+  CK(sync_stream(h));
   h->have_data = true;
   return PLX_OK;
 }
@@ -493,7 +509,7 @@ static int eval_lml(plx_bo* h, const double* thetas, int B, double* lml, double*
     double* out_g = pinned ? h->h_pin + 2 * b : (grad ? grad + first : nullptr);
     CK(cudaMemcpyAsync(out_l, h->d_lml, sizeof(double) * b, cudaMemcpyDeviceToHost, h->stream));
     if (grad) CK(cudaMemcpyAsync(out_g, h->d_grad, sizeof(double) * b, cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaStreamSynchronize(h->stream));
+    CK(sync_stream(h));
     if (pinned) {
       std::memcpy(lml + first, out_l, sizeof(double) * b);
       if (grad) std::memcpy(grad + first, out_g, sizeof(double) * b);
@@ -557,14 +573,14 @@ extern "C" int plx_gp_set_theta(plx_bo_handle h, double theta) {
     LAUNCH_CHECK("state_small_kernel");
     double* st = h->h_pin;
     CK(cudaMemcpyAsync(st, h->d_fs, sizeof(double) * 2, cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaStreamSynchronize(h->stream));
+    CK(sync_stream(h));
     if (st[0] != 0.0)
       return fail(h, PLX_ERR_NOT_PD, "kernel matrix is not positive definite at theta=" + std::to_string(theta));
   } else {
     transpose_kernel<<<dim3(h->npad / 32, h->npad / 32), 256, 0, h->stream>>>(h->bp.U, h->dZ, h->npad);
     LAUNCH_CHECK("transpose_kernel");
     CK(cudaMemcpyAsync(h->d_alpha_state, h->d_alpha, sizeof(double) * h->npad, cudaMemcpyDeviceToDevice, h->stream));
-    CK(cudaStreamSynchronize(h->stream));
+    CK(sync_stream(h));
   }
   if ((r = make_map(h, &h->tmZ, h->dZ, h->npad, h->npad)) != PLX_OK) return r;
   if ((r = make_map(h, &h->tmK, h->dKs, static_cast<size_t>(h->num_sms) * 128, h->npad)) != PLX_OK) return r;
@@ -583,7 +599,7 @@ extern "C" int plx_gp_get_state(plx_bo_handle h, double* L, double* alpha, doubl
   }
   if (Linv) CK(cudaMemcpy2DAsync(Linv, n * 8, h->dZ, npad * 8, n * 8, n, cudaMemcpyDeviceToHost, h->stream));
   if (alpha) CK(cudaMemcpyAsync(alpha, h->d_alpha_state, n * 8, cudaMemcpyDeviceToHost, h->stream));
-  CK(cudaStreamSynchronize(h->stream));
+  CK(sync_stream(h));
   if (L)      // the factor's strict upper triangle is never written on the device
     for (size_t i = 0; i < n; ++i) for (size_t j = i + 1; j < n; ++j) L[i * n + j] = 0.0;
   if (Linv)
@@ -604,7 +620,7 @@ extern "C" int plx_gp_append(plx_bo_handle h, const double* x_new, double y_new)
     const size_t cap = static_cast<size_t>(npad + 128) * d;
     CK(cudaMalloc(reinterpret_cast<void**>(&nx), cap * sizeof(double)));
     CK(cudaMemcpyAsync(nx, h->dX, sizeof(double) * n0 * d, cudaMemcpyDeviceToDevice, st));
-    CK(cudaStreamSynchronize(st));
+    CK(sync_stream(h));
     CK(cudaFree(h->dX));
     h->dX = nx; h->x_cap = cap;
   }
@@ -622,7 +638,7 @@ extern "C" int plx_gp_append(plx_bo_handle h, const double* x_new, double y_new)
   LAUNCH_CHECK("append_pivot_kernel");
   double lam2 = 0.0;
   CK(cudaMemcpyAsync(&lam2, piv, sizeof(double), cudaMemcpyDeviceToHost, st));
-  CK(cudaStreamSynchronize(st));
+  CK(sync_stream(h));
   if (!(lam2 > 0.0))       // nothing of the state has been touched yet
     return fail(h, PLX_ERR_NOT_PD, "gp_append: the extended kernel matrix is not positive definite (pivot^2 = " +
                                        std::to_string(lam2) + ")");
@@ -632,7 +648,7 @@ extern "C" int plx_gp_append(plx_bo_handle h, const double* x_new, double y_new)
     std::vector<double> X(static_cast<size_t>(n0 + 1) * d), y(n0 + 1);
     CK(cudaMemcpyAsync(X.data(), h->dX, sizeof(double) * n0 * d, cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(y.data(), h->dy, sizeof(double) * n0, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
+    CK(sync_stream(h));
     std::memcpy(X.data() + static_cast<size_t>(n0) * d, x_new, sizeof(double) * d);
     y[n0] = y_new;
     const double theta = h->theta;
@@ -658,7 +674,7 @@ extern "C" int plx_gp_append(plx_bo_handle h, const double* x_new, double y_new)
   LAUNCH_CHECK("trmv_lower_t_kernel");
   scale_transpose_x_kernel<<<dim3((npad + 255) / 256, d), 256, 0, st>>>(h->dX, n1, d, npad, ell, h->dXt);
   LAUNCH_CHECK("scale_transpose_x_kernel");
-  CK(cudaStreamSynchronize(st));          // y_new / lam2 live on this frame
+  CK(sync_stream(h));          // y_new / lam2 live on this frame
   h->n = n1; h->i8_state_valid = false;
   { const int nt32 = (n1 + 31) / 32; h->ntri = nt32 * (nt32 + 1) / 2; }
   return PLX_OK;
@@ -689,7 +705,7 @@ extern "C" int plx_gp_fit(plx_bo_handle h, double theta0, const double* theta_re
     fit_small_kernel<<<R, FS_THREADS, FS_SMEM, h->stream>>>(fp);
     LAUNCH_CHECK("fit_small_kernel");
     CK(cudaMemcpyAsync(pinned ? h->h_pin + R : out.data(), h->d_fs + R, sizeof(double) * 4 * R, cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaStreamSynchronize(h->stream));
+    CK(sync_stream(h));
     if (pinned) std::memcpy(out.data(), h->h_pin + R, sizeof(double) * 4 * R);
     int best = 0;
     for (int i = 1; i < R; ++i) if (-out[4 * i + 2] < -out[4 * best + 2]) best = i;     // first minimum of -LML
@@ -950,7 +966,7 @@ static int reset_best(plx_bo* h) {
 // the record (and `extra` doubles after its three scalars) to the host: one copy, one synchronisation
 static int fetch_record(plx_bo* h, int extra, double* best_value, long long* best_index) {
   CK(cudaMemcpyAsync(h->h_pin, h->d_rec, sizeof(double) * (3 + extra), cudaMemcpyDeviceToHost, h->stream));
-  CK(cudaStreamSynchronize(h->stream));
+  CK(sync_stream(h));
   *best_value = h->h_pin[0];
   *best_index = reinterpret_cast<const long long*>(h->h_pin)[1];
   h->last_clamped = reinterpret_cast<const long long*>(h->h_pin)[2];
@@ -1067,7 +1083,7 @@ extern "C" int plx_candidates_set(plx_bo_handle h, const double* Xc, long long N
   int r;
   if ((r = ensure(h, h->d_resident, h->resident_cap, static_cast<size_t>(std::max<long long>(N, 1)) * d)) != PLX_OK) return r;
   if (N > 0) CK(cudaMemcpyAsync(h->d_resident, Xc, sizeof(double) * N * d, cudaMemcpyHostToDevice, h->stream));
-  CK(cudaStreamSynchronize(h->stream));
+  CK(sync_stream(h));
   h->resident_n = N; h->resident_first = 0; h->resident_d = d;
   return PLX_OK;
 }
@@ -1109,7 +1125,7 @@ extern "C" int plx_candidates_draw_mt19937_range(plx_bo_handle h, const unsigned
   LAUNCH_CHECK("mt19937_draw_kernel");
   CK(cudaMemcpyAsync(key_out, d_key + 624, sizeof(unsigned) * 624, cudaMemcpyDeviceToHost, h->stream));
   CK(cudaMemcpyAsync(pos_out, d_pos, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
-  CK(cudaStreamSynchronize(h->stream));
+  CK(sync_stream(h));
   h->resident_n = count; h->resident_first = first; h->resident_d = d;
   return PLX_OK;
 }
@@ -1126,7 +1142,7 @@ extern "C" int plx_candidates_get(plx_bo_handle h, double* out, long long first,
   CK(cudaSetDevice(h->device));
   CK(cudaMemcpyAsync(out, h->d_resident + (first - h->resident_first) * h->resident_d, sizeof(double) * count * h->resident_d,
                      cudaMemcpyDeviceToHost, h->stream));
-  CK(cudaStreamSynchronize(h->stream));
+  CK(sync_stream(h));
   return PLX_OK;
 }
 
@@ -1162,7 +1178,7 @@ extern "C" int plx_kernel_values(plx_bo_handle h, int kernel, double nu, const d
   kern_value_probe_kernel<<<(n + 255) / 256, 256, 0, h->stream>>>(d_in, n, kind, d_out);
   LAUNCH_CHECK("kern_value_probe_kernel");
   CK(cudaMemcpyAsync(out, d_out, sizeof(double) * n, cudaMemcpyDeviceToHost, h->stream));
-  CK(cudaStreamSynchronize(h->stream));
+  CK(sync_stream(h));
   return PLX_OK;
 }
 
@@ -1178,7 +1194,7 @@ extern "C" int plx_measure_i8_peak(plx_bo_handle h, double* tops) {
   i8_peak_kernel<<<h->num_sms, 128, 0, h->stream>>>(repeats);
   LAUNCH_CHECK("i8_peak_kernel");
   CK(cudaEventRecord(h->ev_pool[1], h->stream));
-  CK(cudaStreamSynchronize(h->stream));
+  CK(sync_stream(h));
   float ms = 0.f;
   CK(cudaEventElapsedTime(&ms, h->ev_pool[0], h->ev_pool[1]));
   *tops = 2.0 * 128 * 128 * 128 * static_cast<double>(repeats) * h->num_sms / (ms * 1e-3) / 1e12;
@@ -1288,7 +1304,7 @@ extern "C" int plx_acq_value_grad(plx_bo_handle h, const double* Xp, int S, int 
   if ((r = launch_refine_round(h, p)) != PLX_OK) return r;
   CK(cudaMemcpyAsync(values, h->rf_val, sizeof(double) * S, cudaMemcpyDeviceToHost, h->stream));
   CK(cudaMemcpyAsync(grads, h->rf_grad, sizeof(double) * S * h->d, cudaMemcpyDeviceToHost, h->stream));
-  CK(cudaStreamSynchronize(h->stream));
+  CK(sync_stream(h));
   return PLX_OK;
 }
 
@@ -1333,7 +1349,7 @@ extern "C" int plx_acq_refine(plx_bo_handle h, const double* seeds, int S, const
       if ((r = launch_refine_round(h, p)) != PLX_OK) return r;
     int* pinned_active = reinterpret_cast<int*>(h->h_pin);
     CK(cudaMemcpyAsync(pinned_active, h->rf_active, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaStreamSynchronize(h->stream));
+    CK(sync_stream(h));
     active = *pinned_active;
   }
   h->last_refine_rounds = rounds;
@@ -1346,14 +1362,14 @@ extern "C" int plx_acq_refine(plx_bo_handle h, const double* seeds, int S, const
     CK(cudaMemcpyAsync(pin, h->rf_sc, sizeof(RefineScalars) * S, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaMemcpy2DAsync(pin + sc_bytes, static_cast<size_t>(d) * 8, h->rf_vec, stride * 8, static_cast<size_t>(d) * 8, S,
                          cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaStreamSynchronize(h->stream));
+    CK(sync_stream(h));
     std::memcpy(sc.data(), pin, sizeof(RefineScalars) * S);
     std::memcpy(x_out, pin + sc_bytes, x_bytes);
   } else {
     CK(cudaMemcpyAsync(sc.data(), h->rf_sc, sizeof(RefineScalars) * S, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaMemcpy2DAsync(x_out, static_cast<size_t>(d) * 8, h->rf_vec, stride * 8, static_cast<size_t>(d) * 8, S,
                          cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaStreamSynchronize(h->stream));
+    CK(sync_stream(h));
   }
   for (int s = 0; s < S; ++s) {
     acq_out[s] = -sc[s].f;

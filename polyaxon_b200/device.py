@@ -37,10 +37,19 @@ def get_handle(device=None):
             h = _handles[key] = _lib.Handle(device)
             # PLX_BO_RESERVE="n,d,runs,seeds,candidates": allocate the workspaces of that shape when the worker's
             # handle is opened, so that no call of a group pays for device allocations (plx_bo_reserve)
+            # PLX_BO_BLOCKING_SYNC=1 (set by groups.suggest_groups when its worker threads outnumber the cores the
+            # process may use): wait for the GPU asleep on an event instead of spinning
+            if os.environ.get('PLX_BO_BLOCKING_SYNC', '0') == '1':
+                h.set_option('blocking_sync', 1)
             spec = os.environ.get('PLX_BO_RESERVE')
             if spec:
                 h.reserve(*[int(v) for v in spec.split(',')])
     return h
+
+
+def open_handles():
+    with _lock:
+        return list(_handles.values())
 
 
 def close_all():

@@ -40,11 +40,24 @@ def suggest_groups(hptuning_configs, iteration_configs, gather=True, workers=Non
     lo, hi = pdist.shard_range(n, rank, size)
     out = [None] * n
     previous = os.environ.get('PLX_BO_DISTRIBUTED')
+    sleepers = False
     os.environ['PLX_BO_DISTRIBUTED'] = '0'          # inside a group the single-GPU path is used
     try:
         if workers is None:
             workers = int(os.environ.get('PLX_BO_GROUP_WORKERS', '4') or 4)
         workers = max(1, min(int(workers), hi - lo))
+        # more spinning waiters than cores would starve the threads that hold the interpreter: let them sleep on an
+        # event for the duration of this call (PLX_BO_BLOCKING_SYNC, read by device.get_handle for new handles)
+        try:
+            cores = len(os.sched_getaffinity(0))
+        except AttributeError:
+            cores = os.cpu_count() or 1
+        local_ranks = int(os.environ.get('LOCAL_WORLD_SIZE', '1') or 1)
+        sleepers = workers * local_ranks > cores and 'PLX_BO_BLOCKING_SYNC' not in os.environ
+        if sleepers:
+            os.environ['PLX_BO_BLOCKING_SYNC'] = '1'
+            for h in device.open_handles():
+                h.set_option('blocking_sync', 1)
         if workers == 1:
             for g in range(lo, hi):
                 out[g] = _one_group(hptuning_configs[g], iteration_configs[g], g)
@@ -62,6 +75,10 @@ def suggest_groups(hptuning_configs, iteration_configs, gather=True, workers=Non
             del os.environ['PLX_BO_DISTRIBUTED']
         else:
             os.environ['PLX_BO_DISTRIBUTED'] = previous
+        if sleepers:
+            del os.environ['PLX_BO_BLOCKING_SYNC']
+            for h in device.open_handles():
+                h.set_option('blocking_sync', 0)
     if size > 1 and gather:
         parts = [None] * size
         pdist.dist.all_gather_object(parts, out[lo:hi])
