@@ -555,7 +555,8 @@ def main():
             line['dmma_frac'] = roofline['dmma_frac']
 
         # CPU baseline beside it (bounded sample, all host cores) and the cross-check of the winner on that sample
-        if not args.skip_cpu:
+        # (timed at N = 1 only: at N > 1 the other ranks' host threads spin in the barrier and take the cores away)
+        if not args.skip_cpu and world == 1:
             try:
                 sample = min(args.cpu_sample, n_local)
                 base, _, cpu_best = run_cpu_reference(sample, 2, 1)
