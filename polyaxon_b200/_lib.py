@@ -278,6 +278,8 @@ class Handle(object):
         C-contiguous float64 array to fill (e.g. the numpy view of a pinned buffer)."""
         if out is None:
             out = np.empty((count, d))
+        if count == 0:
+            return out
         assert out.dtype == np.float64 and out.flags.c_contiguous and out.size == count * d
         self._check(self.lib.plx_candidates_get(self._h, _ptr(out), int(first), int(count)))
         return out

@@ -188,7 +188,7 @@ def test_device_mt19937_reproduces_numpy_bit_for_bit(d, n_cand, pre_draws):
 
 
 @pytest.mark.parametrize('d,n_cand,pre_draws,world', [(32, 2000000, 16, 2), (3, 5000000, 0, 1), (32, 300000, 2, 3),
-                                                      (1, 700, 1, 2), (7, 9, 0, 4)])
+                                                      (1, 700, 1, 2), (7, 9, 0, 4), (2, 2, 0, 4)])
 def test_device_mt19937_draws_any_block_of_rows(d, n_cand, pre_draws, world):
     """The sharded draw (plx_candidates_draw_mt19937_range): every rank of a multi-GPU job draws only its block of
     rows of the SAME numpy matrix by jumping ahead in the MT19937 stream (csrc/mt19937.cuh), the blocks are cut
