@@ -191,7 +191,7 @@ __global__ void __launch_bounds__(512, 1) sweep_i8c_kernel(const __grid_constant
       for (long long tile = g; tile < ntiles; tile += groups)
         for (int h = 0; h < nh; ++h) {
           if (part_of(h) != r) continue;
-          mbar_wait(bar_acce, (acc_round & 1) ^ 1);        // the previous half-block has been drained
+          if (!PLX_DBG(p.dbg, 512)) mbar_wait(bar_acce, (acc_round & 1) ^ 1);   // the previous half-block has been drained (512: timing experiment without the wait, results invalid)
           ++acc_round;
           asm volatile("tcgen05.fence::after_thread_sync;\n");
           for (int kc = 0; kc < (h + 1) * I8_CPH; ++kc, ++it) {
