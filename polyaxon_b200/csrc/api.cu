@@ -63,6 +63,7 @@ struct plx_bo {
   double* d_alpha_state = nullptr; size_t as_cap = 0;
   double* dKs = nullptr; size_t ks_cap = 0;
   double* dXt = nullptr; size_t xt_cap = 0;
+  double* d_xnorm = nullptr; size_t xnorm_cap = 0; int i8_expand = 0;   // |X/l|^2 per observation; option: int8 builders expand |c-x|^2
   CUtensorMap tmZ, tmK;
   // int8-sliced variant of the sweep (sweep_impl 2, sweep_i8.cuh)
   signed char* d_kplanes = nullptr; size_t kplanes_cap = 0;     // [I8_S][i8_rows][npad]
@@ -283,7 +284,7 @@ extern "C" void plx_bo_destroy(plx_bo_handle h) {
                   h->d_blk_val, h->d_blk_idx, h->d_rec, h->dcand[0], h->dcand[1],
                   h->d_out[0], h->d_out[1], h->d_out[2], h->rf_kv, h->rf_kp, h->rf_v, h->rf_w, h->rf_vec,
                   h->rf_bounds, h->rf_val, h->rf_grad, h->rf_sc, h->rf_active, h->d_resident, h->d_misc, h->d_app,
-                  h->d_kplanes, h->d_zplanes, h->d_zscale, h->d_i8mean, h->d_i8part, h->d_i8sync, h->d_fs};
+                  h->d_kplanes, h->d_zplanes, h->d_zscale, h->d_i8mean, h->d_i8part, h->d_i8sync, h->d_fs, h->d_xnorm};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (h->h_pin) cudaFreeHost(h->h_pin);
   for (int i = 0; i < 2; ++i) { if (h->ev_copy[i]) cudaEventDestroy(h->ev_copy[i]); if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]); }
@@ -305,6 +306,7 @@ extern "C" int plx_bo_set_option(plx_bo_handle h, const char* name, long long va
   if (!h || !name) return PLX_ERR_INVALID;
   if (std::strcmp(name, "sweep_impl") == 0 && value >= 0 && value <= 7) { h->sweep_impl = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "lml_batch_limit") == 0 && value >= 0) { h->lml_batch_limit = static_cast<int>(value); return PLX_OK; }
+  if (std::strcmp(name, "i8_distance") == 0 && (value == 0 || value == 1)) { h->i8_expand = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "blocking_sync") == 0 && (value == 0 || value == 1)) { h->blocking_sync = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "potf_fused") == 0 && (value == 0 || value == 1)) { h->potf_fused = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "refine_persist") == 0 && (value == 0 || value == 1)) { h->refine_persist = static_cast<int>(value); return PLX_OK; }
@@ -562,6 +564,9 @@ extern "C" int plx_gp_set_theta(plx_bo_handle h, double theta) {
   scale_transpose_x_kernel<<<dim3((h->npad + 255) / 256, h->d), 256, 0, h->stream>>>(h->dX, h->n, h->d, h->npad,
                                                                                    std::exp(theta), h->dXt);
   LAUNCH_CHECK("scale_transpose_x_kernel");
+  if ((r = ensure(h, h->d_xnorm, h->xnorm_cap, static_cast<size_t>(h->npad))) != PLX_OK) return r;
+  xnorm_kernel<<<(h->npad + 127) / 128, 128, 0, h->stream>>>(h->dXt, h->d, h->npad, h->d_xnorm);
+  LAUNCH_CHECK("xnorm_kernel");
   if (small) {
     // small observation sets: factor, inverse and alpha in one launch of one CTA (fit_small.cuh)
     if ((r = ensure(h, h->d_fs, h->fs_cap, 8)) != PLX_OK) return r;
@@ -674,6 +679,8 @@ extern "C" int plx_gp_append(plx_bo_handle h, const double* x_new, double y_new)
   LAUNCH_CHECK("trmv_lower_t_kernel");
   scale_transpose_x_kernel<<<dim3((npad + 255) / 256, d), 256, 0, st>>>(h->dX, n1, d, npad, ell, h->dXt);
   LAUNCH_CHECK("scale_transpose_x_kernel");
+  xnorm_kernel<<<(npad + 127) / 128, 128, 0, st>>>(h->dXt, d, npad, h->d_xnorm);
+  LAUNCH_CHECK("xnorm_kernel");
   CK(sync_stream(h));          // y_new / lam2 live on this frame
   h->n = n1; h->i8_state_valid = false;
   { const int nt32 = (n1 + 31) / 32; h->ntri = nt32 * (nt32 + 1) / 2; }
@@ -752,7 +759,7 @@ static void fill_params(plx_bo* h, SweepParams& p, const double* Xc_dev, long lo
                         double kappa, double eps, double y_max) {
   p.Xc = Xc_dev; p.N = N; p.idx_base = idx_base;
   p.d = h->d; p.n = h->n; p.npad = h->npad; p.n16 = (h->n + 15) / 16 * 16;
-  p.X = h->dX; p.Xt = h->dXt; p.alpha = h->d_alpha_state; p.Z = h->dZ; p.ell = std::exp(h->theta);
+  p.X = h->dX; p.Xt = h->dXt; p.xnorm = h->i8_expand ? h->d_xnorm : nullptr; p.alpha = h->d_alpha_state; p.Z = h->dZ; p.ell = std::exp(h->theta);
   p.kind = h->kind; p.mg = h->mg; p.acq = acq; p.kappa = kappa; p.eps = eps; p.y_max = y_max;
   p.Ks = h->dKs; p.out_mean = p.out_std = p.out_acq = nullptr;
   p.planes = nullptr; p.plane_stride = 0;

@@ -38,6 +38,7 @@ struct SweepParams {
   int d, n, npad, n16;     // observations, padded to 128, padded to 16
   const double* X;         // observations [n][d]
   const double* Xt;        // X / length_scale transposed to [d][npad] (TMA-ring kernel only)
+  const double* xnorm;     // nullable: |X_j / length_scale|^2 [npad]; when set the int8 builders expand |c - x|^2 (sweep_i8f.cuh)
   const double* alpha;     // [npad]
   const double* Z;         // L^-1, row-major [npad][npad]
   double ell;              // length scale
@@ -547,6 +548,16 @@ __global__ void scale_transpose_x_kernel(const double* __restrict__ X, int n, in
   const int j = blockIdx.x * blockDim.x + threadIdx.x, q = blockIdx.y;
   if (j >= npad) return;
   Xt[static_cast<size_t>(q) * npad + j] = (j < n) ? X[static_cast<size_t>(j) * d + q] / ell : 0.0;
+}
+
+// |X_j / l|^2 from the transposed scaled observations, one FMA chain per observation in dimension order (the order the
+// builders use for |c|^2 and c.x, so that identical points cancel exactly)
+__global__ void xnorm_kernel(const double* __restrict__ Xt, int d, int npad, double* __restrict__ xnorm) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= npad) return;
+  double s = 0.0;
+  for (int q = 0; q < d; ++q) { const double v = Xt[static_cast<size_t>(q) * npad + j]; s = fma(v, v, s); }
+  xnorm[j] = s;
 }
 
 // Merge the per-CTA bests into the running best of the whole sweep (one thread; grid <= #SMs).

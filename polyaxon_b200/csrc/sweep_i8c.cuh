@@ -13,6 +13,9 @@
 // sum of squares are added up.
 #pragma once
 #include "sweep_i8f.cuh"
+#ifdef PLX_PROFILE
+#include <cstdio>
+#endif
 
 namespace plx {
 
@@ -74,18 +77,34 @@ __global__ void __launch_bounds__(512, 1) sweep_i8c_kernel(const __grid_constant
     asm volatile("setmaxnreg.inc.sync.aligned.u32 168;\n");
     const uint32_t sm = s0 + I8_STAGES * I8_STAGE;
     uint32_t t = 0;
+#ifdef PLX_PROFILE
+    long long t_wait = 0, t_build = 0;
+#endif
     for (long long tile = g; tile < ntiles; tile += groups, ++t) {
       const uint32_t b = t & 1, use = t >> 1;
+#ifdef PLX_PROFILE
+      const long long c0 = clock64();
+#endif
       if (use > 0) {                                   // every CTA of the group has consumed the tile that used this buffer
         if (tid == 0) spin_until(sync_g + 4 * b + 2, I8C_R * use);
         named_bar_sync(1, 256);
       }
+#ifdef PLX_PROFILE
+      const long long c1 = clock64();
+#endif
       signed char* rows = p.planes + static_cast<size_t>(buf_row0 + 128 * b) * p.npad;
       if (!PLX_DBG(p.dbg, 128) || t < 2) build_tile(p, tile, rows, part_g + (b * I8C_R + r) * 256 + 128, sm, tid, r, I8C_R);
       __threadfence();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_ready + 8 * b);
+#ifdef PLX_PROFILE
+      t_wait += c1 - c0; t_build += clock64() - c1;
+#endif
     }
+#ifdef PLX_PROFILE
+    if (PLX_DBG(p.dbg, 2048) && tid == 0 && (blockIdx.x < 4 || blockIdx.x == 77))
+      printf("cta %d builders: %u tiles, build %lld clk/tile, wait for a free buffer %lld clk/tile\n", blockIdx.x, t, t_build / max(t, 1u), t_wait / max(t, 1u));
+#endif
   } else if (warp < 12) {
     // ===== accumulator drain; CTA 0 of the group also finishes the tile =====
     asm volatile("setmaxnreg.dec.sync.aligned.u32 120;\n");
@@ -154,11 +173,23 @@ __global__ void __launch_bounds__(512, 1) sweep_i8c_kernel(const __grid_constant
     if (warp == 12 && lane == 0) {
       // ===== producer =====
       uint32_t it = 0, t = 0;
+#ifdef PLX_PROFILE
+      long long t_own = 0, t_others = 0, t_stage = 0;
+#endif
       for (long long tile = g; tile < ntiles; tile += groups, ++t) {
         const uint32_t b = t & 1, use = t >> 1;
+#ifdef PLX_PROFILE
+        const long long c0 = clock64();
+#endif
         mbar_wait(bar_ready + 8 * b, use & 1);              // this CTA's blocks of the planes are written ...
+#ifdef PLX_PROFILE
+        const long long c1 = clock64();
+#endif
         red_release_gpu(sync_g + 4 * b, 1u);
         spin_until(sync_g + 4 * b, I8C_R * (use + 1));      // ... and so are the other CTAs'
+#ifdef PLX_PROFILE
+        const long long c2 = clock64(); t_own += c1 - c0; t_others += c2 - c1;
+#endif
         asm volatile("fence.proxy.async;\n" ::: "memory");  // bulk tensor loads issued below see them
         for (int h = 0; h < nh; ++h) {
           if (part_of(h) != r) continue;
@@ -166,17 +197,24 @@ __global__ void __launch_bounds__(512, 1) sweep_i8c_kernel(const __grid_constant
             const uint32_t s = it % I8_STAGES, ph = (it / I8_STAGES) & 1;
             mbar_wait(bar0 + 8 * (I8_STAGES + s), ph ^ 1);
             const uint32_t full = bar0 + 8 * s;
+#ifdef PLX_PROFILE
+            mbar_expect_tx(full, (PLX_DBG(p.dbg, 256) && PLX_DBG(p.dbg, 1024)) ? I8_STAGE / 2 : I8_STAGE);
+#else
             mbar_expect_tx(full, I8_STAGE);
+#endif
 #ifdef PLX_PROFILE
             if (PLX_DBG(p.dbg, 256)) {
               // experiment: the same bytes as two contiguous bulk copies (what a chunk-major plane layout would allow)
               const int nch = p.npad / I8_KC;
               const signed char* srcA = p.planes + (static_cast<size_t>(g * 2 + b) * nch + kc) * I8_A_BYTES;
               const signed char* srcB = ip.zplanes_dbg + (static_cast<size_t>(h) * nch + kc) * I8_B_BYTES;
+              // 1024: only half of the bytes are fetched (the rest of the stage is stale): does the incoming stream
+              // compete with the tensor core's operand reads for the shared-memory port?
+              const uint32_t ab = PLX_DBG(p.dbg, 1024) ? I8_A_BYTES / 2 : I8_A_BYTES, bb = PLX_DBG(p.dbg, 1024) ? I8_B_BYTES / 2 : I8_B_BYTES;
               asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n"
-                           :: "r"(s0 + s * I8_STAGE), "l"(srcA), "r"(I8_A_BYTES), "r"(full) : "memory");
+                           :: "r"(s0 + s * I8_STAGE), "l"(srcA), "r"(ab), "r"(full) : "memory");
               asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n"
-                           :: "r"(s0 + s * I8_STAGE + I8_A_BYTES), "l"(srcB), "r"(I8_B_BYTES), "r"(full) : "memory");
+                           :: "r"(s0 + s * I8_STAGE + I8_A_BYTES), "l"(srcB), "r"(bb), "r"(full) : "memory");
               continue;
             }
 #endif
@@ -184,7 +222,15 @@ __global__ void __launch_bounds__(512, 1) sweep_i8c_kernel(const __grid_constant
             tma_load_3d(s0 + s * I8_STAGE + I8_A_BYTES, &tmB, kc * I8_KC, h * 64, 0, full);
           }
         }
+#ifdef PLX_PROFILE
+        t_stage += clock64() - c2;
+#endif
       }
+#ifdef PLX_PROFILE
+      if (PLX_DBG(p.dbg, 2048) && (blockIdx.x < 4 || blockIdx.x == 77))
+        printf("cta %d producer: per tile %lld clk waiting for its own builders, %lld for the group's, %lld feeding the ring\n",
+               blockIdx.x, t_own / max(t, 1u), t_others / max(t, 1u), t_stage / max(t, 1u));
+#endif
     } else if (warp == 13) {
       // ===== tensor-instruction issuer: the whole warp walks the loops, one elected lane issues =====
       uint32_t it = 0, acc_round = 0, ring = 0;

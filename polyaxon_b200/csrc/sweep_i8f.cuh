@@ -96,12 +96,15 @@ __device__ __forceinline__ void build_tile(const SweepParams& p, long long tile,
     }
   };
   if (jb0 < nblk) fetch(jb0, 0);
+  const bool expand = p.xnorm != nullptr;
   for (int jb = jb0; jb < nblk; jb += jbstep) {
-    double r2[8][4];
+    double r2[8][4], cn[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i)
+    for (int i = 0; i < 8; ++i) {
+      cn[i] = 0.0;
 #pragma unroll
       for (int j = 0; j < 4; ++j) r2[i][j] = 0.0;
+    }
     for (int dc = 0; dc < nchunk_d; ++dc) {
       const int d0 = dc * 32, dn = min(32, p.d - d0);
       named_bar_sync(1, 256);                                 // readers of the previous shared tiles are done
@@ -126,17 +129,46 @@ __device__ __forceinline__ void build_tile(const SweepParams& p, long long tile,
       }
       const uint32_t cs = sm + static_cast<uint32_t>((F_CS + ty * 8) * 8);
       const uint32_t xs = sm + static_cast<uint32_t>((F_XS + 4 * tx) * 8);
+      if (!expand) {
 #pragma unroll 2
-      for (int q = 0; q < dn; ++q) {
-        double cv[8], xv[4];
+        for (int q = 0; q < dn; ++q) {
+          double cv[8], xv[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) { const double2 t2 = lds128(cs + (q * F_CS_LD + 2 * i) * 8); cv[2 * i] = t2.x; cv[2 * i + 1] = t2.y; }
-        { const double2 a = lds128(xs + q * F_XS_LD * 8), b = lds128(xs + q * F_XS_LD * 8 + 16); xv[0] = a.x; xv[1] = a.y; xv[2] = b.x; xv[3] = b.y; }
+          for (int i = 0; i < 4; ++i) { const double2 t2 = lds128(cs + (q * F_CS_LD + 2 * i) * 8); cv[2 * i] = t2.x; cv[2 * i + 1] = t2.y; }
+          { const double2 a = lds128(xs + q * F_XS_LD * 8), b = lds128(xs + q * F_XS_LD * 8 + 16); xv[0] = a.x; xv[1] = a.y; xv[2] = b.x; xv[3] = b.y; }
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
+          for (int i = 0; i < 8; ++i)
 #pragma unroll
-          for (int j = 0; j < 4; ++j) { const double df = cv[i] - xv[j]; r2[i][j] += df * df; }
+            for (int j = 0; j < 4; ++j) { const double df = cv[i] - xv[j]; r2[i][j] += df * df; }
+        }
+      } else {
+        // |c - x|^2 = |c|^2 + |x|^2 - 2 c.x: one FMA per pair and dimension instead of a subtraction and an FMA (the
+        // builders are the critical path of the kernel and two thirds of their FP64 work is this loop).  r2 holds
+        // the dot products here; |c|^2 rides along (8 more FMAs per dimension), |x|^2 comes precomputed with the
+        // same FMA chain, so a candidate that IS an observation still gets exactly zero.
+#pragma unroll 2
+        for (int q = 0; q < dn; ++q) {
+          double cv[8], xv[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) { const double2 t2 = lds128(cs + (q * F_CS_LD + 2 * i) * 8); cv[2 * i] = t2.x; cv[2 * i + 1] = t2.y; }
+          { const double2 a = lds128(xs + q * F_XS_LD * 8), b = lds128(xs + q * F_XS_LD * 8 + 16); xv[0] = a.x; xv[1] = a.y; xv[2] = b.x; xv[3] = b.y; }
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            cn[i] = fma(cv[i], cv[i], cn[i]);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) r2[i][j] = fma(cv[i], xv[j], r2[i][j]);
+          }
+        }
       }
+    }
+    if (expand) {
+      double xn[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) xn[j] = p.xnorm[jb * 64 + 4 * tx + j];
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) r2[i][j] = fmax((cn[i] + xn[j]) - 2.0 * r2[i][j], 0.0);
     }
     const int jo = jb * 64 + 4 * tx;
     switch (p.kind) {

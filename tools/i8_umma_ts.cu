@@ -6,6 +6,10 @@
 //   1  per k32 step: 7 x tcgen05.cp.128x256b of the A planes into TMEM columns 448..503, then 28 MMAs with A in TMEM
 //   2  the same with an 8-slot ring of A planes in columns 448..511: the copy of plane s + 1 is issued before the
 //      MMAs of plane s, slots rotate across k steps (no waits: copies and MMAs execute in issue order)
+//   3  mode 2 with a tcgen05.commit to an mbarrier after every stage (no waits)
+//   4  mode 3 with a window: stage i is issued only after the commit of stage i - 2 has arrived (what a two-stage
+//      operand ring imposes, with the refill itself free)
+//   5  the same with a window of three stages, 6 with four
 // Checks every mode against the host, then times `repeats` stages per SM.
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o tools/i8_umma_ts tools/i8_umma_ts.cu
 #include <cstdint>
@@ -50,6 +54,7 @@ __global__ void __launch_bounds__(128, 1) probe(const int8_t* __restrict__ A, co
   uint8_t* sA = smem;
   uint8_t* sB = smem + S * A_PLANE;
   __shared__ __align__(8) unsigned long long bar;
+  __shared__ __align__(8) unsigned long long sbar[4];
   __shared__ uint32_t tmem_base_s;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   for (int idx = tid; idx < S * 128 * 4; idx += 128) {
@@ -69,6 +74,7 @@ __global__ void __launch_bounds__(128, 1) probe(const int8_t* __restrict__ A, co
   }
   if (tid == 0) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" :: "r"(smem_u32(&bar)));
+    for (int i = 0; i < 4; ++i) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" :: "r"(smem_u32(&sbar[i])));
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
   asm volatile("tcgen05.fence::before_thread_sync;\n");
@@ -78,7 +84,15 @@ __global__ void __launch_bounds__(128, 1) probe(const int8_t* __restrict__ A, co
   if (warp == 0) {
     const uint64_t da0 = umma_desc64(smem_u32(sA)), db0 = umma_desc64(smem_u32(sB));
     uint32_t ring = 0;
+    const int window = mode == 4 ? 2 : (mode == 5 ? 3 : (mode == 6 ? 4 : 0));
     for (int rep = 0; rep < repeats; ++rep) {
+      if (window > 0 && rep >= window) {
+        // the commit of stage rep - window: barrier (rep % window), its (rep / window - 1)-th completion
+        const uint32_t b = smem_u32(&sbar[rep % window]), parity = ((rep / window) - 1) & 1;
+        asm volatile("{\n.reg .pred p;\nWAITS_%=:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n@p bra DONES_%=;\nbra WAITS_%=;\nDONES_%=:\n}\n"
+                     :: "r"(b), "r"(parity) : "memory");
+        asm volatile("tcgen05.fence::after_thread_sync;\n");
+      }
       if (elect_one()) {
         if (mode == 0) {
 #pragma unroll
@@ -117,6 +131,11 @@ __global__ void __launch_bounds__(128, 1) probe(const int8_t* __restrict__ A, co
               umma_ts(tmem + (s + t) * 64, ta, db0 + t * (B_PLANE / 16) + 2 * k, (s == 0 && k == 0) ? (rep != 0) : 1u);
           }
           ring += 2 * S;
+          if (mode >= 3) {
+            const int w = window > 0 ? window : 4;
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.b64 [%0];\n"
+                         :: "l"(__cvta_generic_to_shared(&sbar[rep % w])) : "memory");
+          }
         }
       }
       __syncwarp();
@@ -174,7 +193,7 @@ int main() {
           want[m * 448 + (s + t) * 64 + n] += acc;
         }
   int rc = 0;
-  for (int mode = 0; mode < 3; ++mode) {
+  for (int mode = 0; mode < 7; ++mode) {
     for (int reps : {1, 3}) {
       CK(cudaMemset(dC, 0xff, 128 * 448 * 4));
       probe<<<1, 128, SMEM_BYTES>>>(dA, dB, dC, dAd, mode, reps);
@@ -205,7 +224,7 @@ int main() {
   int sms = 0; CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0));
   cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
   const int repeats = 4000;
-  for (int mode = 0; mode < 3; ++mode) {
+  for (int mode = 0; mode < 7; ++mode) {
     probe<<<sms, 128, SMEM_BYTES>>>(dA, dB, nullptr, nullptr, mode, 200); CK(cudaDeviceSynchronize());
     CK(cudaEventRecord(e0)); probe<<<sms, 128, SMEM_BYTES>>>(dA, dB, nullptr, nullptr, mode, repeats); CK(cudaEventRecord(e1)); CK(cudaDeviceSynchronize());
     float ms = 0; CK(cudaEventElapsedTime(&ms, e0, e1));
