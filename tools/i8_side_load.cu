@@ -2,7 +2,8 @@
 // Warp 0 issues the sweep's stage (tools/i8_umma_ts.cu mode 4: A planes through the tensor-memory ring, commit per stage,
 // two-stage window) on resident operands; eight more warps run a side load until the stream has finished:
 //   0 nothing   1 FP64 FMA chains in registers   2 128-bit shared-memory loads (conflict-free)   3 both (the builders' mix:
-//   6 loads per 64 FP64 operations)   4 integer ALU   5 global (L2) stores of 32-bit words
+//   6 loads per 64 FP64 operations)   4 integer ALU   5 global (L2) stores of 32-bit words   6 FP64 tensor (mma.sync m8n8k4)
+//   7 FP32 FMA chains
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o tools/i8_side_load tools/i8_side_load.cu
 #include <cstdint>
 #include <cstdio>
@@ -124,6 +125,7 @@ __global__ void __launch_bounds__(384, 1) probe(const int8_t* __restrict__ A, co
     const int st = tid - 128;                               // 0 .. 255
     double a0 = 1.0, a1 = 1.1, a2 = 1.2, a3 = 1.3, a4 = 0.9, a5 = 0.8, a6 = 0.7, a7 = 0.6;
     unsigned iacc = st;
+    float f0 = 1.f, f1 = 1.1f, f2 = 1.2f, f3 = 1.3f, f4 = .9f, f5 = .8f, f6 = .7f, f7 = .6f;
     const double* mine = sS + 2 * (st & 255);
     long long it = 0;
     while (!done) {
@@ -138,12 +140,20 @@ __global__ void __launch_bounds__(384, 1) probe(const int8_t* __restrict__ A, co
                        : "r"(smem_u32(mine + ((u * 512) % (SIDE_BYTES / 8 - 512)))));
           a0 += vx * 1e-30; a1 += vy * 1e-30;
         }
+        if (side == 6) {
+          asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};\n" : "+d"(a0), "+d"(a1) : "d"(a4), "d"(a5));
+          asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};\n" : "+d"(a2), "+d"(a3) : "d"(a6), "d"(a7));
+        }
+        if (side == 7) {
+          f0 = fmaf(f0, 1.0000001f, 1e-9f); f1 = fmaf(f1, 1.0000001f, 1e-9f); f2 = fmaf(f2, 0.9999999f, 1e-9f); f3 = fmaf(f3, 0.9999999f, 1e-9f);
+          f4 = fmaf(f4, 1.0000001f, 1e-9f); f5 = fmaf(f5, 1.0000001f, 1e-9f); f6 = fmaf(f6, 0.9999999f, 1e-9f); f7 = fmaf(f7, 0.9999999f, 1e-9f);
+        }
         if (side == 4) { iacc = iacc * 1664525u + 1013904223u; iacc ^= iacc >> 7; iacc += u; iacc = (iacc << 3) | (iacc >> 29); }
         if (side == 5) gbuf[(blockIdx.x * 256 + st) + 65536 * ((it * 64 + u) & 63)] = iacc + u;
       }
       ++it;
     }
-    if (a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7 + iacc == 12345.678) sink[0] = a0;
+    if (a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7 + iacc + f0 + f1 + f2 + f3 + f4 + f5 + f6 + f7 == 12345.678) sink[0] = a0;
     if (lane == 0) atomicAdd(side_iters, static_cast<unsigned long long>(it));
   }
   asm volatile("tcgen05.fence::before_thread_sync;\n");
@@ -166,9 +176,9 @@ int main() {
   int sms = 0; CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0));
   cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
   const int repeats = 4000;
-  const char* names[] = {"none", "fp64 fma", "lds.128", "fp64 + lds (builder mix)", "integer alu", "global stores"};
+  const char* names[] = {"none", "fp64 fma", "lds.128", "fp64 + lds (builder mix)", "integer alu", "global stores", "fp64 tensor (dmma)", "fp32 fma"};
   for (int nomma = 0; nomma < 2; ++nomma)
-    for (int side = 0; side < 6; ++side) {
+    for (int side = 0; side < 8; ++side) {
       probe<<<sms, 384, smem>>>(dA, dB, side, 200, sink, gbuf, iters, nomma); CK(cudaDeviceSynchronize());
       CK(cudaMemset(iters, 0, 8));
       CK(cudaEventRecord(e0)); probe<<<sms, 384, smem>>>(dA, dB, side, repeats, sink, gbuf, iters, nomma); CK(cudaEventRecord(e1)); CK(cudaDeviceSynchronize());
