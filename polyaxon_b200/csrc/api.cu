@@ -102,7 +102,7 @@ struct plx_bo {
 
   // refinement workspace
   int rf_cap_s = 0, rf_cap_npad = 0, rf_cap_d = 0;
-  double *rf_kv = nullptr, *rf_kp = nullptr, *rf_v = nullptr, *rf_w = nullptr, *rf_vec = nullptr,
+  double *rf_kv = nullptr, *rf_kp = nullptr, *rf_v = nullptr, *rf_w = nullptr, *rf_wpart = nullptr, *rf_vec = nullptr,
          *rf_bounds = nullptr, *rf_val = nullptr, *rf_grad = nullptr;
   RefineScalars* rf_sc = nullptr;
   int* rf_active = nullptr;
@@ -282,7 +282,7 @@ extern "C" void plx_bo_destroy(plx_bo_handle h) {
   void* ptrs[] = {h->dX, h->dy, h->bp.A, h->bp.L, h->bp.U, h->bp.W, h->bp.T, h->d_thetas, h->d_logdet, h->d_w,
                   h->d_alpha, h->d_partial, h->d_lml, h->d_grad, h->d_xs, h->d_info, h->dZ, h->d_alpha_state, h->dKs, h->dXt,
                   h->d_blk_val, h->d_blk_idx, h->d_rec, h->dcand[0], h->dcand[1],
-                  h->d_out[0], h->d_out[1], h->d_out[2], h->rf_kv, h->rf_kp, h->rf_v, h->rf_w, h->rf_vec,
+                  h->d_out[0], h->d_out[1], h->d_out[2], h->rf_kv, h->rf_kp, h->rf_v, h->rf_w, h->rf_wpart, h->rf_vec,
                   h->rf_bounds, h->rf_val, h->rf_grad, h->rf_sc, h->rf_active, h->d_resident, h->d_misc, h->d_app,
                   h->d_kplanes, h->d_zplanes, h->d_zscale, h->d_i8mean, h->d_i8part, h->d_i8sync, h->d_fs, h->d_xnorm};
   for (void* p : ptrs) if (p) cudaFree(p);
@@ -1245,15 +1245,16 @@ extern "C" int plx_lbfgsb1d_minimize(plx_fg_callback fg, void* user, double x0, 
 // ---------------------------------------------------------------------------------------------
 static int ensure_refine(plx_bo* h, int S) {
   if (S <= h->rf_cap_s && h->npad == h->rf_cap_npad && h->d == h->rf_cap_d) return PLX_OK;
-  void* old[] = {h->rf_kv, h->rf_kp, h->rf_v, h->rf_w, h->rf_vec, h->rf_bounds, h->rf_val, h->rf_grad, h->rf_sc, h->rf_active};
+  void* old[] = {h->rf_kv, h->rf_kp, h->rf_v, h->rf_w, h->rf_wpart, h->rf_vec, h->rf_bounds, h->rf_val, h->rf_grad, h->rf_sc, h->rf_active};
   for (void* p : old) if (p) CK(cudaFree(p));
-  h->rf_kv = h->rf_kp = h->rf_v = h->rf_w = h->rf_vec = h->rf_bounds = h->rf_val = h->rf_grad = nullptr;
+  h->rf_kv = h->rf_kp = h->rf_v = h->rf_w = h->rf_wpart = h->rf_vec = h->rf_bounds = h->rf_val = h->rf_grad = nullptr;
   h->rf_sc = nullptr; h->rf_active = nullptr; h->rf_cap_s = 0;
   const size_t sn = static_cast<size_t>(S) * h->npad;
   CK(cudaMalloc(&h->rf_kv, sizeof(double) * sn));
   CK(cudaMalloc(&h->rf_kp, sizeof(double) * sn));
   CK(cudaMalloc(&h->rf_v, sizeof(double) * sn));
   CK(cudaMalloc(&h->rf_w, sizeof(double) * sn));
+  CK(cudaMalloc(&h->rf_wpart, sizeof(double) * sn * ((h->npad + RF_WROWS - 1) / RF_WROWS)));
   CK(cudaMalloc(&h->rf_vec, sizeof(double) * rf_vec_stride(h->d) * S));
   CK(cudaMalloc(&h->rf_bounds, sizeof(double) * 2 * h->d));
   CK(cudaMalloc(&h->rf_val, sizeof(double) * S));
@@ -1268,7 +1269,7 @@ static void fill_refine(plx_bo* h, RefineParams& p, int S, int acq, double kappa
   p.S = S; p.d = h->d; p.n = h->n; p.npad = h->npad; p.kind = h->kind; p.mg = h->mg; p.acq = acq; p.max_iter = max_iter;
   p.ell = std::exp(h->theta); p.kappa = kappa; p.eps = eps; p.y_max = y_max;
   p.X = h->dX; p.alpha = h->d_alpha_state; p.Z = h->dZ; p.bounds = h->rf_bounds;
-  p.kv = h->rf_kv; p.kp = h->rf_kp; p.v = h->rf_v; p.w = h->rf_w;
+  p.kv = h->rf_kv; p.kp = h->rf_kp; p.v = h->rf_v; p.w = h->rf_w; p.wpart = nullptr;
   p.vec = h->rf_vec; p.vec_stride = rf_vec_stride(h->d); p.sc = h->rf_sc;
   p.val_out = nullptr; p.grad_out = nullptr; p.active = h->rf_active;
 }
@@ -1280,9 +1281,11 @@ static int launch_refine_round(plx_bo* h, const RefineParams& p) {
   LAUNCH_CHECK("refine_kstar_kernel");
   refine_v_kernel<<<(p.n + 7) / 8, 256, 0, st>>>(p);
   LAUNCH_CHECK("refine_v_kernel");
-  refine_w_kernel<<<(p.n + 31) / 32, 256, 0, st>>>(p);
+  RefineParams q = p;
+  q.wpart = h->rf_wpart;
+  refine_w_kernel<<<dim3((p.n + RF_WROWS - 1) / RF_WROWS, (p.n + 127) / 128), 128, 0, st>>>(q);
   LAUNCH_CHECK("refine_w_kernel");
-  refine_step_kernel<<<p.S, 128, sizeof(double) * 2 * p.d, st>>>(p);
+  refine_step_kernel<<<p.S, 512, sizeof(double) * 2 * p.d, st>>>(q);
   LAUNCH_CHECK("refine_step_kernel");
   return PLX_OK;
 }

@@ -55,6 +55,7 @@ struct RefineParams {
   double ell, kappa, eps, y_max;
   const double* X; const double* alpha; const double* Z; const double* bounds;   // bounds [d][2]
   double* kv; double* kp; double* v; double* w;     // [S][npad]
+  double* wpart;                                     // nullable: [row chunks][S][npad] partial sums of w (round-by-round path)
   double* vec;                                       // per-seed vectors, stride vec_stride
   size_t vec_stride;
   RefineScalars* sc;
@@ -116,33 +117,29 @@ __global__ void __launch_bounds__(256) refine_v_kernel(RefineParams p) {
   }
 }
 
-// w[s][j] = sum_{i >= j} Z[i][j] v[s][i]: block (32 columns, 8 row groups)
-__global__ void __launch_bounds__(256) refine_w_kernel(RefineParams p) {
-  __shared__ double red[8][RF_SB][33];
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int j = blockIdx.x * 32 + tx;
+// w[s][j] = sum_{i >= j} Z[i][j] v[s][i] in two steps.  This kernel: CTA (rc, cb) takes rows 64 rc .. 64 rc + 63 and
+// columns 128 cb .. 128 cb + 127 (skipped when the block lies above the diagonal), a thread per column, and leaves the
+// partial sums of its rows in wpart[rc][s][j]; refine_step_kernel adds the chunks in order.  (One CTA per 32 columns
+// walking ALL rows below them, as in round 1, was the slowest kernel of a round at n = 2048: 64 CTAs, 257 us.)
+constexpr int RF_WROWS = 64;
+__global__ void __launch_bounds__(128) refine_w_kernel(RefineParams p) {
+  const int rc = blockIdx.x, cb = blockIdx.y, r0 = rc * RF_WROWS, j = cb * 128 + threadIdx.x;
+  const int r1 = min(r0 + RF_WROWS, p.n);
+  if (cb * 128 > r1 - 1) return;                                       // above the diagonal: nothing stored, nothing read
   for (int s0 = 0; s0 < p.S; s0 += RF_SB) {
     double acc[RF_SB];
 #pragma unroll
     for (int b = 0; b < RF_SB; ++b) acc[b] = 0.0;
     if (j < p.n) {
-      const int ifirst = blockIdx.x * 32 + ty;          // rows below the block's first column
-      for (int i = ifirst; i < p.n; i += 8) {
-        if (i < j) continue;
+      for (int i = max(r0, j); i < r1; ++i) {
         const double z = p.Z[static_cast<size_t>(i) * p.npad + j];
 #pragma unroll
         for (int b = 0; b < RF_SB; ++b)
           if (s0 + b < p.S) acc[b] += z * p.v[static_cast<size_t>(s0 + b) * p.npad + i];
       }
-    }
-    __syncthreads();
 #pragma unroll
-    for (int b = 0; b < RF_SB; ++b) red[ty][b][tx] = acc[b];
-    __syncthreads();
-    if (ty < RF_SB && s0 + ty < p.S && j < p.n) {
-      double t = 0.0;
-      for (int r = 0; r < 8; ++r) t += red[r][ty][tx];
-      p.w[static_cast<size_t>(s0 + ty) * p.npad + j] = t;
+      for (int b = 0; b < RF_SB; ++b)
+        if (s0 + b < p.S) p.wpart[(static_cast<size_t>(rc) * p.S + s0 + b) * p.npad + j] = acc[b];
     }
   }
 }
@@ -326,12 +323,12 @@ __device__ void rf_advance(const RefineParams& p, int s, RefineScalars& sc, int 
 // Reductions over the observations for seed s, the acquisition and its gradient, then (unless in evaluation-only
 // mode) one optimiser transition by warp 0.  Called by all 128 threads of a CTA; grad_smem holds 2 d doubles.
 __device__ __forceinline__ void refine_step_body(const RefineParams& p, int s, double* grad_smem) {
-  __shared__ double red_mu[4], red_s2[4];
-  __shared__ double gsum[4][2][32];
+  __shared__ double red_mu[16], red_s2[16];
+  __shared__ double gsum[16][2][32];
   __shared__ double sh_mu, sh_s2;
   double* gm = grad_smem;
   double* gv = grad_smem + p.d;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthr = blockDim.x, nw = nthr >> 5;   // 4 .. 16 warps
   const bool eval_only = p.val_out != nullptr;
   const double* kv = p.kv + static_cast<size_t>(s) * p.npad;
   const double* kp = p.kp + static_cast<size_t>(s) * p.npad;
@@ -339,7 +336,7 @@ __device__ __forceinline__ void refine_step_body(const RefineParams& p, int s, d
   const double* w = p.w + static_cast<size_t>(s) * p.npad;
   const double* x = rf_x(p, s);
   double mu = 0.0, s2 = 0.0;
-  for (int j = tid; j < p.n; j += 128) { mu += kv[j] * p.alpha[j]; s2 += v[j] * v[j]; }
+  for (int j = tid; j < p.n; j += nthr) { mu += kv[j] * p.alpha[j]; s2 += v[j] * v[j]; }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) { mu += __shfl_xor_sync(0xffffffffu, mu, o); s2 += __shfl_xor_sync(0xffffffffu, s2, o); }
   if (lane == 0) { red_mu[warp] = mu; red_s2[warp] = s2; }
@@ -350,7 +347,7 @@ __device__ __forceinline__ void refine_step_body(const RefineParams& p, int s, d
     double a1 = 0.0, a2 = 0.0;
     if (q < p.d) {
       const double xq = x[q];
-      for (int j = warp; j < p.n; j += 4) {
+      for (int j = warp; j < p.n; j += nw) {
         const double c = 2.0 * kp[j] * inv_l2 * (xq - p.X[static_cast<size_t>(j) * p.d + q]);
         a1 += c * p.alpha[j];
         a2 += c * w[j];
@@ -359,12 +356,25 @@ __device__ __forceinline__ void refine_step_body(const RefineParams& p, int s, d
     gsum[warp][0][lane] = a1; gsum[warp][1][lane] = a2;
     __syncthreads();
     if (warp == 0 && q < p.d) {
-      gm[q] = gsum[0][0][lane] + gsum[1][0][lane] + gsum[2][0][lane] + gsum[3][0][lane];
-      gv[q] = -2.0 * (gsum[0][1][lane] + gsum[1][1][lane] + gsum[2][1][lane] + gsum[3][1][lane]);
+      // groups of four warps first, then the groups: with four warps this is the order (w0 + w1 + w2 + w3) as before
+      double t1 = 0.0, t2 = 0.0;
+      for (int w4 = 0; w4 < nw; w4 += 4) {
+        t1 += gsum[w4][0][lane] + gsum[w4 + 1][0][lane] + gsum[w4 + 2][0][lane] + gsum[w4 + 3][0][lane];
+        t2 += gsum[w4][1][lane] + gsum[w4 + 1][1][lane] + gsum[w4 + 2][1][lane] + gsum[w4 + 3][1][lane];
+      }
+      gm[q] = t1;
+      gv[q] = -2.0 * t2;
     }
     __syncthreads();
   }
-  if (tid == 0) { sh_mu = red_mu[0] + red_mu[1] + red_mu[2] + red_mu[3]; sh_s2 = red_s2[0] + red_s2[1] + red_s2[2] + red_s2[3]; }
+  if (tid == 0) {
+    double a = 0.0, b = 0.0;
+    for (int w4 = 0; w4 < nw; w4 += 4) {
+      a += red_mu[w4] + red_mu[w4 + 1] + red_mu[w4 + 2] + red_mu[w4 + 3];
+      b += red_s2[w4] + red_s2[w4 + 1] + red_s2[w4 + 2] + red_s2[w4 + 3];
+    }
+    sh_mu = a; sh_s2 = b;
+  }
   __syncthreads();
   if (warp != 0) return;
   const double mean = sh_mu;
@@ -398,10 +408,20 @@ __device__ __forceinline__ void refine_step_body(const RefineParams& p, int s, d
 }
 
 // One CTA (128 threads) per seed, one round: used with refine_kstar / refine_v / refine_w kernels for large n.
-__global__ void __launch_bounds__(128) refine_step_kernel(RefineParams p) {
+__global__ void __launch_bounds__(512) refine_step_kernel(RefineParams p) {
   extern __shared__ double rf_grad_smem[];        // gm[d] | gv[d]
   const int s = blockIdx.x;
   if (p.val_out == nullptr && p.sc[s].phase == 2) return;
+  if (p.wpart != nullptr) {
+    // w[s][j] = sum over the row chunks at or below j of the partial sums refine_w_kernel left, in chunk order
+    const int nrc = (p.n + RF_WROWS - 1) / RF_WROWS;
+    for (int j = threadIdx.x; j < p.n; j += blockDim.x) {
+      double t = 0.0;
+      for (int rc = j / RF_WROWS; rc < nrc; ++rc) t += p.wpart[(static_cast<size_t>(rc) * p.S + s) * p.npad + j];
+      p.w[static_cast<size_t>(s) * p.npad + j] = t;
+    }
+    __syncthreads();
+  }
   refine_step_body(p, s, rf_grad_smem);
 }
 
