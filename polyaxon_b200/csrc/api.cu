@@ -820,8 +820,8 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
   if (impl_i8 == 5 || impl_i8 == 6 || (impl_i8 == 3 && p.n >= 1536)) {
     // cooperative forms: groups of four CTAs share a candidate tile so that the planes in flight stay in L2.
     // 6: the four are two clusters of two that fetch the A stream once per pair (TMA multicast); measured equal to 5
-    // (8.3 ms against 8.2 ms per 151 552 candidates: what a CTA receives, not what L2 reads, bounds the stream), so
-    // the default stays with the plain cooperative form
+    // (8.3 ms against 8.2 ms per 151 552 candidates: the operand stream is not what bounds the kernel), so the
+    // default stays with the plain cooperative form
     const bool paired = impl_i8 == 6;
     const int max_groups = h->num_sms / I8C_R;
     const int groups = static_cast<int>(std::min<long long>((p.N + 127) / 128, max_groups));

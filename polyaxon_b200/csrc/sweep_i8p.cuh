@@ -4,11 +4,12 @@
 // fetched from L2 once per pair instead of once per CTA: each CTA loads half of the planes (even / odd) with a bulk
 // tensor load that is multicast to both CTAs of the cluster, and its own 28 KB chunk of Z planes.
 //
-// Why: with the A planes going to the tensor core through tensor memory the contraction is no longer bound by the
-// shared-memory operand reads, and what is left is the operand stream itself.  Every CTA pulls 84 KB per 56 tensor
-// instructions; 148 of them ask L2 for ~13 TB/s, which is what the L2 delivers (tools/i8_phases.py: the stream
-// alone takes 4.1 ms per 151 552 candidates, the tensor instructions alone need 4.6 ms).  Sharing A in a pair cuts
-// the stream to 56 KB per stage and CTA.
+// Why it was built: with the A planes going to the tensor core through tensor memory the contraction is no longer
+// bound by the shared-memory operand reads, and the operand stream (84 KB per 56 tensor instructions and CTA, ~9 TB/s
+// from L2 over the whole chip) looked like the next limit; sharing A in a pair cuts what L2 has to read by a third.
+// What was measured: the same results at the same speed (8.28 against 8.22 ms per 151 552 candidates; the stream alone
+// 3.86 against 3.94 ms).  The kernel is bound by its builders, which the tensor instructions starve of the FP64 pipe
+// and the shared-memory port, not by the stream.  Kept as `sweep_impl` 6, not the default.
 //
 // Lock step needs equal chunk counts: half-block 2q needs chunks 0 .. 2q, half-block 2q + 1 chunks 0 .. 2q + 1.  CTA 0
 // also takes chunk 2q + 1; there its rows of Z are above the diagonal, i.e. zero planes (zslice_kernel writes zeros for
