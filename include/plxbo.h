@@ -58,9 +58,10 @@ int plx_bo_set_stream(plx_bo_handle h, void* stream);
  * "fit_small" (1 [default]: with at most 64 observations plx_gp_fit runs every optimiser run from start to
  * convergence in ONE launch, optimiser included; 2: the same up to 128 observations (slower than the batched
  * sequence there, kept for tests); 0: always the batched launch sequence used for larger sets);
- * "i8_distance" (0 [default]: squared distances as (c - x)^2 summed directly, the arithmetic of scipy's cdist; 1: the
- * int8-sliced sweeps form them as |c|^2 + |x|^2 - 2 c.x, 40 % fewer FP64 operations in the builders, measured 1.5 %
- * faster and agreeing to 1e-13 in the posterior: kept as an experiment);
+ * "i8_distance" (builders of the int8-sliced sweeps, at most 32 dimensions: 0 = squared distances as (c - x)^2 summed
+ * directly, the arithmetic of scipy's cdist; 1 = as |u|^2 + |v|^2 - 2 u.v with u, v centred on the observations'
+ * mean, u.v on the FP64 tensor path (mma.sync), pairs where that cancels recomputed directly; 2 [default] = 1 in the
+ * cooperative form (4 % faster there at the C3 shape), 0 in the fused form (slower there); posterior equal to 1e-10);
  * "blocking_sync" (0 [default]: calls wait for the GPU by spinning on the stream; 1: the host thread sleeps on an
  * event instead -- for processes whose worker threads outnumber their cores);
  * "potf_fused" (1 [default]: the diagonal 128-blocks of the fit are factorised and inverted in one pass of 128 column

@@ -63,7 +63,10 @@ struct plx_bo {
   double* d_alpha_state = nullptr; size_t as_cap = 0;
   double* dKs = nullptr; size_t ks_cap = 0;
   double* dXt = nullptr; size_t xt_cap = 0;
-  double* d_xnorm = nullptr; size_t xnorm_cap = 0; int i8_expand = 0;   // |X/l|^2 per observation; option: int8 builders expand |c-x|^2
+  int i8_distance = 2;                                // builders of the int8 sweeps: 0 direct differences, 1 FP64 tensor path, 2 by form
+  double* d_xrow = nullptr; size_t xrow_cap = 0;      // centred scaled observation rows [npad][40], their squared norms and the centre:
+  double* d_xnc = nullptr; size_t xnc_cap = 0;        // operands of the tensor-path builders (i8_distance 1 / 2, d <= 32)
+  double* d_xmean = nullptr; size_t xmean_cap = 0;
   CUtensorMap tmZ, tmK;
   // int8-sliced variant of the sweep (sweep_impl 2, sweep_i8.cuh)
   signed char* d_kplanes = nullptr; size_t kplanes_cap = 0;     // [I8_S][i8_rows][npad]
@@ -284,7 +287,7 @@ extern "C" void plx_bo_destroy(plx_bo_handle h) {
                   h->d_blk_val, h->d_blk_idx, h->d_rec, h->dcand[0], h->dcand[1],
                   h->d_out[0], h->d_out[1], h->d_out[2], h->rf_kv, h->rf_kp, h->rf_v, h->rf_w, h->rf_wpart, h->rf_vec,
                   h->rf_bounds, h->rf_val, h->rf_grad, h->rf_sc, h->rf_active, h->d_resident, h->d_misc, h->d_app,
-                  h->d_kplanes, h->d_zplanes, h->d_zscale, h->d_i8mean, h->d_i8part, h->d_i8sync, h->d_fs, h->d_xnorm};
+                  h->d_kplanes, h->d_zplanes, h->d_zscale, h->d_i8mean, h->d_i8part, h->d_i8sync, h->d_fs, h->d_xrow, h->d_xnc, h->d_xmean};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (h->h_pin) cudaFreeHost(h->h_pin);
   for (int i = 0; i < 2; ++i) { if (h->ev_copy[i]) cudaEventDestroy(h->ev_copy[i]); if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]); }
@@ -306,7 +309,7 @@ extern "C" int plx_bo_set_option(plx_bo_handle h, const char* name, long long va
   if (!h || !name) return PLX_ERR_INVALID;
   if (std::strcmp(name, "sweep_impl") == 0 && value >= 0 && value <= 7) { h->sweep_impl = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "lml_batch_limit") == 0 && value >= 0) { h->lml_batch_limit = static_cast<int>(value); return PLX_OK; }
-  if (std::strcmp(name, "i8_distance") == 0 && (value == 0 || value == 1)) { h->i8_expand = static_cast<int>(value); return PLX_OK; }
+  if (std::strcmp(name, "i8_distance") == 0 && value >= 0 && value <= 2) { h->i8_distance = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "blocking_sync") == 0 && (value == 0 || value == 1)) { h->blocking_sync = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "potf_fused") == 0 && (value == 0 || value == 1)) { h->potf_fused = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "refine_persist") == 0 && (value == 0 || value == 1)) { h->refine_persist = static_cast<int>(value); return PLX_OK; }
@@ -564,9 +567,6 @@ extern "C" int plx_gp_set_theta(plx_bo_handle h, double theta) {
   scale_transpose_x_kernel<<<dim3((h->npad + 255) / 256, h->d), 256, 0, h->stream>>>(h->dX, h->n, h->d, h->npad,
                                                                                    std::exp(theta), h->dXt);
   LAUNCH_CHECK("scale_transpose_x_kernel");
-  if ((r = ensure(h, h->d_xnorm, h->xnorm_cap, static_cast<size_t>(h->npad))) != PLX_OK) return r;
-  xnorm_kernel<<<(h->npad + 127) / 128, 128, 0, h->stream>>>(h->dXt, h->d, h->npad, h->d_xnorm);
-  LAUNCH_CHECK("xnorm_kernel");
   if (small) {
     // small observation sets: factor, inverse and alpha in one launch of one CTA (fit_small.cuh)
     if ((r = ensure(h, h->d_fs, h->fs_cap, 8)) != PLX_OK) return r;
@@ -679,8 +679,6 @@ extern "C" int plx_gp_append(plx_bo_handle h, const double* x_new, double y_new)
   LAUNCH_CHECK("trmv_lower_t_kernel");
   scale_transpose_x_kernel<<<dim3((npad + 255) / 256, d), 256, 0, st>>>(h->dX, n1, d, npad, ell, h->dXt);
   LAUNCH_CHECK("scale_transpose_x_kernel");
-  xnorm_kernel<<<(npad + 127) / 128, 128, 0, st>>>(h->dXt, d, npad, h->d_xnorm);
-  LAUNCH_CHECK("xnorm_kernel");
   CK(sync_stream(h));          // y_new / lam2 live on this frame
   h->n = n1; h->i8_state_valid = false;
   { const int nt32 = (n1 + 31) / 32; h->ntri = nt32 * (nt32 + 1) / 2; }
@@ -759,10 +757,11 @@ static void fill_params(plx_bo* h, SweepParams& p, const double* Xc_dev, long lo
                         double kappa, double eps, double y_max) {
   p.Xc = Xc_dev; p.N = N; p.idx_base = idx_base;
   p.d = h->d; p.n = h->n; p.npad = h->npad; p.n16 = (h->n + 15) / 16 * 16;
-  p.X = h->dX; p.Xt = h->dXt; p.xnorm = h->i8_expand ? h->d_xnorm : nullptr; p.alpha = h->d_alpha_state; p.Z = h->dZ; p.ell = std::exp(h->theta);
+  p.X = h->dX; p.Xt = h->dXt; p.alpha = h->d_alpha_state; p.Z = h->dZ; p.ell = std::exp(h->theta);
   p.kind = h->kind; p.mg = h->mg; p.acq = acq; p.kappa = kappa; p.eps = eps; p.y_max = y_max;
   p.Ks = h->dKs; p.out_mean = p.out_std = p.out_acq = nullptr;
   p.planes = nullptr; p.plane_stride = 0;
+  p.xrow = p.xnc = p.xmean = nullptr;         // set by launch_sweep_i8 once the rows are built
   p.blk_val = h->d_blk_val; p.blk_idx = h->d_blk_idx; p.clamped = h->d_clamped; p.dbg = h->sweep_dbg;
 }
 
@@ -798,6 +797,10 @@ static int ensure_i8(plx_bo* h) {
     if ((r = ensure(h, h->d_i8sync, h->i8sync_cap, static_cast<size_t>(max_groups) * 8)) != PLX_OK) return r;
     h->i8_rows = rows; h->i8_npad = h->npad; h->i8_state_valid = false;
   }
+  // operands of the tensor-path builders (d <= 32): centre, centred rows, their norms
+  if ((r = ensure(h, h->d_xmean, h->xmean_cap, 32)) != PLX_OK) return r;
+  if ((r = ensure(h, h->d_xrow, h->xrow_cap, npad * XROW_LD)) != PLX_OK) return r;
+  if ((r = ensure(h, h->d_xnc, h->xnc_cap, npad)) != PLX_OK) return r;
   return PLX_OK;
 }
 
@@ -813,6 +816,14 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     CK(cudaMemsetAsync(h->d_kplanes, 0, static_cast<size_t>(I8_S) * rows * npad, st));
     zslice_kernel<<<h->npad, 128, 0, st>>>(h->dZ, h->npad, h->n, reinterpret_cast<int8_t*>(h->d_zplanes), h->d_zscale);
     LAUNCH_CHECK("zslice_kernel");
+    if (h->d <= 32) {
+      // operands of the tensor-path builders: centre, centred rows, their norms (same stream, before any sweep)
+      obs_centre_kernel<<<32, 256, 0, st>>>(h->dX, h->n, h->d, std::exp(h->theta), h->d_xmean);
+      LAUNCH_CHECK("obs_centre_kernel");
+      obs_rows_kernel<<<(h->npad + 127) / 128, 128, 0, st>>>(h->dX, h->n, h->d, h->npad, std::exp(h->theta), h->d_xmean,
+                                                            h->d_xrow, h->d_xnc);
+      LAUNCH_CHECK("obs_rows_kernel");
+    }
     h->i8_state_valid = true;
   }
   if (e0) CK(cudaEventRecord(e0, st));
@@ -830,6 +841,7 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     CK(cudaMemsetAsync(h->d_i8sync, 0, sizeof(unsigned) * max_groups * 8, st));
     SweepParams q = p;
     q.dbg = p.dbg & ~15; q.planes = h->d_kplanes; q.plane_stride = static_cast<size_t>(rows) * npad;
+    if (h->i8_distance >= 1 && h->d <= 32) { q.xrow = h->d_xrow; q.xnc = h->d_xnc; q.xmean = h->d_xmean; }
     I8Params ip;
     ip.N = p.N; ip.idx_base = p.idx_base; ip.n = p.n; ip.zscale = h->d_zscale; ip.mean = nullptr;
     ip.acq = p.acq; ip.kappa = p.kappa; ip.eps = p.eps; ip.y_max = p.y_max;
@@ -881,6 +893,7 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     const int grid = static_cast<int>(std::min<long long>((p.N + 127) / 128, h->num_sms));
     SweepParams q = p;
     q.dbg = p.dbg & ~15; q.planes = h->d_kplanes; q.plane_stride = static_cast<size_t>(rows) * npad;
+    if (h->i8_distance == 1 && h->d <= 32) { q.xrow = h->d_xrow; q.xnc = h->d_xnc; q.xmean = h->d_xmean; }
     I8Params ip;
     ip.N = p.N; ip.idx_base = p.idx_base; ip.n = p.n; ip.zscale = h->d_zscale; ip.mean = nullptr;
     ip.acq = p.acq; ip.kappa = p.kappa; ip.eps = p.eps; ip.y_max = p.y_max;

@@ -38,7 +38,10 @@ struct SweepParams {
   int d, n, npad, n16;     // observations, padded to 128, padded to 16
   const double* X;         // observations [n][d]
   const double* Xt;        // X / length_scale transposed to [d][npad] (TMA-ring kernel only)
-  const double* xnorm;     // nullable: |X_j / length_scale|^2 [npad]; when set the int8 builders expand |c - x|^2 (sweep_i8f.cuh)
+  const double* xrow;      // nullable: centred scaled observations, row-major [npad][40] (32 dimensions + padding); when set
+                           // (d <= 32) the int8 builders form the squared distances on the FP64 tensor path (sweep_i8f.cuh)
+  const double* xnc;       //   |row|^2 of xrow [npad]
+  const double* xmean;     //   the centre: mean of X / length_scale per dimension [32]
   const double* alpha;     // [npad]
   const double* Z;         // L^-1, row-major [npad][npad]
   double ell;              // length scale
@@ -550,14 +553,40 @@ __global__ void scale_transpose_x_kernel(const double* __restrict__ X, int n, in
   Xt[static_cast<size_t>(q) * npad + j] = (j < n) ? X[static_cast<size_t>(j) * d + q] / ell : 0.0;
 }
 
-// |X_j / l|^2 from the transposed scaled observations, one FMA chain per observation in dimension order (the order the
-// builders use for |c|^2 and c.x, so that identical points cancel exactly)
-__global__ void xnorm_kernel(const double* __restrict__ Xt, int d, int npad, double* __restrict__ xnorm) {
+// Centre of the scaled observations per dimension (one CTA per dimension, a fixed-shape tree sum: deterministic).
+__global__ void __launch_bounds__(256) obs_centre_kernel(const double* __restrict__ X, int n, int d, double ell,
+                                                         double* __restrict__ xmean) {
+  __shared__ double part[256];
+  const int q = blockIdx.x, tid = threadIdx.x;
+  double s = 0.0;
+  if (q < d)
+    for (int j = tid; j < n; j += 256) s += X[static_cast<size_t>(j) * d + q] / ell;
+  part[tid] = s;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (tid < o) part[tid] += part[tid + o];
+    __syncthreads();
+  }
+  if (tid == 0) xmean[q] = (q < d) ? part[0] / n : 0.0;
+}
+
+// Rows of centred scaled observations for the tensor-path builders: xrow[j][0..31] = X_j / l - centre (zero beyond d
+// and beyond n), columns 32..39 zero (the row stride of 40 doubles is what makes the builders' 16-byte fragment loads
+// conflict-free); xnc[j] = |row j|^2.
+constexpr int XROW_LD = 40;
+__global__ void obs_rows_kernel(const double* __restrict__ X, int n, int d, int npad, double ell,
+                                const double* __restrict__ xmean, double* __restrict__ xrow, double* __restrict__ xnc) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= npad) return;
   double s = 0.0;
-  for (int q = 0; q < d; ++q) { const double v = Xt[static_cast<size_t>(q) * npad + j]; s = fma(v, v, s); }
-  xnorm[j] = s;
+  double* row = xrow + static_cast<size_t>(j) * XROW_LD;
+  for (int q = 0; q < XROW_LD; ++q) {
+    double u = 0.0;
+    if (q < d && j < n) u = X[static_cast<size_t>(j) * d + q] / ell - xmean[q];
+    row[q] = u;
+    s = fma(u, u, s);
+  }
+  xnc[j] = s;
 }
 
 // Merge the per-CTA bests into the running best of the whole sweep (one thread; grid <= #SMs).

@@ -20,7 +20,12 @@ namespace plx {
 constexpr int F_CS_LD = 130;                               // Cs[32 dims][130]: scaled candidates of the tile
 constexpr int F_XS_LD = 64;                                // Xs[32 dims][64]: scaled observations of a 64-block
 constexpr int F_CS = 0, F_XS = 32 * F_CS_LD;
-constexpr int F_STAGING = (F_XS + 32 * F_XS_LD) * 8;       // 49 664 bytes
+// Tensor-path builders (build_tile_mma): Xr[64 observations][40] (centred scaled rows as obs_rows_kernel lays them out),
+// then |row|^2 and alpha of the 64 observations.  The larger of the two layouts sizes the staging area.
+constexpr int F_XR_LD = XROW_LD;
+constexpr int F_XN = F_XS + 64 * F_XR_LD, F_AL = F_XN + 64;
+constexpr int F_STAGING = (F_AL + 64) * 8;                 // 54 784 bytes
+static_assert(F_AL + 64 >= F_XS + 32 * F_XS_LD, "staging area holds either layout");
 constexpr int I8F_SMEM = I8_STAGES * I8_STAGE + F_STAGING + 1024 /*align*/ + 3072 /*tail*/;
 
 struct I8FTail {
@@ -74,11 +79,181 @@ __device__ __forceinline__ void builder_block(const SweepParams& p, double (&r2)
   }
 }
 
+// Eight kernel values of one candidate -> 7 planes x 8 packed digits (one 64-bit store per plane).
+__device__ __forceinline__ void store_digits8(signed char* dst, size_t plane_stride, const double (&k)[8]) {
+  long long q[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) q[j] = __double2ll_rn(k[j] * 18014398509481984.0);     // k * 2^54
+#pragma unroll
+  for (int s = I8_S - 1; s >= 0; --s) {
+    uint32_t word[2] = {0, 0};
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      int dgt;
+      if (s > 0) { dgt = static_cast<int>((q[j] + 128) & 255) - 128; q[j] = (q[j] - dgt) >> 8; }
+      else dgt = static_cast<int>(q[j]);                                              // leading digit, 0 .. 65
+      word[j >> 2] |= static_cast<uint32_t>(dgt & 255) << (8 * (j & 3));
+    }
+    *reinterpret_cast<uint2*>(dst + s * plane_stride) = make_uint2(word[0], word[1]);
+  }
+}
+
+// Builder role with the squared distances on the FP64 tensor path (d <= 32, p.xrow set).
+//
+// The distance loop of build_tile is half of the builders' time and the builders are what bounds the kernel: their
+// DFMA / DADD and their shared-memory loads are starved while the int8 tensor instructions execute
+// (tools/i8_side_load.cu).  Here r^2 = |u|^2 + |v|^2 - 2 u.v with u = c / l - m, v = x / l - m (m = centre of the
+// observations, which keeps |u|^2 + |v|^2 near r^2), and u.v comes from mma.sync.m8n8k4 (DMMA): 16x fewer
+// instructions and 6x fewer shared-memory loads than the direct differences for the same pairs.
+//   warp w       candidates 16 w .. 16 w + 15 (two 8-row M tiles), all 64 observations of a block (eight N tiles);
+//   A fragments  the warp's candidates: 16 doubles per thread and observation block, conflict-free 8-byte loads;
+//   B fragments  one 16-byte load per N tile and PAIR of K steps: thread t of a quad takes dimensions 8 P + 2 t
+//                (K step 2 P) and 8 P + 2 t + 1 (K step 2 P + 1) -- both operands use this assignment, so the product
+//                is unchanged;
+//   N tile (h, e), column n <-> observation 32 h + 8 (n >> 1) + 2 e + (n & 1), so that thread (g, t) ends up with
+//                the eight CONSECUTIVE observations 32 h + 8 t .. + 7 of its candidate (one 64-bit digit store).
+// Where the expansion cancels (r^2 < (|u|^2 + |v|^2) / 64: a candidate next to an observation) the pair is recomputed
+// from direct differences of the same u and v, so identical points still give exactly zero.
+template <int KIND>
+__device__ __forceinline__ void builder_rows_mma(const SweepParams& p, const double (&acc)[2][2][4][2], const double (&cn)[2],
+                                                 signed char* rows, int jb, uint32_t sm, int warp, int g, int t,
+                                                 double (&macc)[2]) {
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    double xn[8], al[8];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const double2 a = lds128(sm + static_cast<uint32_t>((F_XN + 32 * h + 8 * t + 2 * u) * 8));
+      const double2 b = lds128(sm + static_cast<uint32_t>((F_AL + 32 * h + 8 * t + 2 * u) * 8));
+      xn[2 * u] = a.x; xn[2 * u + 1] = a.y; al[2 * u] = b.x; al[2 * u + 1] = b.y;
+    }
+    const int jo = jb * 64 + 32 * h + 8 * t;
+#pragma unroll
+    for (int mi = 0; mi < 2; ++mi) {
+      const int c = 16 * warp + 8 * mi + g;
+      double v[8];
+#pragma unroll
+      for (int o = 0; o < 8; ++o) {
+        const double s = cn[mi] + xn[o];
+        double r = fma(-2.0, acc[mi][h][o >> 1][o & 1], s);
+        if (r < s * 0.015625) {                                // rare: direct differences
+          const uint32_t ca = sm + static_cast<uint32_t>((F_CS + c) * 8);
+          const uint32_t xa = sm + static_cast<uint32_t>((F_XS + (32 * h + 8 * t + o) * F_XR_LD) * 8);
+          r = 0.0;
+          for (int q = 0; q < 32; ++q) { const double df = lds64(ca + q * F_CS_LD * 8) - lds64(xa + q * 8); r = fma(df, df, r); }
+        }
+        v[o] = r;
+      }
+      kern_values_n<KIND, 8>(v);
+      double m = 0.0;
+#pragma unroll
+      for (int o = 0; o < 8; ++o) { v[o] = (jo + o < p.n) ? v[o] : 0.0; m = fma(v[o], al[o], m); }
+      store_digits8(rows + static_cast<size_t>(c) * p.npad + jo, p.plane_stride, v);
+      macc[mi] += m;
+    }
+  }
+}
+
+__device__ __forceinline__ void build_tile_mma(const SweepParams& p, long long tile, signed char* rows, double* mean_out,
+                                               uint32_t sm, int tid, int jb0, int jbstep) {
+  const int warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  const long long c_base = tile * 128;
+  const int nblk = (p.n + 63) / 64;
+  const int npair = (p.d + 7) / 8;
+  double2 pre[5];
+  double prex = 0.0;
+  auto fetch = [&](int jb) {
+    const double* src = p.xrow + static_cast<size_t>(jb) * 64 * F_XR_LD;
+#pragma unroll
+    for (int r = 0; r < 5; ++r) pre[r] = ldg128(src + 2 * (tid + 256 * r));
+    if (tid < 64) prex = p.xnc[jb * 64 + tid];
+    else if (tid < 128) prex = (jb * 64 + tid - 64 < p.n) ? p.alpha[jb * 64 + tid - 64] : 0.0;
+  };
+  if (jb0 < nblk) fetch(jb0);
+  named_bar_sync(1, 256);                                     // the previous tile's readers of Cs are done
+  for (int e = tid; e < 128 * 32; e += 256) {
+    const int c = e >> 5, q = e & 31;
+    double v = 0.0;
+    if (q < p.d && c_base + c < p.N) v = p.Xc[(c_base + c) * p.d + q] / p.ell - p.xmean[q];
+    sts64(sm + static_cast<uint32_t>((F_CS + q * F_CS_LD + c) * 8), v);
+  }
+  named_bar_sync(1, 256);
+  // A fragments: re-read from shared memory for every observation block (16 conflict-free 8-byte loads) rather than
+  // kept across the kernel-value stage, where their 32 registers are what would spill
+  const uint32_t afa = sm + static_cast<uint32_t>((F_CS + 2 * t * F_CS_LD + 16 * warp + g) * 8);
+  double cn[2], macc[2] = {0.0, 0.0};
+#pragma unroll
+  for (int mi = 0; mi < 2; ++mi) {
+    double s = 0.0;
+#pragma unroll
+    for (int P = 0; P < 4; ++P)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const double a = lds64(afa + ((8 * P + e) * F_CS_LD + 8 * mi) * 8);
+        s = fma(a, a, s);
+      }
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    cn[mi] = s;
+  }
+  for (int jb = jb0; jb < nblk; jb += jbstep) {
+    named_bar_sync(1, 256);                                   // readers of the previous observation block are done
+#pragma unroll
+    for (int r = 0; r < 5; ++r) sts128(sm + static_cast<uint32_t>(F_XS * 8 + (tid + 256 * r) * 16), pre[r]);
+    if (tid < 128) sts64(sm + static_cast<uint32_t>((F_XN + tid) * 8), prex);
+    named_bar_sync(1, 256);
+    if (jb + jbstep < nblk) fetch(jb + jbstep);
+    double acc[2][2][4][2];
+#pragma unroll
+    for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+      for (int h = 0; h < 2; ++h)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) acc[mi][h][e][0] = acc[mi][h][e][1] = 0.0;
+#pragma unroll
+    for (int P = 0; P < 4; ++P) {
+      if (P < npair) {
+        double af[2][2];
+#pragma unroll
+        for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+          for (int e = 0; e < 2; ++e) af[mi][e] = lds64(afa + ((8 * P + e) * F_CS_LD + 8 * mi) * 8);
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int ob = 32 * h + 8 * (g >> 1) + 2 * e + (g & 1);
+            const double2 b = lds128(sm + static_cast<uint32_t>((F_XS + ob * F_XR_LD + 8 * P + 2 * t) * 8));
+#pragma unroll
+            for (int mi = 0; mi < 2; ++mi) {
+              dmma(acc[mi][h][e][0], acc[mi][h][e][1], af[mi][0], b.x);
+              dmma(acc[mi][h][e][0], acc[mi][h][e][1], af[mi][1], b.y);
+            }
+          }
+      }
+    }
+    switch (p.kind) {
+      case K_RBF: builder_rows_mma<K_RBF>(p, acc, cn, rows, jb, sm, warp, g, t, macc); break;
+      case K_M05: builder_rows_mma<K_M05>(p, acc, cn, rows, jb, sm, warp, g, t, macc); break;
+      case K_M15: builder_rows_mma<K_M15>(p, acc, cn, rows, jb, sm, warp, g, t, macc); break;
+      default: builder_rows_mma<K_M25>(p, acc, cn, rows, jb, sm, warp, g, t, macc); break;
+    }
+  }
+#pragma unroll
+  for (int mi = 0; mi < 2; ++mi) {
+    double m = macc[mi];
+    m += __shfl_xor_sync(0xffffffffu, m, 1);
+    m += __shfl_xor_sync(0xffffffffu, m, 2);
+    if (t == 0) mean_out[16 * warp + 8 * mi + g] = m;
+  }
+}
+
 // Builder role for one tile: planes into `rows` (plane 0, first candidate row of the tile buffer), means into mean_out.
 // Only the 64-observation blocks jb0, jb0 + jbstep, ... are built (1, 0 = all of them; the cooperative kernel deals
 // the blocks to the CTAs of a group, and mean_out then receives this CTA's partial means).
 __device__ __forceinline__ void build_tile(const SweepParams& p, long long tile, signed char* rows, double* mean_out,
                                            uint32_t sm, int tid, int jb0 = 0, int jbstep = 1) {
+  if (p.xrow != nullptr) { build_tile_mma(p, tile, rows, mean_out, sm, tid, jb0, jbstep); return; }
   const int tx = tid & 15, ty = tid >> 4;
   const long long c_base = tile * 128;
   const int nchunk_d = (p.d + 31) / 32;
@@ -96,15 +271,12 @@ __device__ __forceinline__ void build_tile(const SweepParams& p, long long tile,
     }
   };
   if (jb0 < nblk) fetch(jb0, 0);
-  const bool expand = p.xnorm != nullptr;
   for (int jb = jb0; jb < nblk; jb += jbstep) {
-    double r2[8][4], cn[8];
+    double r2[8][4];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      cn[i] = 0.0;
+    for (int i = 0; i < 8; ++i)
 #pragma unroll
       for (int j = 0; j < 4; ++j) r2[i][j] = 0.0;
-    }
     for (int dc = 0; dc < nchunk_d; ++dc) {
       const int d0 = dc * 32, dn = min(32, p.d - d0);
       named_bar_sync(1, 256);                                 // readers of the previous shared tiles are done
@@ -129,46 +301,17 @@ __device__ __forceinline__ void build_tile(const SweepParams& p, long long tile,
       }
       const uint32_t cs = sm + static_cast<uint32_t>((F_CS + ty * 8) * 8);
       const uint32_t xs = sm + static_cast<uint32_t>((F_XS + 4 * tx) * 8);
-      if (!expand) {
 #pragma unroll 2
-        for (int q = 0; q < dn; ++q) {
-          double cv[8], xv[4];
+      for (int q = 0; q < dn; ++q) {
+        double cv[8], xv[4];
 #pragma unroll
-          for (int i = 0; i < 4; ++i) { const double2 t2 = lds128(cs + (q * F_CS_LD + 2 * i) * 8); cv[2 * i] = t2.x; cv[2 * i + 1] = t2.y; }
-          { const double2 a = lds128(xs + q * F_XS_LD * 8), b = lds128(xs + q * F_XS_LD * 8 + 16); xv[0] = a.x; xv[1] = a.y; xv[2] = b.x; xv[3] = b.y; }
+        for (int i = 0; i < 4; ++i) { const double2 t2 = lds128(cs + (q * F_CS_LD + 2 * i) * 8); cv[2 * i] = t2.x; cv[2 * i + 1] = t2.y; }
+        { const double2 a = lds128(xs + q * F_XS_LD * 8), b = lds128(xs + q * F_XS_LD * 8 + 16); xv[0] = a.x; xv[1] = a.y; xv[2] = b.x; xv[3] = b.y; }
 #pragma unroll
-          for (int i = 0; i < 8; ++i)
+        for (int i = 0; i < 8; ++i)
 #pragma unroll
-            for (int j = 0; j < 4; ++j) { const double df = cv[i] - xv[j]; r2[i][j] += df * df; }
-        }
-      } else {
-        // |c - x|^2 = |c|^2 + |x|^2 - 2 c.x: one FMA per pair and dimension instead of a subtraction and an FMA (the
-        // builders are the critical path of the kernel and two thirds of their FP64 work is this loop).  r2 holds
-        // the dot products here; |c|^2 rides along (8 more FMAs per dimension), |x|^2 comes precomputed with the
-        // same FMA chain, so a candidate that IS an observation still gets exactly zero.
-#pragma unroll 2
-        for (int q = 0; q < dn; ++q) {
-          double cv[8], xv[4];
-#pragma unroll
-          for (int i = 0; i < 4; ++i) { const double2 t2 = lds128(cs + (q * F_CS_LD + 2 * i) * 8); cv[2 * i] = t2.x; cv[2 * i + 1] = t2.y; }
-          { const double2 a = lds128(xs + q * F_XS_LD * 8), b = lds128(xs + q * F_XS_LD * 8 + 16); xv[0] = a.x; xv[1] = a.y; xv[2] = b.x; xv[3] = b.y; }
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            cn[i] = fma(cv[i], cv[i], cn[i]);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) r2[i][j] = fma(cv[i], xv[j], r2[i][j]);
-          }
-        }
+          for (int j = 0; j < 4; ++j) { const double df = cv[i] - xv[j]; r2[i][j] += df * df; }
       }
-    }
-    if (expand) {
-      double xn[4];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) xn[j] = p.xnorm[jb * 64 + 4 * tx + j];
-#pragma unroll
-      for (int i = 0; i < 8; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) r2[i][j] = fmax((cn[i] + xn[j]) - 2.0 * r2[i][j], 0.0);
     }
     const int jo = jb * 64 + 4 * tx;
     switch (p.kind) {

@@ -155,3 +155,40 @@ def test_a_planes_through_tensor_memory_equal_shared_memory_operands(handle, imp
         assert np.array_equal(out[0][k], out[1][k], equal_nan=True)
     m, s = _oracle(X, y, 0.2, G.KERNEL_MATERN, 2.5, xc[:4096])
     assert np.abs(out[0][4][:4096] ** 2 - s ** 2).max() <= 1e-9
+
+
+@pytest.mark.parametrize('impl', (5, 4))
+@pytest.mark.parametrize('n,d,kernel,nu', [(1600, 32, G.KERNEL_MATERN, 0.5), (700, 8, G.KERNEL_MATERN, 1.5),
+                                           (300, 1, G.KERNEL_RBF, 0.0), (2048, 31, G.KERNEL_MATERN, 2.5)])
+def test_tensor_path_distances_equal_direct_differences(handle, impl, n, d, kernel, nu):
+    """Option i8_distance: the builders form |c - x|^2 as |u|^2 + |v|^2 - 2 u.v with the cross term on the FP64
+    tensor path (1; the default of the cooperative form) or by direct differences (0).  Candidates that are
+    observations, or sit 1e-12 .. 1e-2 away from one, are where the expansion cancels: those pairs must be recomputed
+    directly (exactly zero / a relative-accurate small distance -- nu = 0.5 takes its square root)."""
+    X, y, _ = synthetic_problem(n, d, seed=11 + d)
+    theta = 0.4
+    handle.set_data(X, y, kernel, nu)
+    handle.set_theta(theta)
+    rs = np.random.RandomState(d)
+    near = [X[:40]] + [X[40 * (k + 1):40 * (k + 2)] + 10.0 ** (-12 + k) * rs.standard_normal((40, d)) for k in range(6)]
+    xc = np.vstack(near + [rs.uniform(0, 1, (128 * 37 + 5, d))])
+    m, s = _oracle(X, y, theta, kernel, nu, xc)
+    cond = np.linalg.cond(G.kernel_matrix(X, theta, kernel, nu) + G.GPR_ALPHA * np.eye(n))
+    mtol = max(1e-9, 100 * EPS * cond) * max(np.abs(m).max(), np.abs(y).max())
+    vtol = max(1e-9, 100 * EPS * cond)
+    out = {}
+    try:
+        handle.set_option('sweep_impl', impl)
+        for dist in (0, 1):
+            handle.set_option('i8_distance', dist)
+            out[dist] = handle.sweep(xc, G.ACQ_UCB, float(y.max()), kappa=1.0, dump=True)
+            assert np.abs(out[dist][3] - m).max() <= mtol, dist
+            assert np.abs(out[dist][4] ** 2 - s ** 2).max() <= vtol, dist
+    finally:
+        handle.set_option('i8_distance', 2)
+        handle.set_option('sweep_impl', 3)
+    if cond < 1e8:                                             # beyond that the runner-up may win within the tolerance
+        assert out[0][1] == out[1][1]
+    assert np.abs(out[0][4] ** 2 - out[1][4] ** 2).max() <= max(1e-10, EPS * cond)
+    assert np.abs(out[0][3] - out[1][3]).max() <= max(1e-10, EPS * cond) * max(np.abs(m).max(), 1.0)
+    assert (out[1][4][:40] ** 2).max() <= vtol                 # on the observations themselves
