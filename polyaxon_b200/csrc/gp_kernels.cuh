@@ -118,17 +118,29 @@ __device__ __forceinline__ double kern_value(int kind, double r2, const MaternGe
 // ~60 cycles of FP64 pipe work).  The arguments here are squared distances (>= 0) and non-positive
 // exponents, so the special cases reduce to two selects.
 
-// sqrt(x) for x >= 0: hardware reciprocal-square-root seed, one coupled Newton step for the
-// reciprocal root and one Heron correction with an exact FMA residual (<= 1 ulp); x below 1e-290 -> 0
+// The range checks below compare the HIGH WORD of the argument as an integer: DSETP runs on the FP64 pipe, which is
+// what the int8 sweep's builders are short of, the integer pipe is not.
+constexpr int HI_1E_290 = 0x03b8f2b1;                    // high word just above that of 1e-290
+constexpr int HI_708 = 0x40862000;                       // high word of 708.0 (low word 0)
+
+// k * 2^54 for a kernel value 0 <= k <= 1 by an integer add on the exponent field (exact, like the multiplication;
+// zero and denormal k turn into something below 2^-900, which the digit extraction rounds to zero all the same)
+__device__ __forceinline__ double scale_2p54(double k) {
+  return __hiloint2double(__double2hiint(k) + (54 << 20), __double2loint(k));
+}
+
+// sqrt(x) for x >= 0: hardware reciprocal-square-root seed (~2^-22), one coupled Goldschmidt step for the root and
+// half the reciprocal root, one Heron correction with an exact FMA residual (<= 1 ulp); x below 1e-290 (and -0) -> 0,
+// NaN -> NaN
 __device__ __forceinline__ double sqrt_pos(double x) {
   double y;
   asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
-  const double e = fma(x, -(y * y), 1.0);               // 1 - x y^2
-  const double y1 = fma(fma(e, 0.375, 0.5), y * e, y);  // y (1 + e/2 + 3 e^2/8)
-  const double r = x * y1;
-  const double res = fma(r, -r, x);
-  const double out = fma(res, 0.5 * y1, r);
-  return (x >= 1e-290) ? out : 0.0;
+  const double r0 = x * y, h0 = 0.5 * y;
+  const double e = fma(-r0, h0, 0.5);
+  const double r1 = fma(r0, e, r0), h1 = fma(h0, e, h0);
+  const double res = fma(-r1, r1, x);
+  const double out = fma(res, h1, r1);
+  return (__double2hiint(x) >= HI_1E_290) ? out : 0.0;
 }
 
 // exp(z) for z <= 0: z = k ln2 + r, |r| <= ln2/2, degree-13 Taylor polynomial in two interleaved
@@ -157,8 +169,9 @@ __device__ __forceinline__ double exp_neg(double z) {
   po = fma(po, r2, 1.0);
   const double p = fma(po, r, pe);
   const double scaled = __hiloint2double(__double2hiint(p) + (k << 20), __double2loint(p));
-  const double out = (z >= -708.0) ? scaled : 0.0;
-  return (z == z) ? out : z;
+  const int az = __double2hiint(z) & 0x7fffffff;         // |z| by its high word
+  const double out = (az <= HI_708) ? scaled : 0.0;
+  return (az > 0x7ff00000) ? z : out;                    // NaN
 }
 
 // N independent evaluations in lock step: every stage is written as a loop over the N values so the
@@ -170,15 +183,15 @@ __device__ __forceinline__ void sqrt_pos_n(double (&x)[N]) {
 #pragma unroll
   for (int i = 0; i < N; ++i) asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y[i]) : "d"(x[i]));
 #pragma unroll
-  for (int i = 0; i < N; ++i) e[i] = fma(x[i], -(y[i] * y[i]), 1.0);
+  for (int i = 0; i < N; ++i) { r[i] = x[i] * y[i]; y[i] = 0.5 * y[i]; }
 #pragma unroll
-  for (int i = 0; i < N; ++i) y[i] = fma(fma(e[i], 0.375, 0.5), y[i] * e[i], y[i]);
+  for (int i = 0; i < N; ++i) e[i] = fma(-r[i], y[i], 0.5);
 #pragma unroll
-  for (int i = 0; i < N; ++i) r[i] = x[i] * y[i];
+  for (int i = 0; i < N; ++i) { r[i] = fma(r[i], e[i], r[i]); y[i] = fma(y[i], e[i], y[i]); }
 #pragma unroll
-  for (int i = 0; i < N; ++i) e[i] = fma(r[i], -r[i], x[i]);
+  for (int i = 0; i < N; ++i) e[i] = fma(-r[i], r[i], x[i]);
 #pragma unroll
-  for (int i = 0; i < N; ++i) { const double o = fma(e[i], 0.5 * y[i], r[i]); x[i] = (x[i] >= 1e-290) ? o : 0.0; }
+  for (int i = 0; i < N; ++i) { const double o = fma(e[i], y[i], r[i]); x[i] = (__double2hiint(x[i]) >= HI_1E_290) ? o : 0.0; }
 }
 
 template <int N>
@@ -200,8 +213,9 @@ __device__ __forceinline__ void exp_neg_n(double (&z)[N]) {
   for (int i = 0; i < N; ++i) {
     const double p = fma(po[i], r[i], pe[i]);
     const double scaled = __hiloint2double(__double2hiint(p) + (__double2loint(kf[i]) << 20), __double2loint(p));
-    const double out = (z[i] >= -708.0) ? scaled : 0.0;
-    z[i] = (z[i] == z[i]) ? out : z[i];
+    const int az = __double2hiint(z[i]) & 0x7fffffff;
+    const double out = (az <= HI_708) ? scaled : 0.0;
+    z[i] = (az > 0x7ff00000) ? z[i] : out;
   }
 }
 

@@ -259,7 +259,7 @@ __device__ __forceinline__ void store_digits_q(signed char* dst, size_t plane_st
 // Kernel value k in [0, 1]: k = 4 * sum_s a_s 256^-(s+1) with the digits of round(k * 2^54) (|residual| <= 2^-55).
 __device__ __forceinline__ void store_digits(signed char* dst, size_t plane_stride, double k, int dbg = 0) {
   if (PLX_DBG(dbg, 16)) return;
-  store_digits_q(dst, plane_stride, __double2ll_rn(k * 18014398509481984.0));
+  store_digits_q(dst, plane_stride, __double2ll_rn(scale_2p54(k)));
 }
 
 // SL = false: FP64 kernel values into the K* slab; SL = true: their digit planes (Kslab then points at the

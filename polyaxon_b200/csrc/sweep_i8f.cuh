@@ -40,7 +40,7 @@ static_assert(sizeof(I8FTail) <= 3072, "tail budget");
 __device__ __forceinline__ void store_digits4(signed char* dst, size_t plane_stride, const double (&k)[4]) {
   long long q[4];
 #pragma unroll
-  for (int j = 0; j < 4; ++j) q[j] = __double2ll_rn(k[j] * 18014398509481984.0);     // k * 2^54
+  for (int j = 0; j < 4; ++j) q[j] = __double2ll_rn(scale_2p54(k[j]));
 #pragma unroll
   for (int s = I8_S - 1; s >= 0; --s) {
     uint32_t word = 0;
@@ -83,7 +83,7 @@ __device__ __forceinline__ void builder_block(const SweepParams& p, double (&r2)
 __device__ __forceinline__ void store_digits8(signed char* dst, size_t plane_stride, const double (&k)[8]) {
   long long q[8];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) q[j] = __double2ll_rn(k[j] * 18014398509481984.0);     // k * 2^54
+  for (int j = 0; j < 8; ++j) q[j] = __double2ll_rn(scale_2p54(k[j]));
 #pragma unroll
   for (int s = I8_S - 1; s >= 0; --s) {
     uint32_t word[2] = {0, 0};
@@ -136,7 +136,8 @@ __device__ __forceinline__ void builder_rows_mma(const SweepParams& p, const dou
       for (int o = 0; o < 8; ++o) {
         const double s = cn[mi] + xn[o];
         double r = fma(-2.0, acc[mi][h][o >> 1][o & 1], s);
-        if (r < s * 0.015625) {                                // rare: direct differences
+        // r < s / 64, compared on the bit patterns (integer pipe; a negative r has the sign bit set and is "less")
+        if (__double_as_longlong(r) < __double_as_longlong(s) - (6LL << 52)) {      // rare: direct differences
           const uint32_t ca = sm + static_cast<uint32_t>((F_CS + c) * 8);
           const uint32_t xa = sm + static_cast<uint32_t>((F_XS + (32 * h + 8 * t + o) * F_XR_LD) * 8);
           r = 0.0;
