@@ -61,7 +61,8 @@ int plx_bo_set_stream(plx_bo_handle h, void* stream);
  * "i8_distance" (builders of the int8-sliced sweeps, at most 32 dimensions: 0 = squared distances as (c - x)^2 summed
  * directly, the arithmetic of scipy's cdist; 1 = as |u|^2 + |v|^2 - 2 u.v with u, v centred on the observations'
  * mean, u.v on the FP64 tensor path (mma.sync), pairs where that cancels recomputed directly; 2 [default] = 1 in the
- * cooperative form (4 % faster there at the C3 shape), 0 in the fused form (slower there); posterior equal to 1e-10);
+ * cooperative form from 16 dimensions up (4 % faster there at the C3 shape), 0 otherwise (the fused form is slower with
+ * it, and with few dimensions too many pairs need the recomputation); posterior equal to 1e-10);
  * "blocking_sync" (0 [default]: calls wait for the GPU by spinning on the stream; 1: the host thread sleeps on an
  * event instead -- for processes whose worker threads outnumber their cores);
  * "potf_fused" (1 [default]: the diagonal 128-blocks of the fit are factorised and inverted in one pass of 128 column

@@ -841,7 +841,7 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     CK(cudaMemsetAsync(h->d_i8sync, 0, sizeof(unsigned) * max_groups * 8, st));
     SweepParams q = p;
     q.dbg = p.dbg & ~15; q.planes = h->d_kplanes; q.plane_stride = static_cast<size_t>(rows) * npad;
-    if (h->i8_distance >= 1 && h->d <= 32) { q.xrow = h->d_xrow; q.xnc = h->d_xnc; q.xmean = h->d_xmean; }
+    if (h->d <= 32 && (h->i8_distance == 1 || (h->i8_distance == 2 && h->d >= 16))) { q.xrow = h->d_xrow; q.xnc = h->d_xnc; q.xmean = h->d_xmean; }
     I8Params ip;
     ip.N = p.N; ip.idx_base = p.idx_base; ip.n = p.n; ip.zscale = h->d_zscale; ip.mean = nullptr;
     ip.acq = p.acq; ip.kappa = p.kappa; ip.eps = p.eps; ip.y_max = p.y_max;

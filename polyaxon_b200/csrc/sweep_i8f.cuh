@@ -112,8 +112,10 @@ __device__ __forceinline__ void store_digits8(signed char* dst, size_t plane_str
 //                is unchanged;
 //   N tile (h, e), column n <-> observation 32 h + 8 (n >> 1) + 2 e + (n & 1), so that thread (g, t) ends up with
 //                the eight CONSECUTIVE observations 32 h + 8 t .. + 7 of its candidate (one 64-bit digit store).
-// Where the expansion cancels (r^2 < (|u|^2 + |v|^2) / 64: a candidate next to an observation) the pair is recomputed
-// from direct differences of the same u and v, so identical points still give exactly zero.
+// Where the expansion cancels (r^2 < (|u|^2 + |v|^2) / 8: a candidate near an observation; the expansion's error is
+// ~32 ulp of |u|^2 + |v|^2, so what it keeps is good to ~3e-14 relative) the pair is recomputed from direct differences
+// of the same u and v, so identical points still give exactly zero.  With few dimensions many pairs fall under that
+// bound and the recomputation diverges the warp: the default takes this path from 16 dimensions up only.
 template <int KIND>
 __device__ __forceinline__ void builder_rows_mma(const SweepParams& p, const double (&acc)[2][2][4][2], const double (&cn)[2],
                                                  signed char* rows, int jb, uint32_t sm, int warp, int g, int t,
@@ -136,12 +138,12 @@ __device__ __forceinline__ void builder_rows_mma(const SweepParams& p, const dou
       for (int o = 0; o < 8; ++o) {
         const double s = cn[mi] + xn[o];
         double r = fma(-2.0, acc[mi][h][o >> 1][o & 1], s);
-        // r < s / 64, compared on the bit patterns (integer pipe; a negative r has the sign bit set and is "less")
-        if (__double_as_longlong(r) < __double_as_longlong(s) - (6LL << 52)) {      // rare: direct differences
+        // r < s / 8, compared on the bit patterns (integer pipe; a negative r has the sign bit set and is "less")
+        if (__double_as_longlong(r) < __double_as_longlong(s) - (3LL << 52)) {      // rare: direct differences
           const uint32_t ca = sm + static_cast<uint32_t>((F_CS + c) * 8);
           const uint32_t xa = sm + static_cast<uint32_t>((F_XS + (32 * h + 8 * t + o) * F_XR_LD) * 8);
           r = 0.0;
-          for (int q = 0; q < 32; ++q) { const double df = lds64(ca + q * F_CS_LD * 8) - lds64(xa + q * 8); r = fma(df, df, r); }
+          for (int q = 0; q < p.d; ++q) { const double df = lds64(ca + q * F_CS_LD * 8) - lds64(xa + q * 8); r = fma(df, df, r); }
         }
         v[o] = r;
       }

@@ -57,3 +57,5 @@ if __name__ == '__main__':
     run(1000, 2, 5000, 2, impl=4)
     run(1999, 32, 20000, 3)
     run(4096, 17, 148 * 128 * 2, 0)
+    run(2048, 2, 148 * 128 * 2, 2, check=False)       # few dimensions: many pairs under the cancellation bound
+    run(2048, 16, 148 * 128 * 2, 2, check=False)
