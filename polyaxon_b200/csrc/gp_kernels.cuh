@@ -239,7 +239,7 @@ __device__ __forceinline__ void kern_values_n(double (&v)[N]) {
 #pragma unroll
   for (int i = 0; i < N; ++i) {
     if (KIND == K_M15) v[i] = (1.0 + t[i]) * v[i];
-    else if (KIND == K_M25) v[i] = (1.0 + t[i] + t[i] * t[i] / 3.0) * v[i];
+    else if (KIND == K_M25) v[i] = (1.0 + t[i] + t[i] * t[i] * 0.3333333333333333) * v[i];   // no FP64 division in the sweep's inner loop
   }
 }
 
@@ -251,7 +251,7 @@ __device__ __forceinline__ double kern_value_t(double r2, const MaternGen& mg) {
   if (KIND == K_M05) return exp_neg(-r);
   if (KIND == K_M15) { const double t = r * 1.7320508075688772; return (1.0 + t) * exp_neg(-t); }
   const double t = r * 2.23606797749979;
-  return (1.0 + t + t * t / 3.0) * exp_neg(-t);
+  return (1.0 + t + t * t * 0.3333333333333333) * exp_neg(-t);
 }
 
 // test hook: out[i] = kern_value_t<kind>(r2[i])
