@@ -23,9 +23,12 @@ constexpr int F_CS = 0, F_XS = 32 * F_CS_LD;
 // Tensor-path builders (build_tile_mma): Xr[64 observations][40] (centred scaled rows as obs_rows_kernel lays them out),
 // then |row|^2 and alpha of the 64 observations.  The larger of the two layouts sizes the staging area.
 constexpr int F_XR_LD = XROW_LD;
-constexpr int F_XN = F_XS + 64 * F_XR_LD, F_AL = F_XN + 64;
-constexpr int F_STAGING = (F_AL + 64) * 8;                 // 54 784 bytes
-static_assert(F_AL + 64 >= F_XS + 32 * F_XS_LD, "staging area holds either layout");
+// |row|^2 and alpha sit at o + 2 (o >> 4): 16 bytes of padding per 128, so that the four threads of a quad, which
+// read eight consecutive values each (64 bytes apart), fall on distinct banks.
+constexpr int F_XN = F_XS + 64 * F_XR_LD, F_AL = F_XN + 72;
+constexpr int F_STAGING = (F_AL + 72) * 8;                 // 54 912 bytes
+static_assert(F_AL + 72 >= F_XS + 32 * F_XS_LD, "staging area holds either layout");
+__device__ __forceinline__ int xn_pos(int o) { return o + 2 * (o >> 4); }
 constexpr int I8F_SMEM = I8_STAGES * I8_STAGE + F_STAGING + 1024 /*align*/ + 3072 /*tail*/;
 
 struct I8FTail {
@@ -125,8 +128,8 @@ __device__ __forceinline__ void builder_rows_mma(const SweepParams& p, const dou
     double xn[8], al[8];
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-      const double2 a = lds128(sm + static_cast<uint32_t>((F_XN + 32 * h + 8 * t + 2 * u) * 8));
-      const double2 b = lds128(sm + static_cast<uint32_t>((F_AL + 32 * h + 8 * t + 2 * u) * 8));
+      const double2 a = lds128(sm + static_cast<uint32_t>((F_XN + xn_pos(32 * h + 8 * t) + 2 * u) * 8));
+      const double2 b = lds128(sm + static_cast<uint32_t>((F_AL + xn_pos(32 * h + 8 * t) + 2 * u) * 8));
       xn[2 * u] = a.x; xn[2 * u + 1] = a.y; al[2 * u] = b.x; al[2 * u + 1] = b.y;
     }
     const int jo = jb * 64 + 32 * h + 8 * t;
@@ -203,7 +206,7 @@ __device__ __forceinline__ void build_tile_mma(const SweepParams& p, long long t
     named_bar_sync(1, 256);                                   // readers of the previous observation block are done
 #pragma unroll
     for (int r = 0; r < 5; ++r) sts128(sm + static_cast<uint32_t>(F_XS * 8 + (tid + 256 * r) * 16), pre[r]);
-    if (tid < 128) sts64(sm + static_cast<uint32_t>((F_XN + tid) * 8), prex);
+    if (tid < 128) sts64(sm + static_cast<uint32_t>(((tid < 64 ? F_XN : F_AL) + xn_pos(tid & 63)) * 8), prex);
     named_bar_sync(1, 256);
     if (jb + jbstep < nblk) fetch(jb + jbstep);
     double acc[2][2][4][2];
