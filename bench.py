@@ -355,7 +355,7 @@ def sweep_kernel_name(impl, n):
         return 'sweep_tma_kernel'
     if impl == 2:
         return 'kstar_slices_kernel + sweep_i8_kernel'
-    if impl == 4 or (impl in (3, 7) and n < 1536):
+    if impl == 4 or (impl in (3, 7) and n < (1024 if 16 <= D <= 32 else 1536)):
         return 'sweep_i8f_kernel'
     if impl == 6:
         return 'sweep_i8p_kernel'

@@ -49,7 +49,7 @@ int plx_bo_set_stream(plx_bo_handle h, void* stream);
 
 /* Options: "sweep_impl" (3 [default] = a thread per candidate against the state in shared memory up to 64 observations
  * (sweep_small.cuh; 7 = the same rule, named), int8-sliced sweep on the tcgen05 tensor cores from 256 observations up
- * (fused form below 1536 observations, cooperative form from there) and the FP64 DMMA kernel below 256; 5 = always the cooperative int8-sliced sweep (four CTAs per
+ * (fused form below 1536 observations -- 1024 where the tensor-path builders apply, see "i8_distance" --, cooperative form from there) and the FP64 DMMA kernel below 256; 5 = always the cooperative int8-sliced sweep (four CTAs per
  * candidate tile); 6 = the cooperative form with the four CTAs as two clusters of two that share the candidate planes'
  * stream by TMA multicast (same results, measured equal in speed); 4 = the fused int8-sliced sweep (one CTA per tile); 2 = int8-sliced as two kernels per chunk;
  * 1 = always FP64 DMMA with the TMA ring; 0 = plain-load cross-check); "i8_operand" (0 [default] = the digit planes of

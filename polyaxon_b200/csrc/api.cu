@@ -828,7 +828,11 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
   }
   if (e0) CK(cudaEventRecord(e0, st));
   const int impl_i8 = h->sweep_impl == 7 ? 3 : h->sweep_impl;
-  if (impl_i8 == 5 || impl_i8 == 6 || (impl_i8 == 3 && p.n >= 1536)) {
+  // squared distances on the FP64 tensor path (build_tile_mma): at most 32 dimensions; by default in the cooperative
+  // form from 16 dimensions up, where it also moves the cross-over with the fused form from 1536 to 1024 observations
+  // (n = 1024, d = 32: 7.97 against 8.46 ms per 400 000 candidates; n = 512, d = 16: the fused form still wins)
+  const bool mma_dist = h->d <= 32 && (h->i8_distance == 1 || (h->i8_distance == 2 && h->d >= 16));
+  if (impl_i8 == 5 || impl_i8 == 6 || (impl_i8 == 3 && (p.n >= 1536 || (mma_dist && p.n >= 1024)))) {
     // cooperative forms: groups of four CTAs share a candidate tile so that the planes in flight stay in L2.
     // 6: the four are two clusters of two that fetch the A stream once per pair (TMA multicast); measured equal to 5
     // (8.3 ms against 8.2 ms per 151 552 candidates: the operand stream is not what bounds the kernel), so the
@@ -841,7 +845,7 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     CK(cudaMemsetAsync(h->d_i8sync, 0, sizeof(unsigned) * max_groups * 8, st));
     SweepParams q = p;
     q.dbg = p.dbg & ~15; q.planes = h->d_kplanes; q.plane_stride = static_cast<size_t>(rows) * npad;
-    if (h->d <= 32 && (h->i8_distance == 1 || (h->i8_distance == 2 && h->d >= 16))) { q.xrow = h->d_xrow; q.xnc = h->d_xnc; q.xmean = h->d_xmean; }
+    if (mma_dist) { q.xrow = h->d_xrow; q.xnc = h->d_xnc; q.xmean = h->d_xmean; }
     I8Params ip;
     ip.N = p.N; ip.idx_base = p.idx_base; ip.n = p.n; ip.zscale = h->d_zscale; ip.mean = nullptr;
     ip.acq = p.acq; ip.kappa = p.kappa; ip.eps = p.eps; ip.y_max = p.y_max;
@@ -935,7 +939,8 @@ static int launch_sweep(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cudaEve
   const int grid = static_cast<int>(std::min<long long>(ntiles, h->num_sms));
   if (grid <= 0) return PLX_OK;
   // 3 (default): the int8-sliced sweep from 256 observations up (measured break-even between 128 and 256; fused
-  // form up to 1535 observations, cooperative form -- four CTAs per tile, planes L2-resident -- from 1536),
+  // form up to 1535 observations, cooperative form -- four CTAs per tile, planes L2-resident -- from 1536, or from
+  // 1024 where the tensor-path builders apply: launch_sweep_i8),
   // FP64 DMMA below and for the general-nu Matern kernel, whose Bessel evaluation dominates anyway
   if ((h->sweep_impl == 3 || h->sweep_impl == 7) && p.n <= SS_NMAX) {
     // small observation sets: a thread per candidate against the state in shared memory (sweep_small.cuh)
