@@ -192,3 +192,25 @@ def test_tensor_path_distances_equal_direct_differences(handle, impl, n, d, kern
     assert np.abs(out[0][4] ** 2 - out[1][4] ** 2).max() <= max(1e-10, EPS * cond)
     assert np.abs(out[0][3] - out[1][3]).max() <= max(1e-10, EPS * cond) * max(np.abs(m).max(), 1.0)
     assert (out[1][4][:40] ** 2).max() <= vtol                 # on the observations themselves
+
+
+@pytest.mark.parametrize('n,d', [(1100, 20), (1100, 8), (1500, 32)])
+def test_default_form_between_1024_and_1536_observations(handle, n, d):
+    """The default (sweep_impl 3) picks the cooperative form from 1024 observations when the tensor-path builders apply
+    (16 to 32 dimensions) and the fused form otherwise; either way the posterior is the oracle's."""
+    X, y, _ = synthetic_problem(n, d, seed=n + d)
+    theta = 0.5
+    handle.set_data(X, y, G.KERNEL_MATERN, 1.5)
+    handle.set_theta(theta)
+    xc = np.random.RandomState(n).uniform(0, 1, (128 * 148 + 9, d))
+    m, s = _oracle(X, y, theta, G.KERNEL_MATERN, 1.5, xc)
+    cond = np.linalg.cond(G.kernel_matrix(X, theta, G.KERNEL_MATERN, 1.5) + G.GPR_ALPHA * np.eye(n))
+    handle.set_option('sweep_impl', 3)
+    val, idx, x, mean, std, acq = handle.sweep(xc, G.ACQ_EI, float(y.max()), eps=0.0, dump=True)
+    assert np.abs(mean - m).max() <= max(1e-9, 100 * EPS * cond) * max(np.abs(m).max(), np.abs(y).max())
+    assert np.abs(std ** 2 - s ** 2).max() <= max(1e-9, 100 * EPS * cond)
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        want = G.acquisition(m, s, G.ACQ_EI, float(y.max()), 0.0, 0.0)
+    if cond < 1e8:
+        assert idx == G.argmax_first(want)
