@@ -234,15 +234,33 @@ __global__ void __launch_bounds__(512, 1) sweep_i8c_kernel(const __grid_constant
     } else if (warp == 13) {
       // ===== tensor-instruction issuer: the whole warp walks the loops, one elected lane issues =====
       uint32_t it = 0, acc_round = 0, ring = 0;
-      for (long long tile = g; tile < ntiles; tile += groups)
+#ifdef PLX_PROFILE
+      long long t_acce = 0, t_full = 0, t_all = clock64(), n_tiles = 0;
+#endif
+      for (long long tile = g; tile < ntiles; tile += groups) {
+#ifdef PLX_PROFILE
+        ++n_tiles;
+#endif
         for (int h = 0; h < nh; ++h) {
           if (part_of(h) != r) continue;
-          if (!PLX_DBG(p.dbg, 512)) mbar_wait(bar_acce, (acc_round & 1) ^ 1);   // the previous half-block has been drained (512: timing experiment without the wait, results invalid)
+#ifdef PLX_PROFILE
+          const long long c0 = clock64();
+#endif
+          mbar_wait(bar_acce, (acc_round & 1) ^ 1);        // the previous half-block has been drained
+#ifdef PLX_PROFILE
+          t_acce += clock64() - c0;
+#endif
           ++acc_round;
           asm volatile("tcgen05.fence::after_thread_sync;\n");
           for (int kc = 0; kc < (h + 1) * I8_CPH; ++kc, ++it) {
             const uint32_t s = it % I8_STAGES, ph = (it / I8_STAGES) & 1;
+#ifdef PLX_PROFILE
+            const long long c1 = clock64();
+#endif
             mbar_wait(bar0 + 8 * s, ph);
+#ifdef PLX_PROFILE
+            t_full += clock64() - c1;
+#endif
             asm volatile("tcgen05.fence::after_thread_sync;\n");
             const uint32_t a0 = s0 + s * I8_STAGE;
             const uint64_t da0 = umma_desc_k(a0), db0 = umma_desc_k(a0 + I8_A_BYTES);
@@ -257,6 +275,12 @@ __global__ void __launch_bounds__(512, 1) sweep_i8c_kernel(const __grid_constant
           if (elect_one()) umma_commit(bar_accf);          // accumulators of this half-block complete
           __syncwarp();
         }
+      }
+#ifdef PLX_PROFILE
+      if (PLX_DBG(p.dbg, 2048) && lane == 0 && (blockIdx.x < 4 || blockIdx.x == 77) && n_tiles > 0)
+        printf("cta %d issuer: per tile %lld clk in all, %lld waiting for the drain, %lld waiting for a full stage\n",
+               blockIdx.x, (clock64() - t_all) / n_tiles, t_acce / n_tiles, t_full / n_tiles);
+#endif
     }
   }
   asm volatile("tcgen05.fence::before_thread_sync;\n");
