@@ -214,3 +214,25 @@ def test_default_form_between_1024_and_1536_observations(handle, n, d):
         want = G.acquisition(m, s, G.ACQ_EI, float(y.max()), 0.0, 0.0)
     if cond < 1e8:
         assert idx == G.argmax_first(want)
+
+
+@pytest.mark.parametrize('impl', (3, 4, 1))
+def test_nan_candidate_wins_the_arg_max_like_numpy(handle, impl):
+    """A candidate with a NaN coordinate has a NaN acquisition value in the reference (sklearn propagates it through
+    cdist and the kernel), and numpy's arg-max returns the first NaN (acquisition_function.py:91).  The builders'
+    range checks work on bit patterns and the tensor-path distances go through DMMA: the NaN must survive both."""
+    n, d = 1600, 20
+    X, y, _ = synthetic_problem(n, d, seed=3)
+    handle.set_data(X, y, G.KERNEL_MATERN, 1.5)
+    handle.set_theta(0.3)
+    xc = np.random.RandomState(8).uniform(0, 1, (128 * 40 + 3, d))
+    xc[777, 5] = np.nan
+    xc[3000, 0] = np.nan
+    try:
+        handle.set_option('sweep_impl', impl)
+        val, idx, x, mean, std, acq = handle.sweep(xc, G.ACQ_UCB, float(y.max()), kappa=1.0, dump=True)
+    finally:
+        handle.set_option('sweep_impl', 3)
+    assert idx == 777 and np.isnan(val)
+    assert np.isnan(acq[777]) and np.isnan(acq[3000])
+    assert np.isfinite(np.delete(acq, [777, 3000])).all()
