@@ -619,10 +619,32 @@ __global__ void __launch_bounds__(256) potf2_inv_kernel(BatchPtrs bp, int k, int
 // BJ the live parts are a, q >= BJ of A and a >= BJ, q <= BJ of R (column block BJ of R is created when it is
 // first needed, which keeps the live registers at 9 (8 - BJ) values).
 // ---------------------------------------------------------------------------------------------
+// Pivot of column step j from the published column: l_jj and 1 / l_jj (reciprocal-square-root seed, one coupled
+// Newton step, one Heron correction, one Newton step for the reciprocal).  A non-positive or NaN pivot is recorded
+// and replaced by 1 so that the remaining steps stay finite.
+__device__ __forceinline__ void potf_pivot(const double* cb, int j, int k, int* bad, int tid, double& ljj, double& inv) {
+  double ajj = cb[j];
+  if (!(ajj > 0.0)) {                   // non-positive or NaN pivot: not positive definite
+    if (tid == 0 && *bad == 0) *bad = k * 128 + j + 1;
+    ajj = 1.0;
+  }
+  double y0;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y0) : "d"(ajj));
+  const double e0 = fma(ajj, -(y0 * y0), 1.0);
+  inv = fma(fma(e0, 0.375, 0.5), y0 * e0, y0);
+  ljj = ajj * inv;
+  ljj = fma(fma(ljj, -ljj, ajj), 0.5 * inv, ljj);
+  inv = fma(fma(-ljj, inv, 1.0), inv, inv);              // 1 / ljj
+}
+
+// (ljj, inv) enter with the pivot of this block's first column and leave with that of the next block's: the pivot of
+// step j + 1 is computed right after the barrier of step j, in the same basic block as the rank-1 update, so that its
+// dependent chain of ~12 FP64 operations is interleaved with the update's independent ones instead of standing at the
+// head of the next step.
 template <int BJ>
 __device__ __forceinline__ bool potf_fused_cols(double (&accA)[8][8], double (&accW)[8][8], double* S,
                                                 double (*colbuf)[128], double (*rowbuf)[128], double* dl, double* wdiag,
-                                                int* bad, int k, int m, int ti, int tc, int tid) {
+                                                int* bad, int k, int m, int ti, int tc, int tid, double& ljj, double& inv) {
   // column block BJ of R: the identity (rows of earlier blocks never reach it)
 #pragma unroll
   for (int a = BJ; a < 8; ++a) accW[a][BJ] = (a == BJ && ti == tc) ? 1.0 : 0.0;
@@ -634,18 +656,6 @@ __device__ __forceinline__ bool potf_fused_cols(double (&accA)[8][8], double (&a
     double* cnx = colbuf[(j + 1) & 1];
     const double* rb = rowbuf[j & 1];
     double* rnx = rowbuf[(j + 1) & 1];
-    double ajj = cb[j];
-    if (!(ajj > 0.0)) {                 // non-positive or NaN pivot: not positive definite
-      if (tid == 0 && *bad == 0) *bad = k * 128 + j + 1;
-      ajj = 1.0;
-    }
-    double y0;
-    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y0) : "d"(ajj));
-    const double e0 = fma(ajj, -(y0 * y0), 1.0);
-    double inv = fma(fma(e0, 0.375, 0.5), y0 * e0, y0);
-    double ljj = ajj * inv;
-    ljj = fma(fma(ljj, -ljj, ajj), 0.5 * inv, ljj);
-    inv = fma(fma(-ljj, inv, 1.0), inv, inv);            // 1 / ljj
     double li[8], lc[8], wr[8];
 #pragma unroll
     for (int a = BJ; a < 8; ++a) { li[a] = cb[ti + 16 * a] * inv; lc[a] = cb[tc + 16 * a] * inv; }
@@ -678,6 +688,7 @@ __device__ __forceinline__ bool potf_fused_cols(double (&accA)[8][8], double (&a
     if (tid < j) S[tid * POTF_LD + j] = rb[tid] * inv;                    // W[j][c], c < j, parked at S[c][j]
     if (tid == 0) { dl[j] = ljj; wdiag[j] = inv; }
     __syncthreads();
+    if (j + 1 < m && j + 1 < 128) potf_pivot(cnx, j + 1, k, bad, tid, ljj, inv);      // column j + 1 is in cnx now
 #pragma unroll
     for (int a = BJ; a < 8; ++a) {
 #pragma unroll
@@ -725,14 +736,16 @@ __global__ void __launch_bounds__(256) potf2_fused_kernel(BatchPtrs bp, int k, i
   for (int e = tid; e < 128 * POTF_LD; e += 256) S[e] = 0.0;
   if (tid < 128) { dl[tid] = 1.0; wdiag[tid] = 1.0; }
   __syncthreads();
-  potf_fused_cols<0>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid) &&
-      potf_fused_cols<1>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid) &&
-      potf_fused_cols<2>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid) &&
-      potf_fused_cols<3>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid) &&
-      potf_fused_cols<4>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid) &&
-      potf_fused_cols<5>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid) &&
-      potf_fused_cols<6>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid) &&
-      potf_fused_cols<7>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid);
+  double ljj = 1.0, inv = 1.0;
+  if (m > 0) potf_pivot(colbuf[0], 0, k, &bad, tid, ljj, inv);
+  potf_fused_cols<0>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid, ljj, inv) &&
+      potf_fused_cols<1>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid, ljj, inv) &&
+      potf_fused_cols<2>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid, ljj, inv) &&
+      potf_fused_cols<3>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid, ljj, inv) &&
+      potf_fused_cols<4>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid, ljj, inv) &&
+      potf_fused_cols<5>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid, ljj, inv) &&
+      potf_fused_cols<6>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid, ljj, inv) &&
+      potf_fused_cols<7>(accA, accW, S, colbuf, rowbuf, dl, wdiag, &bad, k, m, ti, tc, tid, ljj, inv);
   __syncthreads();
   if (tid < 128) S[tid * POTF_LD + tid] = dl[tid];
   __syncthreads();
