@@ -648,7 +648,7 @@ __device__ __forceinline__ bool potf_fused_cols(double (&accA)[8][8], double (&a
   // column block BJ of R: the identity (rows of earlier blocks never reach it)
 #pragma unroll
   for (int a = BJ; a < 8; ++a) accW[a][BJ] = (a == BJ && ti == tc) ? 1.0 : 0.0;
-#pragma unroll 1
+#pragma unroll 4
   for (int jj = 0; jj < 16; ++jj) {
     const int j = 16 * BJ + jj;
     if (j >= m) return false;
