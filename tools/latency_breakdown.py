@@ -22,6 +22,7 @@ def t(fn, reps=5):
 for label, n, d, kern, nu, R, N, S, acq in [
         ('C1', 15, 2, _lib.KERNEL_MATERN, 2.5, 1, 100000, 10, _lib.ACQ_UCB),
         ('C5m', 128, 16, _lib.KERNEL_MATERN, 2.5, 5, 100000, 10, _lib.ACQ_EI),
+        ('C5', 512, 16, _lib.KERNEL_MATERN, 2.5, 5, 100000, 10, _lib.ACQ_EI),
         ('C2', 256, 8, _lib.KERNEL_RBF, 1.5, 1, 1000000, 10, _lib.ACQ_EI),
         ('C3fit', 2048, 32, _lib.KERNEL_MATERN, 1.5, 17, 0, 10, _lib.ACQ_POI),
         ('C4-512', 512, 32, _lib.KERNEL_MATERN, 1.5, 33, 0, 0, _lib.ACQ_POI),
