@@ -51,6 +51,16 @@ TRAFFIC = {
 }
 
 
+def measured_peaks():
+    """The driver-written peaks of this pool (MEASURED_PEAKS.json at the repo root), or None."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'MEASURED_PEAKS.json')
+    try:
+        with open(path) as f:
+            return json.load(f)
+    except (OSError, ValueError):
+        return None
+
+
 def flops_per_eval(n, d):
     """SURVEY.md section 8d / BASELINE.md: n(3d+10) + n^2 + 4n (triangular variance)."""
     return n * (3 * d + 10) + n * n + 4 * n
@@ -522,6 +532,15 @@ def main():
                                '(plx_measure_i8_peak, best of the repeats within 1.5 s); with random operands the same loop draws more power and '
                                'measures ~4070 TOP/s on this pool (tools/i8_umma_gemm.cu), so this is the upper figure',
                 'a_operand': 'shared memory' if args.i8_operand else 'tensor memory (tcgen05.cp ring)'})
+            mp = measured_peaks()
+            if mp and mp.get('bf16_tflops'):
+                # the driver's own figures for this pool: dense bf16 by torch.matmul, burst and sustained; the int8 rate of
+                # the same tensor pipe is twice the bf16 rate, so these are the denominators a reader of that file would use
+                roofline['vs_measured_peaks'] = {
+                    'source': 'MEASURED_PEAKS.json: 2 x bf16_tflops (burst) and 2 x bf16_tflops_sustained (a long step)',
+                    'int8_peak_burst_tops': 2.0 * mp['bf16_tflops'], 'frac_of_burst': achieved / (2.0 * mp['bf16_tflops']),
+                    'int8_peak_sustained_tops': 2.0 * mp['bf16_tflops_sustained'] if mp.get('bf16_tflops_sustained') else None,
+                    'frac_of_sustained': achieved / (2.0 * mp['bf16_tflops_sustained']) if mp.get('bf16_tflops_sustained') else None}
         else:
             roofline.update({'pipe': 'FP64 tensor (DMMA.8x8x4)', 'achieved': fp64_equiv, 'peak': dgemm,
                              'unit': 'TFLOP/s', 'frac': fp64_equiv / dgemm,
