@@ -101,7 +101,24 @@ __global__ void __launch_bounds__(256) refine_v_kernel(RefineParams p) {
     double acc[RF_SB];
 #pragma unroll
     for (int b = 0; b < RF_SB; ++b) acc[b] = 0.0;
-    for (int j = lane; j <= i; j += 32) {
+    // four strides of the row at a time: their loads are issued together (the products are added in the same order as
+    // one stride at a time would add them)
+    int j = lane;
+    for (; j + 96 <= i; j += 128) {
+      double z[4], kk[4][RF_SB];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        z[u] = Zi[j + 32 * u];
+#pragma unroll
+        for (int b = 0; b < RF_SB; ++b) kk[u][b] = (s0 + b < p.S) ? p.kv[static_cast<size_t>(s0 + b) * p.npad + j + 32 * u] : 0.0;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int b = 0; b < RF_SB; ++b)
+          if (s0 + b < p.S) acc[b] += z[u] * kk[u][b];
+    }
+    for (; j <= i; j += 32) {
       const double z = Zi[j];
 #pragma unroll
       for (int b = 0; b < RF_SB; ++b)
@@ -126,16 +143,35 @@ __global__ void __launch_bounds__(128) refine_w_kernel(RefineParams p) {
   const int rc = blockIdx.x, cb = blockIdx.y, r0 = rc * RF_WROWS, j = cb * 128 + threadIdx.x;
   const int r1 = min(r0 + RF_WROWS, p.n);
   if (cb * 128 > r1 - 1) return;                                       // above the diagonal: nothing stored, nothing read
+  __shared__ double vsm[RF_SB][RF_WROWS];                              // v of this CTA's rows for the seeds of a pass
   for (int s0 = 0; s0 < p.S; s0 += RF_SB) {
+    __syncthreads();
+    for (int e = threadIdx.x; e < RF_SB * RF_WROWS; e += 128) {
+      const int b = e / RF_WROWS, i = r0 + e % RF_WROWS;
+      vsm[b][e % RF_WROWS] = (s0 + b < p.S && i < r1) ? p.v[static_cast<size_t>(s0 + b) * p.npad + i] : 0.0;
+    }
+    __syncthreads();
     double acc[RF_SB];
 #pragma unroll
     for (int b = 0; b < RF_SB; ++b) acc[b] = 0.0;
     if (j < p.n) {
-      for (int i = max(r0, j); i < r1; ++i) {
+      // eight rows of the column at a time: their loads are in flight together, the products are added row by row
+      int i = max(r0, j);
+      for (; i + 8 <= r1; i += 8) {
+        double z[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) z[u] = p.Z[static_cast<size_t>(i + u) * p.npad + j];
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+#pragma unroll
+          for (int b = 0; b < RF_SB; ++b)
+            if (s0 + b < p.S) acc[b] += z[u] * vsm[b][i + u - r0];
+      }
+      for (; i < r1; ++i) {
         const double z = p.Z[static_cast<size_t>(i) * p.npad + j];
 #pragma unroll
         for (int b = 0; b < RF_SB; ++b)
-          if (s0 + b < p.S) acc[b] += z * p.v[static_cast<size_t>(s0 + b) * p.npad + i];
+          if (s0 + b < p.S) acc[b] += z * vsm[b][i - r0];
       }
 #pragma unroll
       for (int b = 0; b < RF_SB; ++b)
@@ -347,7 +383,22 @@ __device__ __forceinline__ void refine_step_body(const RefineParams& p, int s, d
     double a1 = 0.0, a2 = 0.0;
     if (q < p.d) {
       const double xq = x[q];
-      for (int j = warp; j < p.n; j += nw) {
+      int j = warp;
+      for (; j + 3 * nw < p.n; j += 4 * nw) {              // four observations' loads in flight, added in the same order
+        double kpj[4], xj[4], aj[4], wj[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int ju = j + u * nw;
+          kpj[u] = kp[ju]; xj[u] = p.X[static_cast<size_t>(ju) * p.d + q]; aj[u] = p.alpha[ju]; wj[u] = w[ju];
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const double c = 2.0 * kpj[u] * inv_l2 * (xq - xj[u]);
+          a1 += c * aj[u];
+          a2 += c * wj[u];
+        }
+      }
+      for (; j < p.n; j += nw) {
         const double c = 2.0 * kp[j] * inv_l2 * (xq - p.X[static_cast<size_t>(j) * p.d + q]);
         a1 += c * p.alpha[j];
         a2 += c * w[j];
@@ -407,7 +458,7 @@ __device__ __forceinline__ void refine_step_body(const RefineParams& p, int s, d
   if (lane == 0) p.sc[s] = sc;
 }
 
-// One CTA (128 threads) per seed, one round: used with refine_kstar / refine_v / refine_w kernels for large n.
+// One CTA per seed, one round: used with refine_kstar / refine_v / refine_w kernels for large n.
 __global__ void __launch_bounds__(512) refine_step_kernel(RefineParams p) {
   extern __shared__ double rf_grad_smem[];        // gm[d] | gv[d]
   const int s = blockIdx.x;
@@ -417,7 +468,15 @@ __global__ void __launch_bounds__(512) refine_step_kernel(RefineParams p) {
     const int nrc = (p.n + RF_WROWS - 1) / RF_WROWS;
     for (int j = threadIdx.x; j < p.n; j += blockDim.x) {
       double t = 0.0;
-      for (int rc = j / RF_WROWS; rc < nrc; ++rc) t += p.wpart[(static_cast<size_t>(rc) * p.S + s) * p.npad + j];
+      int rc = j / RF_WROWS;
+      for (; rc + 8 <= nrc; rc += 8) {                                   // eight chunks' loads in flight, added in chunk order
+        double u[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) u[q] = p.wpart[(static_cast<size_t>(rc + q) * p.S + s) * p.npad + j];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) t += u[q];
+      }
+      for (; rc < nrc; ++rc) t += p.wpart[(static_cast<size_t>(rc) * p.S + s) * p.npad + j];
       p.w[static_cast<size_t>(s) * p.npad + j] = t;
     }
     __syncthreads();
