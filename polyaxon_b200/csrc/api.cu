@@ -64,6 +64,7 @@ struct plx_bo {
   double* dKs = nullptr; size_t ks_cap = 0;
   double* dXt = nullptr; size_t xt_cap = 0;
   int i8_distance = 2;                                // builders of the int8 sweeps: 0 direct differences, 1 FP64 tensor path, 2 by form
+  double* d_mgtab = nullptr; size_t mgtab_cap = 0; int gen_table = 1;   // Chebyshev table of the general-nu kernel value (sweeps)
   double* d_xrow = nullptr; size_t xrow_cap = 0;      // centred scaled observation rows [npad][40], their squared norms and the centre:
   double* d_xnc = nullptr; size_t xnc_cap = 0;        // operands of the tensor-path builders (i8_distance 1 / 2, d <= 32)
   double* d_xmean = nullptr; size_t xmean_cap = 0;
@@ -255,6 +256,8 @@ extern "C" int plx_bo_create(int device, plx_bo_handle* out) {
   cudaFuncSetAttribute(sweep_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, I8_SMEM);
   cudaFuncSetAttribute(sweep_i8f_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, I8F_SMEM);
   cudaFuncSetAttribute(sweep_i8c_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, I8F_SMEM);
+  cudaFuncSetAttribute(sweep_i8f_gen_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, I8F_SMEM);
+  cudaFuncSetAttribute(sweep_i8c_gen_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, I8F_SMEM);
   cudaFuncSetAttribute(sweep_i8p_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, I8F_SMEM);
   cudaFuncSetAttribute(kstar_slices_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, KSL_SMEM);
   cudaFuncSetAttribute(refine_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -287,7 +290,7 @@ extern "C" void plx_bo_destroy(plx_bo_handle h) {
                   h->d_blk_val, h->d_blk_idx, h->d_rec, h->dcand[0], h->dcand[1],
                   h->d_out[0], h->d_out[1], h->d_out[2], h->rf_kv, h->rf_kp, h->rf_v, h->rf_w, h->rf_wpart, h->rf_vec,
                   h->rf_bounds, h->rf_val, h->rf_grad, h->rf_sc, h->rf_active, h->d_resident, h->d_misc, h->d_app,
-                  h->d_kplanes, h->d_zplanes, h->d_zscale, h->d_i8mean, h->d_i8part, h->d_i8sync, h->d_fs, h->d_xrow, h->d_xnc, h->d_xmean};
+                  h->d_kplanes, h->d_zplanes, h->d_zscale, h->d_i8mean, h->d_i8part, h->d_i8sync, h->d_fs, h->d_mgtab, h->d_xrow, h->d_xnc, h->d_xmean};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (h->h_pin) cudaFreeHost(h->h_pin);
   for (int i = 0; i < 2; ++i) { if (h->ev_copy[i]) cudaEventDestroy(h->ev_copy[i]); if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]); }
@@ -309,6 +312,11 @@ extern "C" int plx_bo_set_option(plx_bo_handle h, const char* name, long long va
   if (!h || !name) return PLX_ERR_INVALID;
   if (std::strcmp(name, "sweep_impl") == 0 && value >= 0 && value <= 7) { h->sweep_impl = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "lml_batch_limit") == 0 && value >= 0) { h->lml_batch_limit = static_cast<int>(value); return PLX_OK; }
+  if (std::strcmp(name, "gen_table") == 0 && (value == 0 || value == 1)) {
+    h->gen_table = static_cast<int>(value);
+    if (h->kind == K_GEN && h->d_mgtab && h->have_data) h->mg.tab = value ? h->d_mgtab : nullptr;
+    return PLX_OK;
+  }
   if (std::strcmp(name, "i8_distance") == 0 && value >= 0 && value <= 2) { h->i8_distance = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "blocking_sync") == 0 && (value == 0 || value == 1)) { h->blocking_sync = static_cast<int>(value); return PLX_OK; }
   if (std::strcmp(name, "potf_fused") == 0 && (value == 0 || value == 1)) { h->potf_fused = static_cast<int>(value); return PLX_OK; }
@@ -335,6 +343,14 @@ extern "C" int plx_gp_set_data(plx_bo_handle h, const double* X, const double* y
   CK(cudaSetDevice(h->device));
   h->n = n; h->d = d; h->kind = kind; h->jitter = jitter; h->kernel_id = kernel; h->nu = nu;
   h->mg = (kind == K_GEN) ? make_matern_gen(nu) : MaternGen{};
+  if (kind == K_GEN) {
+    // the sweeps read the kernel value from a table filled once per nu (gp_kernels.cuh); fit and refinement keep the routine
+    int rt;
+    if ((rt = ensure(h, h->d_mgtab, h->mgtab_cap, static_cast<size_t>(MG_NINT) * MG_ROW)) != PLX_OK) return rt;
+    matern_tab_kernel<<<MG_NINT, MG_DEG, 0, h->stream>>>(h->mg, h->d_mgtab);
+    LAUNCH_CHECK("matern_tab_kernel");
+    if (h->gen_table) h->mg.tab = h->d_mgtab;
+  }
   h->npad = (n + 127) / 128 * 128; h->nb = h->npad / 128;
   { const int nt32 = (n + 31) / 32; h->ntri = nt32 * (nt32 + 1) / 2; }   // lower 32-tiles that hold observations
   h->have_data = false; h->have_state = false; h->state_factor_valid = false;
@@ -837,7 +853,8 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     // 6: the four are two clusters of two that fetch the A stream once per pair (TMA multicast); measured equal to 5
     // (8.3 ms against 8.2 ms per 151 552 candidates: the operand stream is not what bounds the kernel), so the
     // default stays with the plain cooperative form
-    const bool paired = impl_i8 == 6;
+    const bool gen = p.kind == K_GEN;                  // its own instantiations; the paired form has none
+    const bool paired = impl_i8 == 6 && !gen;
     const int max_groups = h->num_sms / I8C_R;
     const int groups = static_cast<int>(std::min<long long>((p.N + 127) / 128, max_groups));
     if ((r = ensure(h, h->d_i8part, h->i8part_cap, static_cast<size_t>(max_groups) * 2 * I8C_R * 256)) != PLX_OK) return r;
@@ -883,7 +900,8 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     }
     {
       void* args[] = {&h->tmA8, &h->tmB8, &q, &ip, &h->d_i8part, &h->d_i8sync};
-      CK(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(sweep_i8c_kernel), dim3(groups * I8C_R), dim3(512), args,
+      CK(cudaLaunchCooperativeKernel(gen ? reinterpret_cast<const void*>(sweep_i8c_gen_kernel) : reinterpret_cast<const void*>(sweep_i8c_kernel),
+                                     dim3(groups * I8C_R), dim3(512), args,
                                      I8F_SMEM, st));
     }
     LAUNCH_CHECK("sweep_i8c_kernel");
@@ -903,7 +921,8 @@ static int launch_sweep_i8(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cuda
     ip.acq = p.acq; ip.kappa = p.kappa; ip.eps = p.eps; ip.y_max = p.y_max;
     ip.out_mean = p.out_mean; ip.out_std = p.out_std; ip.out_acq = p.out_acq;
     ip.blk_val = h->d_blk_val; ip.blk_idx = h->d_blk_idx; ip.a_from_smem = h->i8_a_from_smem; ip.zplanes_dbg = h->d_zplanes; ip.clamped = h->d_clamped;
-    sweep_i8f_kernel<<<grid, 512, I8F_SMEM, st>>>(h->tmA8, h->tmB8, q, ip, h->d_i8mean);
+    if (p.kind == K_GEN) sweep_i8f_gen_kernel<<<grid, 512, I8F_SMEM, st>>>(h->tmA8, h->tmB8, q, ip, h->d_i8mean);
+    else sweep_i8f_kernel<<<grid, 512, I8F_SMEM, st>>>(h->tmA8, h->tmB8, q, ip, h->d_i8mean);
     LAUNCH_CHECK("sweep_i8f_kernel");
     sweep_merge_kernel<<<1, 32, 0, st>>>(h->d_blk_val, h->d_blk_idx, grid, h->d_best_val, h->d_best_idx);
     LAUNCH_CHECK("sweep_merge_kernel");
@@ -955,7 +974,7 @@ static int launch_sweep(plx_bo* h, const SweepParams& p, cudaEvent_t e0, cudaEve
   }
   const int impl = h->sweep_impl == 7 ? 3 : h->sweep_impl;       // 7 = 3 with the small-set kernel forced on (it is on by default)
   const bool sliced = impl == 2 || impl >= 4 || (impl == 3 && p.n >= 256);
-  if (sliced && p.kind != K_GEN) return launch_sweep_i8(h, p, e0, e1);
+  if (sliced && (p.kind != K_GEN || p.mg.tab != nullptr)) return launch_sweep_i8(h, p, e0, e1);   // general nu: with its value table only
   if (e0) CK(cudaEventRecord(e0, h->stream));
   if (h->sweep_impl >= 1) {
     sweep_tma_kernel<<<grid, 384, SWEEP_SMEM, h->stream>>>(h->tmZ, h->tmK, p);

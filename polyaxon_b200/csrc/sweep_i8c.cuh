@@ -37,10 +37,9 @@ __device__ __forceinline__ int part_of(int h) { return ((h >> 2) & 1) ? 3 - (h &
 
 // gsync: [groups][2 buffers][4] counters {ready, done, free, unused}, zero at launch.
 // gpart: [groups][2 buffers][I8C_R][256]: 128 partial sums of squares, then 128 partial means.
-__global__ void __launch_bounds__(512, 1) sweep_i8c_kernel(const __grid_constant__ CUtensorMap tmA,
-                                                           const __grid_constant__ CUtensorMap tmB,
-                                                           const SweepParams p, const I8Params ip, double* gpart,
-                                                           unsigned* gsync) {
+template <bool GEN>
+__device__ __forceinline__ void sweep_i8c_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const SweepParams& p,
+                                               const I8Params& ip, double* gpart, unsigned* gsync) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = align1k(smem_raw);
   I8FTail* tail = reinterpret_cast<I8FTail*>(smem + I8_STAGES * I8_STAGE + F_STAGING);
@@ -93,7 +92,7 @@ __global__ void __launch_bounds__(512, 1) sweep_i8c_kernel(const __grid_constant
       const long long c1 = clock64();
 #endif
       signed char* rows = p.planes + static_cast<size_t>(buf_row0 + 128 * b) * p.npad;
-      if (!PLX_DBG(p.dbg, 128) || t < 2) build_tile(p, tile, rows, part_g + (b * I8C_R + r) * 256 + 128, sm, tid, r, I8C_R);
+      if (!PLX_DBG(p.dbg, 128) || t < 2) build_tile<GEN>(p, tile, rows, part_g + (b * I8C_R + r) * 256 + 128, sm, tid, r, I8C_R);
       __threadfence();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_ready + 8 * b);
@@ -286,6 +285,20 @@ __global__ void __launch_bounds__(512, 1) sweep_i8c_kernel(const __grid_constant
   asm volatile("tcgen05.fence::before_thread_sync;\n");
   __syncthreads();
   if (warp == 8) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" :: "r"(tmem), "n"(512));
+}
+
+__global__ void __launch_bounds__(512, 1) sweep_i8c_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                           const __grid_constant__ CUtensorMap tmB,
+                                                           const SweepParams p, const I8Params ip, double* gpart,
+                                                           unsigned* gsync) {
+  sweep_i8c_body<false>(tmA, tmB, p, ip, gpart, gsync);
+}
+// the general-nu Matern kernel (kernel values from the table of gp_kernels.cuh)
+__global__ void __launch_bounds__(512, 1) sweep_i8c_gen_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                               const __grid_constant__ CUtensorMap tmB,
+                                                               const SweepParams p, const I8Params ip, double* gpart,
+                                                               unsigned* gsync) {
+  sweep_i8c_body<true>(tmA, tmB, p, ip, gpart, gsync);
 }
 
 }  // namespace plx

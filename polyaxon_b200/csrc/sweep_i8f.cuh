@@ -70,7 +70,7 @@ __device__ __forceinline__ void builder_block(const SweepParams& p, double (&r2)
     double v[8];
 #pragma unroll
     for (int j = 0; j < 4; ++j) { v[j] = r2[i][j]; v[4 + j] = r2[i + 1][j]; }
-    kern_values_n<KIND, 8>(v);
+    kern_values_any<KIND, 8>(v, p.mg);
 #pragma unroll
     for (int u = 0; u < 2; ++u) {
       double k[4];
@@ -150,7 +150,7 @@ __device__ __forceinline__ void builder_rows_mma(const SweepParams& p, const dou
         }
         v[o] = r;
       }
-      kern_values_n<KIND, 8>(v);
+      kern_values_any<KIND, 8>(v, p.mg);
       double m = 0.0;
 #pragma unroll
       for (int o = 0; o < 8; ++o) { v[o] = (jo + o < p.n) ? v[o] : 0.0; m = fma(v[o], al[o], m); }
@@ -160,6 +160,7 @@ __device__ __forceinline__ void builder_rows_mma(const SweepParams& p, const dou
   }
 }
 
+template <bool GEN>
 __device__ __forceinline__ void build_tile_mma(const SweepParams& p, long long tile, signed char* rows, double* mean_out,
                                                uint32_t sm, int tid, int jb0, int jbstep) {
   const int warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
@@ -238,11 +239,15 @@ __device__ __forceinline__ void build_tile_mma(const SweepParams& p, long long t
           }
       }
     }
-    switch (p.kind) {
-      case K_RBF: builder_rows_mma<K_RBF>(p, acc, cn, rows, jb, sm, warp, g, t, macc); break;
-      case K_M05: builder_rows_mma<K_M05>(p, acc, cn, rows, jb, sm, warp, g, t, macc); break;
-      case K_M15: builder_rows_mma<K_M15>(p, acc, cn, rows, jb, sm, warp, g, t, macc); break;
-      default: builder_rows_mma<K_M25>(p, acc, cn, rows, jb, sm, warp, g, t, macc); break;
+    if constexpr (GEN) {
+      builder_rows_mma<K_GEN>(p, acc, cn, rows, jb, sm, warp, g, t, macc);
+    } else {
+      switch (p.kind) {
+        case K_RBF: builder_rows_mma<K_RBF>(p, acc, cn, rows, jb, sm, warp, g, t, macc); break;
+        case K_M05: builder_rows_mma<K_M05>(p, acc, cn, rows, jb, sm, warp, g, t, macc); break;
+        case K_M15: builder_rows_mma<K_M15>(p, acc, cn, rows, jb, sm, warp, g, t, macc); break;
+        default: builder_rows_mma<K_M25>(p, acc, cn, rows, jb, sm, warp, g, t, macc); break;
+      }
     }
   }
 #pragma unroll
@@ -257,9 +262,12 @@ __device__ __forceinline__ void build_tile_mma(const SweepParams& p, long long t
 // Builder role for one tile: planes into `rows` (plane 0, first candidate row of the tile buffer), means into mean_out.
 // Only the 64-observation blocks jb0, jb0 + jbstep, ... are built (1, 0 = all of them; the cooperative kernel deals
 // the blocks to the CTAs of a group, and mean_out then receives this CTA's partial means).
+// GEN: the instantiation for the general-nu Matern kernel (its own kernels below, so that the closed forms' code is
+// what it was without it)
+template <bool GEN>
 __device__ __forceinline__ void build_tile(const SweepParams& p, long long tile, signed char* rows, double* mean_out,
                                            uint32_t sm, int tid, int jb0 = 0, int jbstep = 1) {
-  if (p.xrow != nullptr) { build_tile_mma(p, tile, rows, mean_out, sm, tid, jb0, jbstep); return; }
+  if (p.xrow != nullptr) { build_tile_mma<GEN>(p, tile, rows, mean_out, sm, tid, jb0, jbstep); return; }
   const int tx = tid & 15, ty = tid >> 4;
   const long long c_base = tile * 128;
   const int nchunk_d = (p.d + 31) / 32;
@@ -320,11 +328,15 @@ __device__ __forceinline__ void build_tile(const SweepParams& p, long long tile,
       }
     }
     const int jo = jb * 64 + 4 * tx;
-    switch (p.kind) {
-      case K_RBF: builder_block<K_RBF>(p, r2, rows, jo, ty, macc); break;
-      case K_M05: builder_block<K_M05>(p, r2, rows, jo, ty, macc); break;
-      case K_M15: builder_block<K_M15>(p, r2, rows, jo, ty, macc); break;
-      default: builder_block<K_M25>(p, r2, rows, jo, ty, macc); break;
+    if constexpr (GEN) {
+      builder_block<K_GEN>(p, r2, rows, jo, ty, macc);
+    } else {
+      switch (p.kind) {
+        case K_RBF: builder_block<K_RBF>(p, r2, rows, jo, ty, macc); break;
+        case K_M05: builder_block<K_M05>(p, r2, rows, jo, ty, macc); break;
+        case K_M15: builder_block<K_M15>(p, r2, rows, jo, ty, macc); break;
+        default: builder_block<K_M25>(p, r2, rows, jo, ty, macc); break;
+      }
     }
   }
 #pragma unroll
@@ -340,9 +352,9 @@ __device__ __forceinline__ void build_tile(const SweepParams& p, long long tile,
 
 // p: the builders' view (candidates, observations, planes = this launch's plane buffer of gridDim.x * 2 tiles,
 // plane_stride); ip: the contraction's view (ip.mean = mean buffer of gridDim.x * 256 doubles).
-__global__ void __launch_bounds__(512, 1) sweep_i8f_kernel(const __grid_constant__ CUtensorMap tmA,
-                                                           const __grid_constant__ CUtensorMap tmB,
-                                                           const SweepParams p, const I8Params ip, double* meanbuf) {
+template <bool GEN>
+__device__ __forceinline__ void sweep_i8f_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const SweepParams& p,
+                                               const I8Params& ip, double* meanbuf) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = align1k(smem_raw);
   I8FTail* tail = reinterpret_cast<I8FTail*>(smem + I8_STAGES * I8_STAGE + F_STAGING);
@@ -380,7 +392,7 @@ __global__ void __launch_bounds__(512, 1) sweep_i8f_kernel(const __grid_constant
       const uint32_t b = t & 1, use = t >> 1;
       if (use > 0) mbar_wait(bar_free + 8 * b, (use - 1) & 1);       // the tile that used this buffer is consumed
       signed char* rows = p.planes + static_cast<size_t>(buf_row0 + 128 * b) * p.npad;
-      if (!PLX_DBG(p.dbg, 128) || t < 2) build_tile(p, tile, rows, meanbuf + buf_row0 + 128 * b, sm, tid);
+      if (!PLX_DBG(p.dbg, 128) || t < 2) build_tile<GEN>(p, tile, rows, meanbuf + buf_row0 + 128 * b, sm, tid);
       __threadfence();
       asm volatile("fence.proxy.async;\n" ::: "memory");            // generic-proxy stores -> visible to TMA
       __syncwarp();
@@ -475,6 +487,18 @@ __global__ void __launch_bounds__(512, 1) sweep_i8f_kernel(const __grid_constant
   asm volatile("tcgen05.fence::before_thread_sync;\n");
   __syncthreads();
   if (warp == 8) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" :: "r"(tmem), "n"(512));
+}
+
+__global__ void __launch_bounds__(512, 1) sweep_i8f_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                           const __grid_constant__ CUtensorMap tmB,
+                                                           const SweepParams p, const I8Params ip, double* meanbuf) {
+  sweep_i8f_body<false>(tmA, tmB, p, ip, meanbuf);
+}
+// the general-nu Matern kernel (kernel values from the table of gp_kernels.cuh)
+__global__ void __launch_bounds__(512, 1) sweep_i8f_gen_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                               const __grid_constant__ CUtensorMap tmB,
+                                                               const SweepParams p, const I8Params ip, double* meanbuf) {
+  sweep_i8f_body<true>(tmA, tmB, p, ip, meanbuf);
 }
 
 }  // namespace plx

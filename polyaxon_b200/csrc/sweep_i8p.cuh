@@ -103,7 +103,7 @@ __global__ void __launch_bounds__(512, 1) sweep_i8p_kernel(const __grid_constant
         named_bar_sync(1, 256);
       }
       signed char* rows = p.planes + static_cast<size_t>(buf_row0 + 128 * b) * p.npad;
-      if (!PLX_DBG(p.dbg, 128) || t < 2) build_tile(p, tile, rows, part_g + (b * I8C_R + r) * 256 + 128, sm, tid, r, I8C_R);
+      if (!PLX_DBG(p.dbg, 128) || t < 2) build_tile<false>(p, tile, rows, part_g + (b * I8C_R + r) * 256 + 128, sm, tid, r, I8C_R);
       __threadfence();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_ready + 8 * b);

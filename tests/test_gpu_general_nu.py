@@ -121,3 +121,40 @@ def test_refinement_and_gradient(handle, name):
         if s and v >= ref:
             ref = v
     assert best >= ref - 1e-6 * max(1.0, abs(ref))
+
+
+@pytest.mark.parametrize('n,d,nu,theta', [(300, 2, 1.9, -1.0), (40, 3, 0.7, 0.0), (700, 8, 3.3, 0.5), (1100, 20, 1.9, 1.0),
+                                          (260, 5, 1.9, 3.5)])
+def test_value_table_equals_the_bessel_routine(handle, n, d, nu, theta):
+    """The sweeps read the general-nu kernel value from a Chebyshev table of k(t) e^t (option gen_table 1, the default;
+    gp_kernels.cuh), filled once per nu from the Bessel routine, and use the routine itself below t = 1/4 and above 512
+    (theta = 3.5 puts every pair below 1/4: the two must then be identical).  Both paths through every sweep form that
+    takes the general kernel: thread per candidate (n <= 64), FP64 DMMA, int8-sliced fused and cooperative."""
+    from oracle.reference_path import synthetic_problem
+    X, y, _ = synthetic_problem(n, d, seed=17 + n)
+    handle.set_data(X, y, G.KERNEL_MATERN, nu)
+    handle.set_theta(theta)
+    rs = np.random.RandomState(n)
+    xc = np.vstack([X[:30], rs.uniform(0, 1, (128 * 9 + 7, d))])
+    cond = np.linalg.cond(G.kernel_matrix(X, theta, G.KERNEL_MATERN, nu) + G.GPR_ALPHA * np.eye(n))
+    out = {}
+    try:
+        for impl in ((3, 1) if n <= 64 else (3, 1, 4, 5)):
+            for tab in (0, 1):
+                if tab == 0 and impl in (4, 5):
+                    continue                               # the int8 forms take the general kernel with its table only
+                handle.set_option('sweep_impl', impl)
+                handle.set_option('gen_table', tab)
+                out[impl, tab] = handle.sweep(xc, G.ACQ_UCB, float(y.max()), kappa=1.0, dump=True)
+    finally:
+        handle.set_option('gen_table', 1)
+        handle.set_option('sweep_impl', 3)
+    ref = out[1, 0]                                         # FP64 DMMA sweep, Bessel routine for every value
+    scale = max(np.abs(ref[3]).max(), 1.0)
+    for key, res in out.items():
+        assert np.abs(res[3] - ref[3]).max() <= max(1e-11, 10 * EPS * cond) * scale, key
+        assert np.abs(res[4] ** 2 - ref[4] ** 2).max() <= max(1e-11, 10 * EPS * cond), key
+        if cond < 1e8:
+            assert res[1] == ref[1], key
+    if theta >= 3.0:
+        assert np.array_equal(out[1, 1][3], ref[3]) and np.array_equal(out[1, 1][4], ref[4])
