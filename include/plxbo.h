@@ -63,9 +63,9 @@ int plx_bo_set_stream(plx_bo_handle h, void* stream);
  * mean, u.v on the FP64 tensor path (mma.sync), pairs where that cancels recomputed directly; 2 [default] = 1 in the
  * cooperative form from 16 dimensions up (4 % faster there at the C3 shape), 0 otherwise (the fused form is slower with
  * it, and with few dimensions too many pairs need the recomputation); posterior equal to 1e-10);
- * "gen_table" (1 [default]: for a general Matern nu the sweeps read the kernel value from a Chebyshev table of
- * k(t) e^t filled once per nu from the Bessel routine -- 14x faster at the C3 shape, equal to the routine within
- * 1e-14 --; 0: the routine for every value; fit and refinement always use the routine);
+ * "gen_table" (1 [default]: for a general Matern nu the kernel value and its derivative are read from Chebyshev
+ * tables of k(t) e^t and g(t) e^t filled once per nu from the Bessel routine -- sweeps 27x faster at the C3 shape, fits
+ * as fast as with a closed form, equal to the routine within 1e-14 --; 0: the routine for every value);
  * "blocking_sync" (0 [default]: calls wait for the GPU by spinning on the stream; 1: the host thread sleeps on an
  * event instead -- for processes whose worker threads outnumber their cores);
  * "potf_fused" (1 [default]: the diagonal 128-blocks of the fit are factorised and inverted in one pass of 128 column

@@ -344,9 +344,9 @@ extern "C" int plx_gp_set_data(plx_bo_handle h, const double* X, const double* y
   h->n = n; h->d = d; h->kind = kind; h->jitter = jitter; h->kernel_id = kernel; h->nu = nu;
   h->mg = (kind == K_GEN) ? make_matern_gen(nu) : MaternGen{};
   if (kind == K_GEN) {
-    // the sweeps read the kernel value from a table filled once per nu (gp_kernels.cuh); fit and refinement keep the routine
+    // kernel value and derivative come from tables filled once per nu (gp_kernels.cuh)
     int rt;
-    if ((rt = ensure(h, h->d_mgtab, h->mgtab_cap, static_cast<size_t>(MG_NINT) * MG_ROW)) != PLX_OK) return rt;
+    if ((rt = ensure(h, h->d_mgtab, h->mgtab_cap, static_cast<size_t>(2) * MG_NINT * MG_ROW)) != PLX_OK) return rt;
     matern_tab_kernel<<<MG_NINT, MG_DEG, 0, h->stream>>>(h->mg, h->d_mgtab);
     LAUNCH_CHECK("matern_tab_kernel");
     if (h->gen_table) h->mg.tab = h->d_mgtab;

@@ -33,20 +33,22 @@ struct MaternGen {
   double nu, mu, coef, s;                // order, fractional order, 2^(1-nu)/Gamma(nu), sqrt(2 nu)
   double gam1, gam2, gampl, gammi;       // Temme's Gamma_1, Gamma_2, 1/Gamma(1+mu), 1/Gamma(1-mu)
   int nl;                                // upward recurrence steps: nu = mu + nl (nl = 0: mu = -nu)
-  const double* tab;                     // nullable, device: Chebyshev table of the kernel value for the sweeps (below)
+  const double* tab;                     // nullable, device: Chebyshev tables of the kernel value and its derivative (below)
 };
 
-// Table of the general-nu kernel value for the sweeps.  The Bessel routine below costs ~2 000 FP64 operations per value
-// (series / continued fraction to convergence, pow, log, sinh): at the C3 shape 358 ms per 151 552 candidates against
-// 20 ms for the closed forms.  For ONE nu the value k(t) = coef t^nu K_nu(t) is a fixed smooth function of t > 0, so
-// h(t) = k(t) e^t is tabulated once per handle as Chebyshev interpolants of degree 15 on the intervals
-// [t0 2^(i/2), t0 2^((i+1)/2)), i < MG_NINT (t0 = 1/4 ... 512; the only singularity, t^(2 nu) at 0, is 4.8 half-widths
-// away from every interval: interpolation error ~1e-16), filled from the routine below at the Chebyshev nodes.  Outside
-// [t0, 512) the routine itself is used.  Row i of the table: centre, 1 / half-width, c_0 / 2, c_1 .. c_15.
-constexpr int MG_NINT = 22, MG_DEG = 16, MG_ROW = MG_DEG + 2;
-constexpr double MG_T0 = 0.25, MG_SQRT2 = 1.4142135623730951;
+// Tables of the general-nu kernel.  The Bessel routine below costs ~2 000 FP64 operations per value (series / continued
+// fraction to convergence, pow, log, sinh): at the C3 shape 358 ms per 151 552 candidates of a sweep against 20 ms for
+// the closed forms, and ten times a closed form's time for the kernel matrices of a fit.  For ONE nu the value
+// k(t) = coef t^nu K_nu(t) and g(t) = coef t^(nu+1) K_(nu-1)(t), which carries both derivatives (dk/dtheta = g,
+// dk/d(r^2) = -nu g / t^2), are fixed smooth functions of t > 0.  h1 = k e^t and h2 = g e^t are tabulated once per handle
+// as Chebyshev interpolants of degree 15 on the intervals [t0 2^(i/2), t0 2^((i+1)/2)), i < MG_NINT (t0 = 2^-10 ... 512;
+// the only singularity, t^(2 nu) at 0, is 4.8 half-widths away from every interval: interpolation error ~1e-16 of the
+// interval's maximum), filled from the routine at the Chebyshev nodes.  Outside [t0, 512) the routine itself is used.
+// Row i of a table: centre, 1 / half-width, c_0 / 2, c_1 .. c_15; the table of h2 follows that of h1.
+constexpr int MG_E0 = 10, MG_NINT = 2 * (MG_E0 + 9), MG_DEG = 16, MG_ROW = MG_DEG + 2;
+constexpr double MG_SQRT2 = 1.4142135623730951;
 __device__ __forceinline__ double mg_edge(int i) {          // lower edge of interval i: exact products of powers of two and fl(sqrt 2)
-  return __hiloint2double((1023 - 2 + (i >> 1)) << 20, 0) * ((i & 1) ? MG_SQRT2 : 1.0);
+  return __hiloint2double((1023 - MG_E0 + (i >> 1)) << 20, 0) * ((i & 1) ? MG_SQRT2 : 1.0);
 }
 
 // K_nu(x) and K_{nu-1}(x) for x > 0
@@ -105,61 +107,82 @@ __device__ __forceinline__ void bessel_k_pair(const MaternGen& m, double x, doub
   k = rkmu; km1 = prev;
 }
 
+// k and g at t = sqrt(2 nu) r from the Bessel routine (the tables are filled from this; not inlined: it is the rare path of
+// the inner loops, which would otherwise carry a copy of the routine per unrolled value)
+__device__ __noinline__ void matern_gen_routine(const MaternGen& m, double t, double& val, double& g) {
+  double k, km1;
+  bessel_k_pair(m, t, k, km1);
+  const double tp = m.coef * pow(t, m.nu);
+  val = tp * k;
+  g = tp * t * km1;
+}
+
+// One CTA per interval, one thread per Chebyshev node / coefficient.
+__global__ void __launch_bounds__(MG_DEG) matern_tab_kernel(MaternGen m, double* __restrict__ tab) {
+  __shared__ double hs[2][MG_DEG];
+  const int i = blockIdx.x, k = threadIdx.x;
+  const double a = mg_edge(i), b = mg_edge(i + 1), cen = 0.5 * (a + b), hw = 0.5 * (b - a);
+  const double t = cen + hw * cospi((k + 0.5) / MG_DEG);
+  double val, g;
+  matern_gen_routine(m, t, val, g);
+  const double et = exp(t);
+  hs[0][k] = val * et; hs[1][k] = g * et;
+  __syncthreads();
+#pragma unroll
+  for (int f = 0; f < 2; ++f) {
+    double c = 0.0;
+    for (int q = 0; q < MG_DEG; ++q) c += hs[f][q] * cospi(k * (q + 0.5) / MG_DEG);
+    c *= 2.0 / MG_DEG;
+    double* row = tab + (f * MG_NINT + i) * MG_ROW;
+    row[2 + k] = (k == 0) ? 0.5 * c : c;
+    if (k == 0) { row[0] = cen; row[1] = 1.0 / hw; }
+  }
+}
+
+// interval of t in the tables, or -1 (no table, out of range, NaN): 2 floor(log2(t / t0)) + (mantissa >= sqrt 2)
+__device__ __forceinline__ int mg_interval(const MaternGen& m, double t) {
+  if (m.tab == nullptr || !(t >= mg_edge(0)) || !(t < 512.0)) return -1;
+  const int hi = __double2hiint(t);
+  const int e = ((hi >> 20) & 0x7ff) - 1023 + MG_E0;
+  const double mant = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(t));
+  return 2 * e + (mant >= MG_SQRT2 ? 1 : 0);
+}
+__device__ __forceinline__ double mg_cheb(const double* row, double x) {
+  const double x2 = 2.0 * x;
+  double b1 = row[2 + MG_DEG - 1], b2 = 0.0;
+#pragma unroll
+  for (int j = MG_DEG - 2; j >= 1; --j) { const double b0 = fma(x2, b1, row[2 + j] - b2); b2 = b1; b1 = b0; }
+  return fma(x, b1, row[2] - b2);
+}
+
 // value, d/dtheta and d/d(r^2) of the general-nu Matern kernel at squared scaled distance r2
 __device__ __forceinline__ void matern_gen_eval(const MaternGen& m, double r2, double& val, double& dtheta, double& dr2) {
   double r = sqrt(r2);
   if (r == 0.0) r = 2.220446049250313e-16;             // sklearn: K[K == 0.0] += eps
   const double t = m.s * r;
-  double k, km1;
-  bessel_k_pair(m, t, k, km1);
-  const double tp = m.coef * pow(t, m.nu);
-  val = tp * k;
-  dtheta = tp * t * km1;                                // d/dtheta, theta = log(length_scale): dt/dtheta = -t
-  dr2 = -m.nu * tp / t * km1;                           // d/d(r^2)
+  double g;
+  const int idx = mg_interval(m, t);
+  if (idx < 0) {
+    matern_gen_routine(m, t, val, g);
+  } else {
+    const double* row = m.tab + idx * MG_ROW;
+    const double x = (t - row[0]) * row[1], et = exp_neg(-t);
+    val = mg_cheb(row, x) * et;
+    g = mg_cheb(row + MG_NINT * MG_ROW, x) * et;
+  }
+  dtheta = g;                                           // d/dtheta, theta = log(length_scale): dt/dtheta = -t
+  dr2 = -m.nu * g / (t * t);                            // d/d(r^2)
 }
 
-// k at t = sqrt(2 nu) r directly (the table is filled from this; not inlined: it is the rare path of the sweeps'
-// inner loops, which would otherwise carry a copy of the Bessel routine per unrolled value)
-__device__ __noinline__ double matern_gen_value_t(const MaternGen& m, double t) {
-  double k, km1;
-  bessel_k_pair(m, t, k, km1);
-  return m.coef * pow(t, m.nu) * k;
-}
-
-// One CTA per interval, one thread per Chebyshev node / coefficient.
-__global__ void __launch_bounds__(MG_DEG) matern_tab_kernel(MaternGen m, double* __restrict__ tab) {
-  __shared__ double hs[MG_DEG];
-  const int i = blockIdx.x, k = threadIdx.x;
-  const double a = mg_edge(i), b = mg_edge(i + 1), cen = 0.5 * (a + b), hw = 0.5 * (b - a);
-  const double t = cen + hw * cospi((k + 0.5) / MG_DEG);
-  hs[k] = matern_gen_value_t(m, t) * exp(t);
-  __syncthreads();
-  double c = 0.0;
-  for (int q = 0; q < MG_DEG; ++q) c += hs[q] * cospi(k * (q + 0.5) / MG_DEG);
-  c *= 2.0 / MG_DEG;
-  double* row = tab + i * MG_ROW;
-  row[2 + k] = (k == 0) ? 0.5 * c : c;
-  if (k == 0) { row[0] = cen; row[1] = 1.0 / hw; }
-}
-
-// The kernel value for the sweeps: from the table where it reaches, else from the routine.
+// The kernel value alone (the sweeps).
 __device__ __forceinline__ double matern_gen_value(const MaternGen& m, double r2) {
   double r = sqrt(r2);
   if (r == 0.0) r = 2.220446049250313e-16;             // sklearn: K[K == 0.0] += eps
   const double t = m.s * r;
-  if (m.tab == nullptr || !(t >= MG_T0) || !(t < 512.0)) return matern_gen_value_t(m, t);     // (NaN goes this way too)
-  // interval: 2 floor(log2(4 t)) + (mantissa >= sqrt 2)
-  const int hi = __double2hiint(t);
-  const int e = ((hi >> 20) & 0x7ff) - 1023 + 2;
-  const double mant = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(t));
-  const int idx = 2 * e + (mant >= MG_SQRT2 ? 1 : 0);
+  const int idx = mg_interval(m, t);
+  if (idx < 0) { double val, g; matern_gen_routine(m, t, val, g); return val; }
   const double* row = m.tab + idx * MG_ROW;
-  const double x = (t - row[0]) * row[1], x2 = 2.0 * x;
-  double b1 = row[2 + MG_DEG - 1], b2 = 0.0;
-#pragma unroll
-  for (int j = MG_DEG - 2; j >= 1; --j) { const double b0 = fma(x2, b1, row[2 + j] - b2); b2 = b1; b1 = b0; }
-  const double h = fma(x, b1, row[2] - b2);
-  return h * exp_neg(-t);
+  return mg_cheb(row, (t - row[0]) * row[1]) * exp_neg(-t);
 }
 
 __device__ __forceinline__ double kern_value(int kind, double r2, const MaternGen& mg) {

@@ -126,10 +126,10 @@ def test_refinement_and_gradient(handle, name):
 @pytest.mark.parametrize('n,d,nu,theta', [(300, 2, 1.9, -1.0), (40, 3, 0.7, 0.0), (700, 8, 3.3, 0.5), (1100, 20, 1.9, 1.0),
                                           (260, 5, 1.9, 3.5)])
 def test_value_table_equals_the_bessel_routine(handle, n, d, nu, theta):
-    """The sweeps read the general-nu kernel value from a Chebyshev table of k(t) e^t (option gen_table 1, the default;
-    gp_kernels.cuh), filled once per nu from the Bessel routine, and use the routine itself below t = 1/4 and above 512
-    (theta = 3.5 puts every pair below 1/4: the two must then be identical).  Both paths through every sweep form that
-    takes the general kernel: thread per candidate (n <= 64), FP64 DMMA, int8-sliced fused and cooperative."""
+    """The general-nu kernel value (and its derivative) come from Chebyshev tables of k(t) e^t (option gen_table 1, the
+    default; gp_kernels.cuh), filled once per nu from the Bessel routine, which itself is used below t = 2^-10 and above
+    512 (theta = 3.5 exercises the intervals far below t = 1).  Both paths through every sweep form that takes the general
+    kernel: thread per candidate (n <= 64), FP64 DMMA, int8-sliced fused and cooperative."""
     from oracle.reference_path import synthetic_problem
     X, y, _ = synthetic_problem(n, d, seed=17 + n)
     handle.set_data(X, y, G.KERNEL_MATERN, nu)
@@ -156,5 +156,29 @@ def test_value_table_equals_the_bessel_routine(handle, n, d, nu, theta):
         assert np.abs(res[4] ** 2 - ref[4] ** 2).max() <= max(1e-11, 10 * EPS * cond), key
         if cond < 1e8:
             assert res[1] == ref[1], key
-    if theta >= 3.0:
-        assert np.array_equal(out[1, 1][3], ref[3]) and np.array_equal(out[1, 1][4], ref[4])
+
+
+@pytest.mark.parametrize('n,d,theta', [(300, 4, -0.5), (512, 16, 1.1), (150, 2, 2.0)])
+def test_tables_carry_the_derivatives_of_fit_and_refinement(handle, n, d, theta):
+    """With the tables the LML, its theta-gradient and the acquisition gradient no longer call the Bessel routine
+    (dk/dtheta = g, dk/d(r^2) = -nu g / t^2 with g = coef t^(nu+1) K_(nu-1) tabulated beside k): same numbers as the routine."""
+    from oracle.reference_path import synthetic_problem
+    X, y, _ = synthetic_problem(n, d, seed=5 + n)
+    pts = np.random.RandomState(n).uniform(0, 1, (40, d))
+    out = {}
+    try:
+        for tab in (0, 1):
+            handle.set_option('gen_table', tab)
+            handle.set_data(X, y, G.KERNEL_MATERN, 1.9)
+            lml, grad = handle.lml(np.array([theta, theta - 0.4]))
+            handle.set_theta(theta)
+            v, g = handle.acq_value_grad(pts, G.ACQ_EI, float(y.max()), eps=0.0)
+            out[tab] = (lml, grad, v, g)
+    finally:
+        handle.set_option('gen_table', 1)
+    cond = np.linalg.cond(G.kernel_matrix(X, theta, G.KERNEL_MATERN, 1.9) + G.GPR_ALPHA * np.eye(n))
+    tol = max(1e-11, 100 * EPS * cond)
+    assert np.allclose(out[0][0], out[1][0], rtol=tol, atol=0)
+    assert np.allclose(out[0][1], out[1][1], rtol=tol, atol=tol * np.abs(out[0][0]).max())
+    assert np.abs(out[0][2] - out[1][2]).max() <= tol * max(np.abs(out[0][2]).max(), 1e-300)
+    assert np.abs(out[0][3] - out[1][3]).max() <= tol * max(np.abs(out[0][3]).max(), 1e-300)
