@@ -1,3 +1,5 @@
+"""General-nu Matern: acquisition value / gradient and LML / gradient with the Chebyshev tables (gen_table 1) against the Bessel
+routine (0) at a few states.  python tools/gen_nu_grad_check.py"""
 import sys
 sys.path.insert(0, '.')
 import numpy as np
