@@ -124,7 +124,7 @@ def test_refinement_and_gradient(handle, name):
 
 
 @pytest.mark.parametrize('n,d,nu,theta', [(300, 2, 1.9, -1.0), (40, 3, 0.7, 0.0), (700, 8, 3.3, 0.5), (1100, 20, 1.9, 1.0),
-                                          (260, 5, 1.9, 3.5)])
+                                          (260, 5, 1.9, 3.5), (120, 3, 0.2, 0.0), (200, 4, 12.5, 0.3)])
 def test_value_table_equals_the_bessel_routine(handle, n, d, nu, theta):
     """The general-nu kernel value (and its derivative) come from Chebyshev tables of k(t) e^t (option gen_table 1, the
     default; gp_kernels.cuh), filled once per nu from the Bessel routine, which itself is used below t = 2^-10 and above
