@@ -1455,6 +1455,7 @@ extern "C" int plx_bo_reserve(plx_bo_handle h, int n, int d, int runs, int seeds
     if ((r = ensure(h, h->d_alpha_state, h->as_cap, static_cast<size_t>(h->npad))) != PLX_OK) break;
     if ((r = ensure(h, h->dKs, h->ks_cap, static_cast<size_t>(h->num_sms) * 128 * h->npad)) != PLX_OK) break;
     if ((r = ensure(h, h->dXt, h->xt_cap, static_cast<size_t>(d) * h->npad)) != PLX_OK) break;
+    if ((r = ensure(h, h->d_mgtab, h->mgtab_cap, static_cast<size_t>(2) * MG_NINT * MG_ROW)) != PLX_OK) break;   // general-nu tables (11 KB)
     if (n >= 256 && (r = ensure_i8(h)) != PLX_OK) break;
     if (seeds > 0 && (r = ensure_refine(h, seeds)) != PLX_OK) break;
     if (candidates > 0) {
