@@ -339,6 +339,39 @@ def workload_config(args, world):
             'l2': 'inputs larger than L2 (candidate block >= 0.5 GB per rank)'}
 
 
+def measure_general_nu(nu=1.9, N=148 * 128 * 8):
+    """Matern nu = 1.9 (the value in the reference's own fixtures) at the C3 shape: one sweep over 151 552 device
+    candidates with the kernel value from the per-nu Chebyshev tables (default) and from the Bessel routine per value,
+    and a three-run fit the same two ways.  Same arg-max both ways."""
+    import torch
+    from polyaxon_b200 import _lib
+    from oracle.reference_path import synthetic_problem
+    X, y, _ = synthetic_problem(N_OBS, D)
+    g = _lib.Handle(int(os.environ.get('LOCAL_RANK', '0')))
+    out = {'nu': nu, 'candidates': N, 'n_obs': N_OBS, 'd': D}
+    try:
+        xc = torch.rand(N, D, dtype=torch.float64, device='cuda', generator=torch.Generator(device='cuda').manual_seed(7))
+        torch.cuda.synchronize()
+        rs = np.random.RandomState(3)
+        restarts = rs.uniform(np.log(1e-5), np.log(1e5), 2)
+        best = {}
+        for tab, key in ((1, 'tables'), (0, 'routine')):
+            g.set_option('gen_table', tab)
+            g.set_data(X, y, _lib.KERNEL_MATERN, nu)
+            t0 = time.perf_counter()
+            g.fit(0.0, restarts, apply=False)
+            out['fit3_ms_' + key] = (time.perf_counter() - t0) * 1e3
+            g.set_theta(THETA)
+            for _ in range(2):
+                v, i, _ = g.sweep_dev(xc.data_ptr(), N, _lib.ACQ_POI, float(y.max()))
+            out['sweep_ms_' + key] = g.last_sweep_stats()[0]
+            best[key] = i
+        out['same_argmax'] = bool(best['tables'] == best['routine'])
+    finally:
+        g.close()
+    return out
+
+
 def measure_dgemm_tflops(torch, dev, n=8192, reps=6):
     a = torch.randn(n, n, dtype=torch.float64, device=dev)
     b = torch.randn(n, n, dtype=torch.float64, device=dev)
@@ -640,6 +673,11 @@ def main():
                 line['fit_c4'] = measure_fit(h)
             except Exception as exc:
                 line['fit_c4'] = 'failed: %r' % (exc,)
+            try:
+                line['general_nu'] = measure_general_nu()
+                line['general_nu_sweep_ms'] = line['general_nu']['sweep_ms_tables']
+            except Exception as exc:
+                line['general_nu'] = 'failed: %r' % (exc,)
     if line is not None:
         print(json.dumps(line))
     h.close()
